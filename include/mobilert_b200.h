@@ -1,0 +1,186 @@
+/*
+ * mobilert_b200.h — C-ABI of libmobilert_b200.so: the B200-native (sm_100a CUDA) drop-in for MobileRT's
+ * per-pixel ray-tracing hot path (Renderer::renderFrame -> Shader::rayTrace/shadowTrace -> BVH -> intersect -> shade).
+ *
+ * Every entry point cites the reference interface it replaces (paths relative to the reference's app/ directory).
+ * Plain pointers and sizes only; no exceptions cross this boundary; every function returns an mrt_status
+ * (0 = ok) unless stated otherwise and leaves errno == 0 on success, because the reference's callers poll errno
+ * right after the frame (System_dependent/Native/C_wrapper.cpp:234, Android_JNI/JNI_layer.cpp:821).
+ * There is no CPU fallback: without a CUDA device every compute entry point fails with MRT_ERR_CUDA.
+ */
+#ifndef MOBILERT_B200_H
+#define MOBILERT_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum mrt_status {
+    MRT_OK = 0,
+    MRT_ERR_INVALID = 1,   /* bad argument (null pointer, negative size, unknown enum) */
+    MRT_ERR_CUDA = 2,      /* CUDA runtime error or no device; see mrt_last_error() */
+    MRT_ERR_OOM = 3,       /* host or device allocation failed (JNI maps this to LowMemoryException, JNI_layer.cpp:706-715) */
+    MRT_ERR_STOPPED = 4,   /* mrt_stop() was called while rendering (Renderer::stopRender, MobileRT/Renderer.cpp:93-99) */
+    MRT_ERR_OVERFLOW = 5   /* an internal queue or traversal stack overflowed; result is invalid */
+} mrt_status;
+
+/* ---- scene records: byte-for-byte the reference's own layouts ---------------------------------------------- */
+/* MobileRT/Shapes/Triangle.hpp:18-27 (100 bytes) */
+typedef struct mrt_triangle {
+    float AC[3], AB[3], A[3];
+    float nA[3], nB[3], nC[3];
+    float tA[2], tB[2], tC[2];
+    int32_t material;
+} mrt_triangle;
+/* MobileRT/Shapes/Sphere.hpp (20 bytes): centre, squared radius, material index */
+typedef struct mrt_sphere { float center[3]; float sq_radius; int32_t material; } mrt_sphere;
+/* MobileRT/Shapes/Plane.hpp (28 bytes): unit normal, point, material index */
+typedef struct mrt_plane { float normal[3]; float point[3]; int32_t material; } mrt_plane;
+/* MobileRT/Material.hpp:18-38 without the texture */
+typedef struct mrt_material { float Le[3], Kd[3], Ks[3], Kt[3]; float ior; } mrt_material;
+
+enum { MRT_LIGHT_POINT = 0, MRT_LIGHT_AREA = 1 };
+/* Components/Lights/PointLight.hpp:12-13, AreaLight.hpp:19-21 (+ Light::radiance_.Le_, MobileRT/Light.hpp:16) */
+typedef struct mrt_light {
+    int32_t kind;
+    float position[3];       /* point light */
+    mrt_triangle triangle;   /* area light */
+    float Le[3];
+} mrt_light;
+
+/* MobileRT/Scene.hpp:20-27 flattened. The library copies everything at mrt_create; the caller may free at once. */
+typedef struct mrt_scene_desc {
+    const mrt_triangle *triangles; int64_t n_triangles;
+    const mrt_sphere *spheres;     int64_t n_spheres;
+    const mrt_plane *planes;       int64_t n_planes;
+    const mrt_material *materials; int64_t n_materials;
+    const mrt_light *lights;       int64_t n_lights;
+} mrt_scene_desc;
+
+enum { MRT_CAMERA_PERSPECTIVE = 0, MRT_CAMERA_ORTHOGRAPHIC = 1 };
+/* Arguments of Perspective(position, lookAt, up, hFovDeg, vFovDeg) (Components/Cameras/Perspective.cpp:8-14)
+ * or Orthographic(position, lookAt, up, sizeH, sizeV) (Components/Cameras/Orthographic.cpp:7-13). */
+typedef struct mrt_camera_desc {
+    int32_t kind;
+    float position[3], look_at[3], up[3];
+    float a, b;
+} mrt_camera_desc;
+
+/* Shader ids of MobileRT::Config::shader (MobileRT/Config.hpp, C_wrapper.cpp:154-194) */
+enum { MRT_SHADER_NOSHADOWS = 0, MRT_SHADER_WHITTED = 1, MRT_SHADER_PATHTRACER = 2, MRT_SHADER_DEPTHMAP = 3, MRT_SHADER_DIFFUSE = 4 };
+/* MobileRT/Shader.hpp:20-24 plus the new value a front-end selects to get this library */
+enum { MRT_ACC_NAIVE = 1, MRT_ACC_REGULAR_GRID = 2, MRT_ACC_BVH = 3, MRT_ACC_B200 = 4 };
+/* pixel-jitter sampler (C_wrapper.cpp:144-148 picks Constant(0.5) for spp==1, StaticHaltonSeq otherwise) */
+enum { MRT_SAMPLER_AUTO = 0, MRT_SAMPLER_CONSTANT = 1, MRT_SAMPLER_STATIC_HALTON = 2, MRT_SAMPLER_STATIC_MT = 3 };
+
+enum {
+    MRT_FLAG_FP32_ACCUMULATE = 1,  /* accumulate radiance in fp32 and quantise once (needed for multi-GPU partitions);
+                                      default is the reference's 8-bit running average (MobileRT/Utils/Utils.cpp:66-90) */
+    MRT_FLAG_SORT_BY_MATERIAL = 2, /* wavefront path tracer: counting-sort the hit queue by material before shading */
+    MRT_FLAG_REPLAY_SAMPLERS = 4   /* deterministic shaders: replay the reference's single-thread draw order of
+                                      getLightIndex / AreaLight::getPosition exactly (count + scan + render) */
+};
+
+typedef struct mrt_render_desc {
+    int32_t width, height;          /* used as given; front-ends round to x16 first (Qt main.cpp:36-44, F8) */
+    int32_t samples_pixel;          /* Config::samplesPixel */
+    int32_t samples_light;          /* Config::samplesLight */
+    int32_t shader;                 /* MRT_SHADER_* */
+    int32_t accelerator;            /* must be MRT_ACC_B200 or MRT_ACC_BVH (both select the BVH8 path) */
+    int32_t pixel_sampler;          /* MRT_SAMPLER_* */
+    uint32_t seed;                  /* seeds the library's own table shuffles when mrt_sampler_tables is NULL */
+    uint32_t flags;                 /* MRT_FLAG_* */
+    float depth_max_point[3];       /* DepthMap's maxPoint (Components/Shaders/DepthMap.cpp:7-10) */
+    int32_t device;                 /* CUDA device ordinal; -1 = current */
+} mrt_render_desc;
+
+/* The reference's shuffled tables, when the caller wants the very same sequences (parity runs):
+ * tile_order = Renderer.cpp:12 (256 floats); shader_table = Shader.cpp:20 (1<<20 floats, getLightIndex and
+ * getCosineSampleHemisphere); static_halton = Components/Samplers/StaticHaltonSeq.cpp:7 (1<<20, pixel jitter, area
+ * lights, russian roulette); static_mt = StaticMersenneTwister.cpp:7. Any pointer may be NULL. */
+typedef struct mrt_sampler_tables {
+    const float *tile_order;
+    const float *shader_table;
+    const float *static_halton;
+    const float *static_mt;
+} mrt_sampler_tables;
+
+typedef struct mrt_stats {
+    double build_ms;            /* "Creating Time": acceleration-structure build on the GPU (C_wrapper.cpp:152-198) */
+    double upload_ms;           /* host->device copy of the scene */
+    double frame_ms;            /* last frame, device time */
+    double extend_ms, shadow_ms, shade_ms, other_ms; /* last frame, device time per kernel class */
+    uint64_t rays_primary, rays_shadow, rays_secondary; /* last frame; their sum is the reference's "Casted rays" (MobileRT/Ray.cpp:11,26) */
+    uint64_t launches;          /* kernels launched by the last frame */
+    uint64_t bvh_nodes, bvh_bytes, scene_bytes;
+    int64_t  n_primitives;      /* JNI rtInitialize's return value (JNI_layer.cpp:676-680) */
+} mrt_stats;
+
+typedef struct mrt_handle mrt_handle;
+
+/* Replaces: Scene -> Shader subclass ctor (-> Shader::initializeAccelerators, MobileRT/Shader.cpp:33-77, BVH build
+ * MobileRT/Accelerators/BVH.hpp:125-283) -> Renderer ctor (MobileRT/Renderer.cpp:25-45), i.e. what work_thread
+ * (C_wrapper.cpp:76-203) and rtInitialize (JNI_layer.cpp:465-716) do before the first frame. */
+int mrt_create(const mrt_scene_desc *scene, const mrt_camera_desc *camera, const mrt_render_desc *render,
+               const mrt_sampler_tables *tables, mrt_handle **out);
+/* Replaces: ~Renderer / renderer_.reset (C_wrapper.cpp:266, JNI_layer.cpp:406-431). */
+void mrt_destroy(mrt_handle *h);
+
+/* Replaces: Renderer::renderFrame(int32* bitmap, int nThreads) (MobileRT/Renderer.cpp:53-88). Blocking. Writes packed
+ * ABGR8888 (0xFF000000|B<<16|G<<8|R, MobileRT/Utils/Utils.cpp:66-90) into the caller-owned HOST bitmap of
+ * width*height int32. The thread count of the reference signature has no meaning here. */
+int mrt_render_frame(mrt_handle *h, int32_t *host_bitmap);
+/* Same, into a caller-owned DEVICE buffer (headless replacement of the GL/Qt display path). */
+int mrt_render_frame_device(mrt_handle *h, void *device_bitmap);
+/* Multi-GPU building block (sample partition): renders samples sample_begin, sample_begin+sample_stride, ...
+ * (< samples_pixel) and ADDS their radiance into a caller-owned DEVICE fp32 RGBA buffer (width*height*4 floats;
+ * .w counts samples). The buffers of all ranks are summed by one NCCL reduce, then resolved on the root. */
+int mrt_render_accumulate_device(mrt_handle *h, void *device_accum_rgba32f, int32_t sample_begin, int32_t sample_stride);
+/* Quantises an fp32 RGBA accumulator (sum of per-sample trunc(255*c), .w = sample count) to ABGR8888 on the device. */
+int mrt_resolve_device(mrt_handle *h, const void *device_accum_rgba32f, void *device_bitmap);
+
+/* Replaces: the camera_ member the front-ends rebuild between frames (JNI_layer.cpp:164; C_wrapper.cpp:76-141). */
+int mrt_set_camera(mrt_handle *h, const mrt_camera_desc *camera);
+
+/* Replaces: Renderer::stopRender (Renderer.cpp:93-99), Renderer::getSample (:176-178),
+ * Renderer::getTotalCastedRays (:204-207). Thread-safe; may be called while mrt_render_frame runs. */
+int mrt_stop(mrt_handle *h);
+int mrt_get_sample(mrt_handle *h, int32_t *sample);
+int mrt_get_total_rays(mrt_handle *h, uint64_t *rays);
+int mrt_get_stats(mrt_handle *h, mrt_stats *stats);
+/* Human-readable description of the last failure on this handle (or of the last failed mrt_create when h == NULL). */
+const char *mrt_last_error(mrt_handle *h);
+
+/* Per-ray ground-truth access for parity tests (what Shader::rayTrace's geometric part, Shader.cpp:86-111, and
+ * Shader::shadowTrace, :132-158, compute). HOST arrays. origin_kind/origin_idx give the primitive a ray leaves
+ * (self-hit skip, Triangle.cpp:64, Plane.cpp:39); shadow_dist[i] >= 0 selects any-hit semantics.
+ * out_kind: 0 miss, 1 plane, 2 sphere, 3 triangle, 4 light; out_idx indexes the arrays given to mrt_create. */
+int mrt_trace_rays(mrt_handle *h, int64_t n, const float *origins, const float *directions,
+                   const int32_t *origin_kind, const int32_t *origin_idx, const float *shadow_dist,
+                   float *out_t, int32_t *out_kind, int32_t *out_idx, int32_t *out_material, float *out_normal);
+/* Camera::generateRay (Perspective.cpp:16-28, Orthographic.cpp:15-23) for n (u,v,du,dv) tuples. HOST arrays. */
+int mrt_generate_rays(mrt_handle *h, int64_t n, const float *uvdd, float *out_origins, float *out_directions);
+/* Shader::rayTrace (Shader.cpp:86) on arbitrary rays of the given depth -> rgb (deterministic shaders). HOST arrays. */
+int mrt_shade_rays(mrt_handle *h, int64_t n, const float *origins, const float *directions, int32_t depth, float *out_rgb);
+
+/* Primitive-level device functions exposed for the reference's known-answer tests (Unit_Testing/TestTriangle.cpp,
+ * TestAABB.cpp, TestPlane.cpp). Each runs the device function in a one-thread kernel. */
+int mrt_test_triangle_intersect(const mrt_triangle *tri, const float *o, const float *d, float t_max, int32_t self_skip,
+                                float *out_t, float *out_normal_uv_point8);
+int mrt_test_sphere_intersect(const mrt_sphere *s, const float *o, const float *d, float t_max, float *out_t, float *out_normal);
+int mrt_test_plane_intersect(const mrt_plane *p, const float *o, const float *d, float t_max, float *out_t);
+int mrt_test_aabb_intersect(const float *box_min, const float *box_max, const float *o, const float *d, int32_t *out_hit);
+int mrt_test_incremental_avg(const float *rgb, int32_t avg, int32_t num_sample, int32_t *out);
+/* MobileRT::haltonSequence (MobileRT/Utils/Utils.cpp:43-53) evaluated on the device for indices [first, first+n). */
+int mrt_test_halton(uint32_t first, int64_t n, uint32_t base, float *out);
+
+/* Library / device info: returns the number of CUDA devices visible, 0 when none (never falls back to the CPU). */
+int mrt_device_count(void);
+const char *mrt_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MOBILERT_B200_H */

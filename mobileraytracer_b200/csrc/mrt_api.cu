@@ -1,0 +1,637 @@
+// C-ABI of libmobilert_b200.so (include/mobilert_b200.h): handle, scene upload, frame driver.
+// Host logic only; every ray is traced by the CUDA kernels of mrt_render.cu / mrt_wavefront.cu. No CPU fallback.
+#include "../../include/mobilert_b200.h"
+#include "mrt_build.h"
+#include "mrt_refbvh.h"
+#include "mrt_render.h"
+#include "mrt_wavefront.h"
+#include <atomic>
+#include <cerrno>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <random>
+#include <string>
+#include <vector>
+
+using namespace mrt;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct DevMem {
+    void *p = nullptr;
+    size_t bytes = 0;
+    ~DevMem() { release(); }
+    void release() { if (p) { cudaFree(p); p = nullptr; bytes = 0; } }
+    cudaError_t alloc(size_t n) { release(); bytes = n; return cudaMalloc(&p, n ? n : 16); }
+    cudaError_t upload(const void *src, size_t n, cudaStream_t st) {
+        cudaError_t e = alloc(n);
+        if (e != cudaSuccess || n == 0) { return e; }
+        return cudaMemcpyAsync(p, src, n, cudaMemcpyHostToDevice, st);
+    }
+    template <typename T> T *as() const { return static_cast<T *>(p); }
+};
+
+}  // namespace
+
+struct mrt_handle {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+    std::vector<cudaEvent_t> sample_events;
+    SceneDev scene {};
+    CameraRec camera {};
+    RenderParams rp {};
+    uint32_t flags = 0;
+    Bvh8 bvh {};
+    DevMem d_tris9, d_tri_shade, d_sphere_nodes, d_spheres, d_plane_nodes, d_planes, d_materials, d_lights;
+    DevMem d_tile, d_shader_table, d_static_halton, d_static_mt, d_inv_tile, d_bitmap, d_accum, d_counters, d_scratch;
+    std::vector<int> plane_slot_of_id, sphere_slot_of_id;
+    int32_t *h_pinned_bitmap = nullptr;
+    size_t pinned_bytes = 0;
+    std::atomic<int> stop {0};
+    std::atomic<int> sample {0};
+    std::atomic<unsigned long long> total_rays {0};
+    mrt_stats stats {};
+    std::string error;
+    std::mutex mutex;
+    Wavefront *wavefront = nullptr;
+};
+
+namespace {
+
+int fail(mrt_handle *h, int code, const std::string &msg) {
+    if (h) { h->error = msg; } else { g_create_error = msg; }
+    errno = 0;
+    return code;
+}
+int cuda_fail(mrt_handle *h, cudaError_t e, const char *what) {
+    const int code = (e == cudaErrorMemoryAllocation) ? MRT_ERR_OOM : MRT_ERR_CUDA;
+    return fail(h, code, std::string(what) + ": " + cudaGetErrorString(e));
+}
+#define API_CUDA(h, x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { return cuda_fail((h), e_, #x); } } while (0)
+
+// Camera ctor (MobileRT/Camera.cpp:14-19) + Perspective ctor (Perspective.cpp:8-14, degToRad Camera.cpp:28-31)
+// + Orthographic ctor (Orthographic.cpp:7-13)
+CameraRec make_camera(const mrt_camera_desc &c) {
+    CameraRec r {};
+    r.kind = c.kind;
+    const v3 pos = mk3(c.position[0], c.position[1], c.position[2]);
+    const v3 look = mk3(c.look_at[0], c.look_at[1], c.look_at[2]);
+    const v3 up = mk3(c.up[0], c.up[1], c.up[2]);
+    r.position = pos;
+    r.direction = normalize(look - pos);
+    r.right = cross(up, r.direction);
+    r.up = cross(r.direction, r.right);
+    if (c.kind == MRT_CAMERA_PERSPECTIVE) {
+        const float pi = 3.14159265358979323846264338327950288f;
+        r.a = (c.a * pi) / 180.0f;
+        r.b = (c.b * pi) / 180.0f;
+    } else {
+        r.a = c.a / 2.0f;
+        r.b = c.b / 2.0f;
+    }
+    return r;
+}
+
+// fillArrayWithHaltonSeq (MobileRT/Utils/Utils.hpp:209-218) with a caller-visible seed instead of std::random_device
+void make_halton_table(std::vector<float> &t, size_t n, uint32_t seed) {
+    t.resize(n);
+    for (size_t i = 0; i < n; ++i) { t[i] = halton_sequence(static_cast<uint32_t>(i), 2u); }
+    std::mt19937 gen(seed);
+    std::shuffle(t.begin(), t.end(), gen);
+}
+// fillArrayWithMersenneTwister (Utils.hpp:230-235)
+void make_mt_table(std::vector<float> &t, size_t n, uint32_t seed) {
+    t.resize(n);
+    std::uniform_real_distribution<float> dist(0.0f, 1.0f);
+    std::mt19937 gen(seed);
+    for (size_t i = 0; i < n; ++i) { t[i] = dist(gen); }
+}
+
+int upload_scene(mrt_handle *h, const mrt_scene_desc &sc) {
+    cudaStream_t st = h->stream;
+    const int64_t nt = sc.n_triangles, nl = sc.n_lights;
+    int64_t n_area = 0;
+    for (int64_t i = 0; i < nl; ++i) { if (sc.lights[i].kind == MRT_LIGHT_AREA) { ++n_area; } }
+    if (nt + nl > 0x7ffffff0ll) { return fail(h, MRT_ERR_INVALID, "too many primitives"); }
+    // BVH8 primitive ids: [0, nt) scene triangles, nt + i = light i (point lights get a degenerate, unhittable triangle)
+    const int64_t nprims = nt + (n_area > 0 ? nl : 0);
+    std::vector<float> tris9(static_cast<size_t>(nprims) * 9);
+    std::vector<TriShade> shade(static_cast<size_t>(nt > 0 ? nt : 1));
+    for (int64_t i = 0; i < nt; ++i) {
+        const mrt_triangle &t = sc.triangles[i];
+        float *o = &tris9[static_cast<size_t>(i) * 9];
+        for (int k = 0; k < 3; ++k) { o[k] = t.A[k]; o[3 + k] = t.AB[k]; o[6 + k] = t.AC[k]; }
+        TriShade &s = shade[static_cast<size_t>(i)];
+        s.s0 = make_float4(t.nA[0], t.nA[1], t.nA[2], t.nB[0]);
+        s.s1 = make_float4(t.nB[1], t.nB[2], t.nC[0], t.nC[1]);
+        s.s2 = make_float4(t.nC[2], t.tA[0], t.tA[1], t.tB[0]);
+        float matbits;
+        std::memcpy(&matbits, &t.material, 4);
+        s.s3 = make_float4(t.tB[1], t.tC[0], t.tC[1], matbits);
+        if (t.material < 0 || t.material >= sc.n_materials) { return fail(h, MRT_ERR_INVALID, "triangle material index out of range"); }
+    }
+    std::vector<LightRec> lights(static_cast<size_t>(nl > 0 ? nl : 1));
+    for (int64_t i = 0; i < nl; ++i) {
+        const mrt_light &l = sc.lights[i];
+        LightRec &r = lights[static_cast<size_t>(i)];
+        std::memset(&r, 0, sizeof(r));
+        r.kind = l.kind;
+        for (int k = 0; k < 3; ++k) { r.Le[k] = l.Le[k]; }
+        if (l.kind == MRT_LIGHT_AREA) {
+            for (int k = 0; k < 3; ++k) { r.A[k] = l.triangle.A[k]; r.AB[k] = l.triangle.AB[k]; r.AC[k] = l.triangle.AC[k]; }
+        } else {
+            for (int k = 0; k < 3; ++k) { r.A[k] = l.position[k]; }
+        }
+        if (n_area > 0) {
+            float *o = &tris9[static_cast<size_t>(nt + i) * 9];
+            for (int k = 0; k < 3; ++k) { o[k] = r.A[k]; o[3 + k] = l.kind == MRT_LIGHT_AREA ? r.AB[k] : 0.0f; o[6 + k] = l.kind == MRT_LIGHT_AREA ? r.AC[k] : 0.0f; }
+        }
+    }
+    std::vector<MaterialRec> mats(static_cast<size_t>(sc.n_materials > 0 ? sc.n_materials : 1));
+    for (int64_t i = 0; i < sc.n_materials; ++i) {
+        MaterialRec &m = mats[static_cast<size_t>(i)];
+        std::memset(&m, 0, sizeof(m));
+        for (int k = 0; k < 3; ++k) { m.Le[k] = sc.materials[i].Le[k]; m.Kd[k] = sc.materials[i].Kd[k]; m.Ks[k] = sc.materials[i].Ks[k]; m.Kt[k] = sc.materials[i].Kt[k]; }
+        m.ior = sc.materials[i].ior;
+    }
+    // planes and spheres: reference-layout BVHs built on the host
+    std::vector<HostBox> boxes;
+    std::vector<RefNode> pnodes, snodes;
+    std::vector<int> porder, sorder;
+    for (int64_t i = 0; i < sc.n_planes; ++i) { boxes.push_back(hb_plane(sc.planes[i].normal, sc.planes[i].point)); }
+    build_ref_bvh(boxes, pnodes, porder);
+    boxes.clear();
+    for (int64_t i = 0; i < sc.n_spheres; ++i) { boxes.push_back(hb_sphere(sc.spheres[i].center, sc.spheres[i].sq_radius)); }
+    build_ref_bvh(boxes, snodes, sorder);
+    std::vector<PlaneRec> planes(porder.size() ? porder.size() : 1);
+    h->plane_slot_of_id.assign(porder.size(), 0);
+    for (size_t sidx = 0; sidx < porder.size(); ++sidx) {
+        const mrt_plane &p = sc.planes[porder[sidx]];
+        planes[sidx] = PlaneRec{p.normal[0], p.normal[1], p.normal[2], p.point[0], p.point[1], p.point[2], p.material, porder[sidx]};
+        h->plane_slot_of_id[static_cast<size_t>(porder[sidx])] = static_cast<int>(sidx);
+        if (p.material < 0 || p.material >= sc.n_materials) { return fail(h, MRT_ERR_INVALID, "plane material index out of range"); }
+    }
+    std::vector<SphereRec> spheres(sorder.size() ? sorder.size() : 1);
+    h->sphere_slot_of_id.assign(sorder.size(), 0);
+    for (size_t sidx = 0; sidx < sorder.size(); ++sidx) {
+        const mrt_sphere &p = sc.spheres[sorder[sidx]];
+        spheres[sidx] = SphereRec{p.center[0], p.center[1], p.center[2], p.sq_radius, p.material, sorder[sidx], 0, 0};
+        h->sphere_slot_of_id[static_cast<size_t>(sorder[sidx])] = static_cast<int>(sidx);
+        if (p.material < 0 || p.material >= sc.n_materials) { return fail(h, MRT_ERR_INVALID, "sphere material index out of range"); }
+    }
+    cudaEvent_t e0, e1;
+    API_CUDA(h, cudaEventCreate(&e0)); API_CUDA(h, cudaEventCreate(&e1));
+    API_CUDA(h, cudaEventRecord(e0, st));
+    API_CUDA(h, h->d_tris9.upload(tris9.data(), tris9.size() * sizeof(float), st));
+    API_CUDA(h, h->d_tri_shade.upload(shade.data(), shade.size() * sizeof(TriShade), st));
+    API_CUDA(h, h->d_lights.upload(lights.data(), lights.size() * sizeof(LightRec), st));
+    API_CUDA(h, h->d_materials.upload(mats.data(), mats.size() * sizeof(MaterialRec), st));
+    API_CUDA(h, h->d_plane_nodes.upload(pnodes.data(), pnodes.size() * sizeof(RefNode), st));
+    API_CUDA(h, h->d_planes.upload(planes.data(), planes.size() * sizeof(PlaneRec), st));
+    API_CUDA(h, h->d_sphere_nodes.upload(snodes.data(), snodes.size() * sizeof(RefNode), st));
+    API_CUDA(h, h->d_spheres.upload(spheres.data(), spheres.size() * sizeof(SphereRec), st));
+    API_CUDA(h, cudaEventRecord(e1, st));
+    API_CUDA(h, cudaEventSynchronize(e1));
+    float ms = 0.0f;
+    cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    h->stats.upload_ms = ms;
+    // acceleration structure over triangles + light triangles, on the GPU
+    API_CUDA(h, build_bvh8(h->d_tris9.as<float>(), static_cast<int>(nprims), 1u, st, &h->bvh));
+    h->stats.build_ms = h->bvh.build_ms;
+    h->stats.bvh_nodes = h->bvh.n_nodes;
+    h->stats.bvh_bytes = h->bvh.bytes();
+    h->stats.scene_bytes = h->bvh.bytes() + shade.size() * sizeof(TriShade) + mats.size() * sizeof(MaterialRec) + lights.size() * sizeof(LightRec);
+    h->stats.n_primitives = nt + sc.n_spheres + sc.n_planes;
+    h->d_tris9.release();   // geometry now lives in the BVH8 leaf array
+    SceneDev &s = h->scene;
+    s.nodes = h->bvh.nodes; s.tri_geom = h->bvh.tri_geom; s.tri_shade = h->d_tri_shade.as<TriShade>();
+    s.n_triangles = static_cast<int32_t>(nt); s.n_bvh_prims = static_cast<int32_t>(nprims);
+    s.sphere_nodes = h->d_sphere_nodes.as<RefNode>(); s.spheres = h->d_spheres.as<SphereRec>(); s.n_spheres = static_cast<int32_t>(sc.n_spheres);
+    s.plane_nodes = h->d_plane_nodes.as<RefNode>(); s.planes = h->d_planes.as<PlaneRec>(); s.n_planes = static_cast<int32_t>(sc.n_planes);
+    s.materials = h->d_materials.as<MaterialRec>(); s.n_materials = static_cast<int32_t>(sc.n_materials);
+    s.lights = h->d_lights.as<LightRec>(); s.n_lights = static_cast<int32_t>(nl);
+    return MRT_OK;
+}
+
+int upload_tables(mrt_handle *h, const mrt_render_desc &rd, const mrt_sampler_tables *tb) {
+    cudaStream_t st = h->stream;
+    std::vector<float> tile, shader, sh, smt;
+    const float *p_tile = tb ? tb->tile_order : nullptr, *p_shader = tb ? tb->shader_table : nullptr;
+    const float *p_sh = tb ? tb->static_halton : nullptr, *p_smt = tb ? tb->static_mt : nullptr;
+    if (!p_tile) { make_halton_table(tile, kNumberOfTiles, rd.seed * 4u + 0u); p_tile = tile.data(); }
+    if (!p_shader) { make_halton_table(shader, kArraySize, rd.seed * 4u + 1u); p_shader = shader.data(); }
+    if (!p_sh) { make_halton_table(sh, kArraySize, rd.seed * 4u + 2u); p_sh = sh.data(); }
+    const bool need_mt = rd.pixel_sampler == MRT_SAMPLER_STATIC_MT;
+    if (need_mt && !p_smt) { make_mt_table(smt, kArraySize, rd.seed * 4u + 3u); p_smt = smt.data(); }
+    // inverse of the tile order: Renderer::renderScene maps table value -> tile roundf(value * 256) (Renderer.cpp:125)
+    std::vector<int32_t> inv(kNumberOfTiles, -1);
+    for (int k = 0; k < kNumberOfTiles; ++k) {
+        const int rb = static_cast<int>(::roundf(p_tile[k] * static_cast<float>(kNumberOfTiles)));
+        if (rb < 0 || rb >= kNumberOfTiles || inv[static_cast<size_t>(rb)] >= 0) { return fail(h, MRT_ERR_INVALID, "tile_order is not a permutation of k/256"); }
+        inv[static_cast<size_t>(rb)] = k;
+    }
+    API_CUDA(h, h->d_tile.upload(p_tile, kNumberOfTiles * sizeof(float), st));
+    API_CUDA(h, h->d_shader_table.upload(p_shader, kArraySize * sizeof(float), st));
+    API_CUDA(h, h->d_static_halton.upload(p_sh, kArraySize * sizeof(float), st));
+    if (need_mt) { API_CUDA(h, h->d_static_mt.upload(p_smt, kArraySize * sizeof(float), st)); }
+    API_CUDA(h, h->d_inv_tile.upload(inv.data(), inv.size() * sizeof(int32_t), st));
+    API_CUDA(h, cudaStreamSynchronize(st));
+    SceneDev &s = h->scene;
+    s.tile_order = h->d_tile.as<float>(); s.shader_table = h->d_shader_table.as<float>(); s.static_halton = h->d_static_halton.as<float>();
+    int ps = rd.pixel_sampler;
+    if (ps == MRT_SAMPLER_AUTO) { ps = rd.samples_pixel > 1 ? MRT_SAMPLER_STATIC_HALTON : MRT_SAMPLER_CONSTANT; }  // C_wrapper.cpp:144-148
+    h->rp.pixel_sampler = ps;
+    s.pixel_table = ps == MRT_SAMPLER_STATIC_HALTON ? s.static_halton : (ps == MRT_SAMPLER_STATIC_MT ? h->d_static_mt.as<float>() : nullptr);
+    return MRT_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int mrt_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); n = 0; }
+    errno = 0;
+    return n;
+}
+const char *mrt_version(void) { return "mobilert_b200 0.1 (sm_100a)"; }
+
+const char *mrt_last_error(mrt_handle *h) { return h ? h->error.c_str() : g_create_error.c_str(); }
+
+void mrt_destroy(mrt_handle *h) {
+    if (!h) { return; }
+    cudaSetDevice(h->device);
+    if (h->stream) { cudaStreamSynchronize(h->stream); }
+    if (h->wavefront) { wavefront_destroy(h->wavefront); }
+    free_bvh8(&h->bvh);
+    for (cudaEvent_t e : h->sample_events) { cudaEventDestroy(e); }
+    if (h->ev0) { cudaEventDestroy(h->ev0); }
+    if (h->ev1) { cudaEventDestroy(h->ev1); }
+    if (h->h_pinned_bitmap) { cudaFreeHost(h->h_pinned_bitmap); }
+    cudaStream_t st = h->stream;
+    delete h;   // DevMem destructors free the device arrays
+    if (st) { cudaStreamDestroy(st); }
+    errno = 0;
+}
+
+int mrt_create(const mrt_scene_desc *scene, const mrt_camera_desc *camera, const mrt_render_desc *render,
+               const mrt_sampler_tables *tables, mrt_handle **out) {
+    if (!scene || !camera || !render || !out) { return fail(nullptr, MRT_ERR_INVALID, "null argument"); }
+    *out = nullptr;
+    if (render->width <= 0 || render->height <= 0 || render->samples_pixel < 0 || render->samples_light < 0) { return fail(nullptr, MRT_ERR_INVALID, "bad render size / sample counts"); }
+    if (render->shader < 0 || render->shader > 4) { return fail(nullptr, MRT_ERR_INVALID, "unknown shader"); }
+    if (render->accelerator != MRT_ACC_B200 && render->accelerator != MRT_ACC_BVH) { return fail(nullptr, MRT_ERR_INVALID, "this library only provides the BVH accelerator (MRT_ACC_B200 / MRT_ACC_BVH)"); }
+    if (scene->n_triangles < 0 || scene->n_spheres < 0 || scene->n_planes < 0 || scene->n_materials < 0 || scene->n_lights < 0) { return fail(nullptr, MRT_ERR_INVALID, "negative count"); }
+    if ((scene->n_triangles && !scene->triangles) || (scene->n_spheres && !scene->spheres) || (scene->n_planes && !scene->planes) ||
+        (scene->n_materials && !scene->materials) || (scene->n_lights && !scene->lights)) { return fail(nullptr, MRT_ERR_INVALID, "null array with non-zero count"); }
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(nullptr, MRT_ERR_CUDA, "no CUDA device: this library has no CPU fallback"); }
+    mrt_handle *h = new (std::nothrow) mrt_handle;
+    if (!h) { return fail(nullptr, MRT_ERR_OOM, "host allocation failed"); }
+    int rc = MRT_OK;
+    do {
+        if (render->device >= 0) { h->device = render->device; } else { cudaGetDevice(&h->device); }
+        cudaError_t e = cudaSetDevice(h->device);
+        if (e == cudaSuccess) { e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking); }
+        if (e == cudaSuccess) { e = cudaEventCreate(&h->ev0); }
+        if (e == cudaSuccess) { e = cudaEventCreate(&h->ev1); }
+        if (e != cudaSuccess) { rc = cuda_fail(h, e, "device setup"); break; }
+        h->flags = render->flags;
+        h->rp.width = render->width; h->rp.height = render->height; h->rp.spp = render->samples_pixel; h->rp.spl = render->samples_light;
+        h->rp.shader = render->shader; h->rp.seed = render->seed;
+        h->rp.bsx = render->width / 16; h->rp.bsy = render->height / 16;   // Renderer.cpp:33-34
+        h->rp.depth_max_point = mk3(render->depth_max_point[0], render->depth_max_point[1], render->depth_max_point[2]);
+        h->camera = make_camera(*camera);
+        if ((rc = upload_scene(h, *scene)) != MRT_OK) { break; }
+        if ((rc = upload_tables(h, *render, tables)) != MRT_OK) { break; }
+        const size_t npix = static_cast<size_t>(render->width) * render->height;
+        if ((e = h->d_bitmap.alloc(npix * sizeof(int32_t))) != cudaSuccess) { rc = cuda_fail(h, e, "bitmap"); break; }
+        if ((e = h->d_accum.alloc(npix * sizeof(float4))) != cudaSuccess) { rc = cuda_fail(h, e, "accumulator"); break; }
+        if ((e = h->d_counters.alloc(sizeof(DeviceCounters))) != cudaSuccess) { rc = cuda_fail(h, e, "counters"); break; }
+        if ((e = cudaMemsetAsync(h->d_bitmap.p, 0, npix * sizeof(int32_t), h->stream)) != cudaSuccess) { rc = cuda_fail(h, e, "memset"); break; }
+        if ((e = cudaMallocHost(reinterpret_cast<void **>(&h->h_pinned_bitmap), npix * sizeof(int32_t))) != cudaSuccess) { rc = cuda_fail(h, e, "pinned bitmap"); break; }
+        h->pinned_bytes = npix * sizeof(int32_t);
+        if (render->shader == MRT_SHADER_PATHTRACER) {
+            if ((e = wavefront_create(render->width, render->height, &h->wavefront)) != cudaSuccess) { rc = cuda_fail(h, e, "wavefront queues"); break; }
+        }
+        if ((e = cudaStreamSynchronize(h->stream)) != cudaSuccess) { rc = cuda_fail(h, e, "create sync"); break; }
+    } while (false);
+    if (rc != MRT_OK) { g_create_error = h->error; mrt_destroy(h); errno = 0; return rc; }
+    *out = h;
+    errno = 0;
+    return MRT_OK;
+}
+
+int mrt_set_camera(mrt_handle *h, const mrt_camera_desc *camera) {
+    if (!h || !camera) { return fail(h, MRT_ERR_INVALID, "null argument"); }
+    std::lock_guard<std::mutex> lock(h->mutex);
+    h->camera = make_camera(*camera);
+    errno = 0;
+    return MRT_OK;
+}
+
+int mrt_stop(mrt_handle *h) { if (!h) { return MRT_ERR_INVALID; } h->stop.store(1); errno = 0; return MRT_OK; }
+int mrt_get_sample(mrt_handle *h, int32_t *sample) { if (!h || !sample) { return MRT_ERR_INVALID; } *sample = h->sample.load(); errno = 0; return MRT_OK; }
+int mrt_get_total_rays(mrt_handle *h, uint64_t *rays) { if (!h || !rays) { return MRT_ERR_INVALID; } *rays = h->total_rays.load(); errno = 0; return MRT_OK; }
+int mrt_get_stats(mrt_handle *h, mrt_stats *stats) {
+    if (!h || !stats) { return MRT_ERR_INVALID; }
+    std::lock_guard<std::mutex> lock(h->mutex);
+    *stats = h->stats;
+    errno = 0;
+    return MRT_OK;
+}
+
+}  // extern "C"
+
+namespace {
+
+// Frame driver shared by the three render entry points. Exactly one of bitmap / accum is the target:
+//   bitmap: the reference's in-place integer running average, samples applied in order (Renderer.cpp:117-157)
+//   accum : fp32 sums of the selected samples (multi-GPU partitions), resolved later
+int render_samples(mrt_handle *h, int32_t *d_bitmap, float4 *d_accum, int sample_begin, int sample_stride) {
+    cudaStream_t st = h->stream;
+    API_CUDA(h, cudaSetDevice(h->device));
+    h->stop.store(0);
+    h->sample.store(0);
+    API_CUDA(h, cudaMemsetAsync(h->d_counters.p, 0, sizeof(DeviceCounters), st));
+    API_CUDA(h, cudaEventRecord(h->ev0, st));
+    FrameTargets tg {d_bitmap, d_accum};
+    WavefrontTimes wt {};
+    uint64_t launches = 0;
+    const int spp = h->rp.spp;
+    bool stopped = false;
+    if (h->rp.shader == MRT_SHADER_PATHTRACER) {
+        for (int s = sample_begin, k = 0; s < spp; s += sample_stride, ++k) {
+            if (h->stop.load()) { stopped = true; break; }
+            API_CUDA(h, wavefront_render_sample(h->wavefront, h->scene, h->camera, h->rp, h->d_inv_tile.as<int32_t>(), s, d_bitmap ? s + 1 : k + 1,
+                                                tg, h->d_counters.as<DeviceCounters>(), (h->flags & MRT_FLAG_SORT_BY_MATERIAL) != 0, &wt, &launches, st));
+            h->sample.store(s + 1);
+        }
+    } else {
+        const size_t depth = 4;   // samples in flight, so that mrt_stop() takes effect within a few samples
+        int k = 0;
+        for (int s = sample_begin; s < spp; s += sample_stride, ++k) {
+            if (static_cast<size_t>(k) >= depth) {
+                API_CUDA(h, cudaEventSynchronize(h->sample_events[static_cast<size_t>(k) % depth]));
+                h->sample.store(s - static_cast<int>(depth - 1) * sample_stride);
+            }
+            if (h->stop.load()) { stopped = true; break; }
+            API_CUDA(h, launch_render_sample(h->scene, h->camera, h->rp, h->d_inv_tile.as<int32_t>(), s, d_bitmap ? s + 1 : k + 1, tg,
+                                             h->d_counters.as<DeviceCounters>(), st));
+            ++launches;
+            while (h->sample_events.size() < depth) { cudaEvent_t e; API_CUDA(h, cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); h->sample_events.push_back(e); }
+            API_CUDA(h, cudaEventRecord(h->sample_events[static_cast<size_t>(k) % depth], st));
+        }
+    }
+    API_CUDA(h, cudaEventRecord(h->ev1, st));
+    DeviceCounters hc {};
+    API_CUDA(h, cudaMemcpyAsync(&hc, h->d_counters.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
+    API_CUDA(h, cudaStreamSynchronize(st));
+    float ms = 0.0f;
+    cudaEventElapsedTime(&ms, h->ev0, h->ev1);
+    if (h->wavefront) { API_CUDA(h, wavefront_collect_times(h->wavefront, &wt)); }
+    {
+        std::lock_guard<std::mutex> lock(h->mutex);
+        h->stats.frame_ms = ms;
+        h->stats.extend_ms = wt.extend_ms; h->stats.shadow_ms = wt.shadow_ms; h->stats.shade_ms = wt.shade_ms; h->stats.other_ms = wt.other_ms;
+        h->stats.rays_primary = hc.rays_primary; h->stats.rays_shadow = hc.rays_shadow; h->stats.rays_secondary = hc.rays_secondary;
+        h->stats.launches = launches;
+    }
+    h->total_rays.store(hc.rays_primary + hc.rays_shadow + hc.rays_secondary);
+    if (!stopped) { h->sample.store(spp); }
+    if (hc.overflow) { return fail(h, MRT_ERR_OVERFLOW, "traversal stack or ray queue overflow"); }
+    if (stopped) { return fail(h, MRT_ERR_STOPPED, "stopped"); }
+    errno = 0;
+    return MRT_OK;
+}
+
+int render_to_device_bitmap(mrt_handle *h, int32_t *d_bitmap) {
+    if (h->flags & MRT_FLAG_FP32_ACCUMULATE) {
+        const size_t npix = static_cast<size_t>(h->rp.width) * h->rp.height;
+        API_CUDA(h, cudaMemsetAsync(h->d_accum.p, 0, npix * sizeof(float4), h->stream));
+        const int rc = render_samples(h, nullptr, h->d_accum.as<float4>(), 0, 1);
+        if (rc != MRT_OK && rc != MRT_ERR_STOPPED) { return rc; }
+        API_CUDA(h, launch_resolve(h->d_accum.as<float4>(), d_bitmap, static_cast<int>(npix), h->stream));
+        API_CUDA(h, cudaStreamSynchronize(h->stream));
+        return rc;
+    }
+    return render_samples(h, d_bitmap, nullptr, 0, 1);
+}
+
+}  // namespace
+
+extern "C" {
+
+int mrt_render_frame_device(mrt_handle *h, void *device_bitmap) {
+    if (!h || !device_bitmap) { return fail(h, MRT_ERR_INVALID, "null argument"); }
+    return render_to_device_bitmap(h, static_cast<int32_t *>(device_bitmap));
+}
+
+int mrt_render_frame(mrt_handle *h, int32_t *host_bitmap) {
+    if (!h || !host_bitmap) { return fail(h, MRT_ERR_INVALID, "null argument"); }
+    const int rc = render_to_device_bitmap(h, h->d_bitmap.as<int32_t>());
+    if (rc != MRT_OK && rc != MRT_ERR_STOPPED) { return rc; }
+    // only the 16x16 tile grid is ever written (Renderer.cpp:33-34,125-135); remainder pixels keep the caller's content
+    const size_t w = static_cast<size_t>(h->rp.width), rw = static_cast<size_t>(h->rp.bsx) * 16, rh = static_cast<size_t>(h->rp.bsy) * 16;
+    if (rw > 0 && rh > 0) {
+        API_CUDA(h, cudaMemcpy2DAsync(h->h_pinned_bitmap, w * 4, h->d_bitmap.p, w * 4, rw * 4, rh, cudaMemcpyDeviceToHost, h->stream));
+        API_CUDA(h, cudaStreamSynchronize(h->stream));
+        for (size_t y = 0; y < rh; ++y) { std::memcpy(host_bitmap + y * w, h->h_pinned_bitmap + y * w, rw * 4); }
+    }
+    errno = 0;
+    return rc;
+}
+
+int mrt_render_accumulate_device(mrt_handle *h, void *device_accum, int32_t sample_begin, int32_t sample_stride) {
+    if (!h || !device_accum || sample_begin < 0 || sample_stride <= 0) { return fail(h, MRT_ERR_INVALID, "bad argument"); }
+    return render_samples(h, nullptr, static_cast<float4 *>(device_accum), sample_begin, sample_stride);
+}
+
+int mrt_resolve_device(mrt_handle *h, const void *device_accum, void *device_bitmap) {
+    if (!h || !device_accum || !device_bitmap) { return fail(h, MRT_ERR_INVALID, "null argument"); }
+    API_CUDA(h, cudaSetDevice(h->device));
+    API_CUDA(h, launch_resolve(static_cast<const float4 *>(device_accum), static_cast<int32_t *>(device_bitmap), h->rp.width * h->rp.height, h->stream));
+    API_CUDA(h, cudaStreamSynchronize(h->stream));
+    errno = 0;
+    return MRT_OK;
+}
+
+}  // extern "C"
+
+// ---- per-ray and primitive-level entry points (parity tests) -----------------------------------------------------
+namespace {
+struct TmpDev {
+    std::vector<void *> ptrs;
+    ~TmpDev() { for (void *p : ptrs) { cudaFree(p); } }
+    template <typename T> cudaError_t get(T **out, size_t count) {
+        void *p = nullptr;
+        cudaError_t e = cudaMalloc(&p, (count ? count : 1) * sizeof(T));
+        if (e == cudaSuccess) { ptrs.push_back(p); *out = static_cast<T *>(p); }
+        return e;
+    }
+    template <typename T> cudaError_t put(T **out, const T *src, size_t count, cudaStream_t st) {
+        cudaError_t e = get(out, count);
+        if (e == cudaSuccess && count) { e = cudaMemcpyAsync(*out, src, count * sizeof(T), cudaMemcpyHostToDevice, st); }
+        return e;
+    }
+};
+#define TEST_CUDA(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { return cuda_fail(nullptr, e_, #x); } } while (0)
+}  // namespace
+
+extern "C" {
+
+int mrt_trace_rays(mrt_handle *h, int64_t n, const float *origins, const float *directions, const int32_t *origin_kind,
+                   const int32_t *origin_idx, const float *shadow_dist, float *out_t, int32_t *out_kind, int32_t *out_idx,
+                   int32_t *out_material, float *out_normal) {
+    if (!h || n < 0 || !origins || !directions || !out_t || !out_kind || !out_idx || !out_material) { return fail(h, MRT_ERR_INVALID, "bad argument"); }
+    API_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t st = h->stream;
+    TmpDev tmp;
+    const size_t N = static_cast<size_t>(n);
+    float *d_o, *d_d, *d_sd = nullptr, *d_t, *d_n = nullptr;
+    int32_t *d_ok = nullptr, *d_oi = nullptr, *d_kind, *d_idx, *d_mat;
+    API_CUDA(h, tmp.put(&d_o, origins, 3 * N, st));
+    API_CUDA(h, tmp.put(&d_d, directions, 3 * N, st));
+    std::vector<int32_t> slots;
+    if (origin_kind && origin_idx) {
+        // caller indices -> device slots for planes (spheres never self-skip)
+        slots.assign(origin_idx, origin_idx + N);
+        for (size_t i = 0; i < N; ++i) {
+            if (origin_kind[i] == HIT_PLANE && slots[i] >= 0 && static_cast<size_t>(slots[i]) < h->plane_slot_of_id.size()) { slots[i] = h->plane_slot_of_id[static_cast<size_t>(slots[i])]; }
+        }
+        API_CUDA(h, tmp.put(&d_ok, origin_kind, N, st));
+        API_CUDA(h, tmp.put(&d_oi, slots.data(), N, st));
+    }
+    if (shadow_dist) { API_CUDA(h, tmp.put(&d_sd, shadow_dist, N, st)); }
+    API_CUDA(h, tmp.get(&d_t, N)); API_CUDA(h, tmp.get(&d_kind, N)); API_CUDA(h, tmp.get(&d_idx, N)); API_CUDA(h, tmp.get(&d_mat, N));
+    if (out_normal) { API_CUDA(h, tmp.get(&d_n, 3 * N)); API_CUDA(h, cudaMemsetAsync(d_n, 0, 3 * N * sizeof(float), st)); }
+    API_CUDA(h, cudaMemsetAsync(h->d_counters.p, 0, sizeof(DeviceCounters), st));
+    API_CUDA(h, launch_trace_rays(h->scene, n, d_o, d_d, d_ok, d_oi, d_sd, d_t, d_kind, d_idx, d_mat, d_n, h->d_counters.as<DeviceCounters>(), st));
+    DeviceCounters hc {};
+    API_CUDA(h, cudaMemcpyAsync(out_t, d_t, N * 4, cudaMemcpyDeviceToHost, st));
+    API_CUDA(h, cudaMemcpyAsync(out_kind, d_kind, N * 4, cudaMemcpyDeviceToHost, st));
+    API_CUDA(h, cudaMemcpyAsync(out_idx, d_idx, N * 4, cudaMemcpyDeviceToHost, st));
+    API_CUDA(h, cudaMemcpyAsync(out_material, d_mat, N * 4, cudaMemcpyDeviceToHost, st));
+    if (out_normal) { API_CUDA(h, cudaMemcpyAsync(out_normal, d_n, 3 * N * 4, cudaMemcpyDeviceToHost, st)); }
+    API_CUDA(h, cudaMemcpyAsync(&hc, h->d_counters.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
+    API_CUDA(h, cudaStreamSynchronize(st));
+    if (hc.overflow) { return fail(h, MRT_ERR_OVERFLOW, "traversal stack overflow"); }
+    errno = 0;
+    return MRT_OK;
+}
+
+int mrt_generate_rays(mrt_handle *h, int64_t n, const float *uvdd, float *out_origins, float *out_directions) {
+    if (!h || n < 0 || !uvdd || !out_origins || !out_directions) { return fail(h, MRT_ERR_INVALID, "bad argument"); }
+    API_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t st = h->stream;
+    TmpDev tmp;
+    const size_t N = static_cast<size_t>(n);
+    float *d_in, *d_o, *d_d;
+    API_CUDA(h, tmp.put(&d_in, uvdd, 4 * N, st));
+    API_CUDA(h, tmp.get(&d_o, 3 * N)); API_CUDA(h, tmp.get(&d_d, 3 * N));
+    API_CUDA(h, launch_generate_rays(h->camera, n, d_in, d_o, d_d, st));
+    API_CUDA(h, cudaMemcpyAsync(out_origins, d_o, 3 * N * 4, cudaMemcpyDeviceToHost, st));
+    API_CUDA(h, cudaMemcpyAsync(out_directions, d_d, 3 * N * 4, cudaMemcpyDeviceToHost, st));
+    API_CUDA(h, cudaStreamSynchronize(st));
+    errno = 0;
+    return MRT_OK;
+}
+
+int mrt_shade_rays(mrt_handle *h, int64_t n, const float *origins, const float *directions, int32_t depth, float *out_rgb) {
+    if (!h || n < 0 || !origins || !directions || !out_rgb) { return fail(h, MRT_ERR_INVALID, "bad argument"); }
+    if (h->rp.shader == MRT_SHADER_PATHTRACER) { return fail(h, MRT_ERR_INVALID, "mrt_shade_rays serves the deterministic shaders only"); }
+    API_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t st = h->stream;
+    TmpDev tmp;
+    const size_t N = static_cast<size_t>(n);
+    float *d_o, *d_d, *d_rgb;
+    API_CUDA(h, tmp.put(&d_o, origins, 3 * N, st));
+    API_CUDA(h, tmp.put(&d_d, directions, 3 * N, st));
+    API_CUDA(h, tmp.get(&d_rgb, 3 * N));
+    API_CUDA(h, cudaMemsetAsync(h->d_counters.p, 0, sizeof(DeviceCounters), st));
+    API_CUDA(h, launch_shade_rays(h->scene, h->rp, n, d_o, d_d, depth, d_rgb, h->d_counters.as<DeviceCounters>(), st));
+    API_CUDA(h, cudaMemcpyAsync(out_rgb, d_rgb, 3 * N * 4, cudaMemcpyDeviceToHost, st));
+    API_CUDA(h, cudaStreamSynchronize(st));
+    errno = 0;
+    return MRT_OK;
+}
+
+int mrt_test_triangle_intersect(const mrt_triangle *tri, const float *o, const float *d, float t_max, int32_t self_skip,
+                                float *out_t, float *out8) {
+    if (!tri || !o || !d || !out_t) { return fail(nullptr, MRT_ERR_INVALID, "null argument"); }
+    TmpDev tmp;
+    float *d_tri, *d_o, *d_d, *d_out;
+    TEST_CUDA(tmp.put(&d_tri, reinterpret_cast<const float *>(tri), 25, nullptr));
+    TEST_CUDA(tmp.put(&d_o, o, 3, nullptr)); TEST_CUDA(tmp.put(&d_d, d, 3, nullptr)); TEST_CUDA(tmp.get(&d_out, 9));
+    TEST_CUDA(launch_test_triangle(d_tri, d_o, d_d, t_max, self_skip, d_out, nullptr));
+    float out[9];
+    TEST_CUDA(cudaMemcpy(out, d_out, sizeof(out), cudaMemcpyDeviceToHost));
+    *out_t = out[0];
+    if (out8) { std::memcpy(out8, out + 1, 8 * sizeof(float)); }
+    errno = 0;
+    return MRT_OK;
+}
+int mrt_test_sphere_intersect(const mrt_sphere *s, const float *o, const float *d, float t_max, float *out_t, float *out_normal) {
+    if (!s || !o || !d || !out_t) { return fail(nullptr, MRT_ERR_INVALID, "null argument"); }
+    TmpDev tmp;
+    float *d_s, *d_o, *d_d, *d_out;
+    const float s4[4] = {s->center[0], s->center[1], s->center[2], s->sq_radius};
+    TEST_CUDA(tmp.put(&d_s, s4, 4, nullptr)); TEST_CUDA(tmp.put(&d_o, o, 3, nullptr)); TEST_CUDA(tmp.put(&d_d, d, 3, nullptr)); TEST_CUDA(tmp.get(&d_out, 4));
+    TEST_CUDA(launch_test_sphere(d_s, d_o, d_d, t_max, d_out, nullptr));
+    float out[4];
+    TEST_CUDA(cudaMemcpy(out, d_out, sizeof(out), cudaMemcpyDeviceToHost));
+    *out_t = out[0];
+    if (out_normal) { std::memcpy(out_normal, out + 1, 3 * sizeof(float)); }
+    errno = 0;
+    return MRT_OK;
+}
+int mrt_test_plane_intersect(const mrt_plane *p, const float *o, const float *d, float t_max, float *out_t) {
+    if (!p || !o || !d || !out_t) { return fail(nullptr, MRT_ERR_INVALID, "null argument"); }
+    TmpDev tmp;
+    float *d_p, *d_o, *d_d, *d_out;
+    const float p6[6] = {p->normal[0], p->normal[1], p->normal[2], p->point[0], p->point[1], p->point[2]};
+    TEST_CUDA(tmp.put(&d_p, p6, 6, nullptr)); TEST_CUDA(tmp.put(&d_o, o, 3, nullptr)); TEST_CUDA(tmp.put(&d_d, d, 3, nullptr)); TEST_CUDA(tmp.get(&d_out, 1));
+    TEST_CUDA(launch_test_plane(d_p, d_o, d_d, t_max, d_out, nullptr));
+    TEST_CUDA(cudaMemcpy(out_t, d_out, sizeof(float), cudaMemcpyDeviceToHost));
+    errno = 0;
+    return MRT_OK;
+}
+int mrt_test_aabb_intersect(const float *box_min, const float *box_max, const float *o, const float *d, int32_t *out_hit) {
+    if (!box_min || !box_max || !o || !d || !out_hit) { return fail(nullptr, MRT_ERR_INVALID, "null argument"); }
+    TmpDev tmp;
+    float *d_b, *d_o, *d_d; int32_t *d_out;
+    const float b6[6] = {box_min[0], box_min[1], box_min[2], box_max[0], box_max[1], box_max[2]};
+    TEST_CUDA(tmp.put(&d_b, b6, 6, nullptr)); TEST_CUDA(tmp.put(&d_o, o, 3, nullptr)); TEST_CUDA(tmp.put(&d_d, d, 3, nullptr)); TEST_CUDA(tmp.get(&d_out, 1));
+    TEST_CUDA(launch_test_aabb(d_b, d_o, d_d, d_out, nullptr));
+    TEST_CUDA(cudaMemcpy(out_hit, d_out, sizeof(int32_t), cudaMemcpyDeviceToHost));
+    errno = 0;
+    return MRT_OK;
+}
+int mrt_test_incremental_avg(const float *rgb, int32_t avg, int32_t num_sample, int32_t *out) {
+    if (!rgb || !out || num_sample <= 0) { return fail(nullptr, MRT_ERR_INVALID, "bad argument"); }
+    TmpDev tmp;
+    float *d_rgb; int32_t *d_out;
+    TEST_CUDA(tmp.put(&d_rgb, rgb, 3, nullptr)); TEST_CUDA(tmp.get(&d_out, 1));
+    TEST_CUDA(launch_test_incavg(d_rgb, avg, num_sample, d_out, nullptr));
+    TEST_CUDA(cudaMemcpy(out, d_out, sizeof(int32_t), cudaMemcpyDeviceToHost));
+    errno = 0;
+    return MRT_OK;
+}
+int mrt_test_halton(uint32_t first, int64_t n, uint32_t base, float *out) {
+    if (!out || n < 0 || base < 2) { return fail(nullptr, MRT_ERR_INVALID, "bad argument"); }
+    TmpDev tmp;
+    float *d_out;
+    TEST_CUDA(tmp.get(&d_out, static_cast<size_t>(n)));
+    TEST_CUDA(launch_test_halton(first, n, base, d_out, nullptr));
+    TEST_CUDA(cudaMemcpy(out, d_out, static_cast<size_t>(n) * sizeof(float), cudaMemcpyDeviceToHost));
+    errno = 0;
+    return MRT_OK;
+}
+
+}  // extern "C"

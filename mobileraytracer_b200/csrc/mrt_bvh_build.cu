@@ -1,0 +1,499 @@
+// GPU builder for the compressed 8-wide BVH (replaces BVH<T>::build, MobileRT/Accelerators/BVH.hpp:160-283,
+// getSplitIndexSah :396-439). The topology does not have to match the reference's binary tree; only hit
+// results must. Chain of kernels, all on one stream, no host-side geometry work:
+//   k_prim_bounds -> k_morton -> radix sort (hist/scan/scatter x 8) -> k_hierarchy (Karras 2012) -> k_refit
+//   -> [k_top_* : binned-SAH rebuild of the upper tree over LBVH clusters] -> k_collapse8 (level-synchronous)
+#include "mrt_build.h"
+#include <cstdio>
+#include <vector>
+
+namespace mrt {
+
+#define CUDA_TRY(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { return e_; } } while (0)
+
+// order-preserving float <-> int mapping so that atomicMin/atomicMax on ints order floats
+__device__ __forceinline__ int f2ord(float f) { int i = __float_as_int(f); return i ^ ((i >> 31) & 0x7fffffff); }
+__device__ __forceinline__ float ord2f(int i) { return __int_as_float(i ^ ((i >> 31) & 0x7fffffff)); }
+
+// ---------------------------------------------------------------------------------------------------------
+// 1. primitive boxes (Triangle::getAABB, Triangle.cpp:116-123) and centroid bounds
+// ---------------------------------------------------------------------------------------------------------
+__global__ void k_prim_bounds(const float *__restrict__ tris9, int n, float *__restrict__ plo, float *__restrict__ phi,
+                              int *__restrict__ cbounds /* 6 ordered ints: min xyz, max xyz */) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    float c[3] = {0, 0, 0};
+    const bool valid = i < n;
+    if (valid) {
+        const float *t = tris9 + 9ll * i;
+        for (int k = 0; k < 3; ++k) {
+            const float a = t[k], b = a + t[3 + k], cc = a + t[6 + k];
+            const float lo = fminf(a, fminf(b, cc)), hi = fmaxf(a, fmaxf(b, cc));
+            plo[3ll * i + k] = lo; phi[3ll * i + k] = hi;
+            c[k] = 0.5f * lo + 0.5f * hi;
+        }
+    }
+    // warp reduce then one atomic per warp
+    for (int k = 0; k < 3; ++k) {
+        float mn = valid ? c[k] : 3.0e38f, mx = valid ? c[k] : -3.0e38f;
+        for (int o = 16; o > 0; o >>= 1) {
+            mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+            mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        }
+        if ((threadIdx.x & 31) == 0) { atomicMin(&cbounds[k], f2ord(mn)); atomicMax(&cbounds[3 + k], f2ord(mx)); }
+    }
+}
+
+__device__ __forceinline__ unsigned long long expand21(unsigned long long v) {
+    v &= 0x1fffffull;
+    v = (v | v << 32) & 0x1f00000000ffffull;
+    v = (v | v << 16) & 0x1f0000ff0000ffull;
+    v = (v | v << 8) & 0x100f00f00f00f00full;
+    v = (v | v << 4) & 0x10c30c30c30c30c3ull;
+    v = (v | v << 2) & 0x1249249249249249ull;
+    return v;
+}
+
+// 2. 63-bit Morton codes of the box centroids
+__global__ void k_morton(const float *__restrict__ plo, const float *__restrict__ phi, int n, const int *__restrict__ cbounds,
+                         unsigned long long *__restrict__ keys, uint32_t *__restrict__ vals) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) { return; }
+    unsigned long long code = 0;
+    for (int k = 0; k < 3; ++k) {
+        const float mn = ord2f(cbounds[k]), mx = ord2f(cbounds[3 + k]);
+        const float c = 0.5f * plo[3ll * i + k] + 0.5f * phi[3ll * i + k];
+        const float ext = mx - mn;
+        float f = ext > 0.0f ? (c - mn) / ext : 0.0f;
+        f = fminf(fmaxf(f, 0.0f), 1.0f);
+        const unsigned long long q = static_cast<unsigned long long>(fminf(f * 2097152.0f, 2097151.0f));
+        code |= expand21(q) << (2 - k);
+    }
+    keys[i] = code;
+    vals[i] = static_cast<uint32_t>(i);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// 3. LSD radix sort of (u64 key, u32 value), 8 bits per pass, stable. Block = 256 threads = 8 warps, each warp
+//    owns a contiguous segment of the block's tile so that ranks can be produced with warp match + popc.
+// ---------------------------------------------------------------------------------------------------------
+constexpr int RS_THREADS = 256;
+constexpr int RS_WARPS = RS_THREADS / 32;
+constexpr int RS_SEG = 512;                  // keys per warp
+constexpr int RS_TILE = RS_WARPS * RS_SEG;   // keys per block
+
+__global__ void __launch_bounds__(RS_THREADS) k_rs_hist(const unsigned long long *__restrict__ keys, int n, int shift,
+                                                        uint32_t *__restrict__ hist, int nblocks) {
+    __shared__ uint32_t sh[256];
+    sh[threadIdx.x] = 0;
+    __syncthreads();
+    const long long base = static_cast<long long>(blockIdx.x) * RS_TILE;
+    for (int j = threadIdx.x; j < RS_TILE; j += RS_THREADS) {
+        const long long i = base + j;
+        if (i < n) { atomicAdd(&sh[(keys[i] >> shift) & 0xff], 1u); }
+    }
+    __syncthreads();
+    hist[static_cast<long long>(threadIdx.x) * nblocks + blockIdx.x] = sh[threadIdx.x];
+}
+
+// exclusive scan over the digit-major histogram (256 * nblocks entries) by one block
+__global__ void __launch_bounds__(1024) k_rs_scan(uint32_t *__restrict__ hist, long long total) {
+    __shared__ uint32_t warpsum[32];
+    __shared__ uint32_t carry;
+    if (threadIdx.x == 0) { carry = 0; }
+    __syncthreads();
+    for (long long base = 0; base < total; base += 1024) {
+        const long long i = base + threadIdx.x;
+        const uint32_t v = i < total ? hist[i] : 0u;
+        uint32_t x = v;
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, x, o); if ((threadIdx.x & 31) >= o) { x += y; } }
+        if ((threadIdx.x & 31) == 31) { warpsum[threadIdx.x >> 5] = x; }
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            uint32_t w = warpsum[threadIdx.x];
+            for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, w, o); if (threadIdx.x >= o) { w += y; } }
+            warpsum[threadIdx.x] = w;
+        }
+        __syncthreads();
+        const uint32_t woff = (threadIdx.x >> 5) ? warpsum[(threadIdx.x >> 5) - 1] : 0u;
+        const uint32_t incl = x + woff + carry;
+        if (i < total) { hist[i] = incl - v; }
+        __syncthreads();
+        if (threadIdx.x == 1023) { carry = incl; }
+        __syncthreads();
+    }
+}
+
+__global__ void __launch_bounds__(RS_THREADS) k_rs_scatter(const unsigned long long *__restrict__ keys, const uint32_t *__restrict__ vals,
+                                                           unsigned long long *__restrict__ okeys, uint32_t *__restrict__ ovals,
+                                                           int n, int shift, const uint32_t *__restrict__ hist, int nblocks) {
+    __shared__ uint32_t wcnt[RS_WARPS][256];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    for (int j = threadIdx.x; j < RS_WARPS * 256; j += RS_THREADS) { (&wcnt[0][0])[j] = 0; }
+    __syncthreads();
+    const long long wbase = static_cast<long long>(blockIdx.x) * RS_TILE + static_cast<long long>(warp) * RS_SEG;
+    // phase 1: per-warp digit counts
+    for (int j = lane; j < RS_SEG; j += 32) {
+        const long long i = wbase + j;
+        if (i < n) { atomicAdd(&wcnt[warp][(keys[i] >> shift) & 0xff], 1u); }
+    }
+    __syncthreads();
+    // phase 2: per digit, exclusive scan over warps + global base of this block
+    {
+        const int d = threadIdx.x;
+        uint32_t run = hist[static_cast<long long>(d) * nblocks + blockIdx.x];
+        for (int w = 0; w < RS_WARPS; ++w) { const uint32_t c = wcnt[w][d]; wcnt[w][d] = run; run += c; }
+    }
+    __syncthreads();
+    // phase 3: stable scatter, 32 keys at a time per warp
+    for (int j0 = 0; j0 < RS_SEG; j0 += 32) {
+        const long long i = wbase + j0 + lane;
+        const bool valid = i < n;
+        const unsigned long long key = valid ? keys[i] : 0ull;
+        const uint32_t digit = valid ? static_cast<uint32_t>((key >> shift) & 0xff) : 0x100u + lane;
+        const uint32_t peers = __match_any_sync(0xffffffffu, digit);
+        if (valid) {
+            const uint32_t rank = __popc(peers & ((1u << lane) - 1u));
+            const uint32_t base = wcnt[warp][digit];
+            const uint32_t dst = base + rank;
+            okeys[dst] = key;
+            ovals[dst] = vals[i];
+            __syncwarp(peers);
+            if (rank == 0) { wcnt[warp][digit] = base + __popc(peers); }
+        }
+        __syncwarp();
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// 4. LBVH hierarchy (Karras 2012). Internal nodes 0..n-2, leaves n-1..2n-2 (leaf j = node n-1+j).
+// ---------------------------------------------------------------------------------------------------------
+struct BinTree {
+    int *left, *right, *parent;   // [2n-1] (left/right only for internal nodes)
+    int *first, *count;           // [2n-1] sorted-primitive range covered by the node
+    float *lo, *hi;               // [2n-1][3]
+    int *flags;                   // [n-1] refit arrival counters
+};
+
+__device__ __forceinline__ int lbvh_delta(const unsigned long long *keys, int n, int i, int j) {
+    if (j < 0 || j >= n) { return -1; }
+    const unsigned long long a = keys[i], b = keys[j];
+    if (a == b) { return 64 + __clz(i ^ j); }
+    return __clzll(static_cast<long long>(a ^ b));
+}
+
+__global__ void k_hierarchy(const unsigned long long *__restrict__ keys, int n, BinTree t) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) { return; }
+    const int d = (lbvh_delta(keys, n, i, i + 1) - lbvh_delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+    const int dmin = lbvh_delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (lbvh_delta(keys, n, i, i + lmax * d) > dmin) { lmax <<= 1; }
+    int l = 0;
+    for (int s = lmax >> 1; s >= 1; s >>= 1) {
+        if (lbvh_delta(keys, n, i, i + (l + s) * d) > dmin) { l += s; }
+    }
+    const int j = i + l * d;
+    const int dnode = lbvh_delta(keys, n, i, j);
+    int s = 0;
+    for (int tt = (l + 1) >> 1; ; tt = (tt + 1) >> 1) {
+        if (lbvh_delta(keys, n, i, i + (s + tt) * d) > dnode) { s += tt; }
+        if (tt == 1) { break; }
+    }
+    const int gamma = i + s * d + min(d, 0);
+    const int lo = min(i, j), hi = max(i, j);
+    const int left = (lo == gamma) ? (n - 1 + gamma) : gamma;
+    const int right = (hi == gamma + 1) ? (n - 1 + gamma + 1) : (gamma + 1);
+    t.left[i] = left; t.right[i] = right;
+    t.parent[left] = i; t.parent[right] = i;
+    t.first[i] = lo; t.count[i] = hi - lo + 1;
+    if (i == 0) { t.parent[0] = -1; }
+}
+
+// 5. bottom-up refit: second arrival at an internal node merges the children boxes
+__global__ void k_refit(const uint32_t *__restrict__ sorted, const float *__restrict__ plo, const float *__restrict__ phi, int n, BinTree t) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) { return; }
+    const int leaf = n - 1 + j;
+    const uint32_t p = sorted[j];
+    for (int k = 0; k < 3; ++k) { t.lo[3ll * leaf + k] = plo[3ll * p + k]; t.hi[3ll * leaf + k] = phi[3ll * p + k]; }
+    t.first[leaf] = j; t.count[leaf] = 1;
+    if (n == 1) { t.parent[leaf] = -1; return; }
+    int node = t.parent[leaf];
+    while (node >= 0) {
+        __threadfence();
+        if (atomicAdd(&t.flags[node], 1) == 0) { return; }
+        __threadfence();
+        const int l = t.left[node], r = t.right[node];
+        for (int k = 0; k < 3; ++k) {
+            const float a = __ldcg(&t.lo[3ll * l + k]), b = __ldcg(&t.lo[3ll * r + k]);
+            const float c = __ldcg(&t.hi[3ll * l + k]), d = __ldcg(&t.hi[3ll * r + k]);
+            t.lo[3ll * node + k] = fminf(a, b);
+            t.hi[3ll * node + k] = fmaxf(c, d);
+        }
+        node = t.parent[node];
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// 6. collapse to 8-wide + quantise + pack triangles. One thread per wide node, level by level.
+// ---------------------------------------------------------------------------------------------------------
+struct WorkItem { int bin; int wide; };
+
+struct CollapseArgs {
+    BinTree t; int n;
+    const uint32_t *sorted; const float *tris9;
+    Node8 *nodes; TriGeom *tri_geom;
+    uint32_t *node_counter, *tri_counter;
+    const WorkItem *in; int n_in; WorkItem *out; uint32_t *n_out;
+    uint32_t max_nodes;
+    int *error;
+};
+
+__device__ __forceinline__ float box_area(const float *lo, const float *hi) {
+    const float dx = hi[0] - lo[0], dy = hi[1] - lo[1], dz = hi[2] - lo[2];
+    return dx * dy + dy * dz + dz * dx;
+}
+
+__global__ void k_collapse8(CollapseArgs a) {
+    const int w = blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= a.n_in) { return; }
+    const WorkItem item = a.in[w];
+    const BinTree &t = a.t;
+    const int nint = a.n - 1;  // nodes >= nint are leaves
+    int kids[8]; int nk = 0;
+    // a binary subtree with <= 3 primitives can live in one leaf slot
+    if (item.bin >= nint || t.count[item.bin] <= 3) { kids[nk++] = item.bin; }
+    else { kids[nk++] = t.left[item.bin]; kids[nk++] = t.right[item.bin]; }
+    while (nk < 8) {
+        int best = -1; float bestA = -1.0f;
+        for (int k = 0; k < nk; ++k) {
+            const int b = kids[k];
+            if (b >= nint) { continue; }
+            const float A = box_area(&t.lo[3ll * b], &t.hi[3ll * b]);
+            // prefer opening subtrees that would need their own wide node; ties by area
+            const float key = (t.count[b] > 3 ? 1.0e30f : 0.0f) + A;
+            if (key > bestA) { bestA = key; best = k; }
+        }
+        if (best < 0) { break; }
+        const int b = kids[best];
+        kids[best] = t.left[b];
+        kids[nk++] = t.right[b];
+    }
+    // node frame
+    float plo[3], phi[3];
+    for (int k = 0; k < 3; ++k) { plo[k] = 3.0e38f; phi[k] = -3.0e38f; }
+    for (int c = 0; c < nk; ++c) for (int k = 0; k < 3; ++k) {
+        plo[k] = fminf(plo[k], t.lo[3ll * kids[c] + k]); phi[k] = fmaxf(phi[k], t.hi[3ll * kids[c] + k]);
+    }
+    int e8[3]; float scale[3];
+    for (int k = 0; k < 3; ++k) {
+        const float ext = phi[k] - plo[k];
+        int e = 1;
+        if (ext > 0.0f) {
+            int ex; frexpf(ext / 255.0f, &ex);      // ext/255 = m * 2^ex, m in [0.5,1)  =>  2^ex >= ext/255
+            e = ex + 127;
+            if (e < 1) { e = 1; }
+            while (e < 254 && __int_as_float(e << 23) * 255.0f < ext) { ++e; }
+        }
+        e8[k] = e; scale[k] = __int_as_float(e << 23);
+    }
+    // greedy slot assignment: slot s prefers children lying in direction (bit k of s set => +axis k)
+    float cen[8][3];
+    float pc[3];
+    for (int k = 0; k < 3; ++k) { pc[k] = 0.5f * plo[k] + 0.5f * phi[k]; }
+    for (int c = 0; c < nk; ++c) for (int k = 0; k < 3; ++k) {
+        cen[c][k] = (0.5f * t.lo[3ll * kids[c] + k] + 0.5f * t.hi[3ll * kids[c] + k]) - pc[k];
+    }
+    int slot_of[8]; int child_in_slot[8];
+    for (int s = 0; s < 8; ++s) { child_in_slot[s] = -1; }
+    for (int c = 0; c < nk; ++c) { slot_of[c] = -1; }
+    for (int round = 0; round < nk; ++round) {
+        float bestCost = -3.0e38f; int bc = -1, bs = -1;
+        for (int c = 0; c < nk; ++c) {
+            if (slot_of[c] >= 0) { continue; }
+            for (int s = 0; s < 8; ++s) {
+                if (child_in_slot[s] >= 0) { continue; }
+                const float cost = ((s & 1) ? cen[c][0] : -cen[c][0]) + ((s & 2) ? cen[c][1] : -cen[c][1]) + ((s & 4) ? cen[c][2] : -cen[c][2]);
+                if (cost > bestCost) { bestCost = cost; bc = c; bs = s; }
+            }
+        }
+        slot_of[bc] = bs; child_in_slot[bs] = bc;
+    }
+    // count inner children / leaf triangles
+    uint32_t imask = 0; int ninner = 0, ntris = 0;
+    for (int s = 0; s < 8; ++s) {
+        const int c = child_in_slot[s];
+        if (c < 0) { continue; }
+        const int b = kids[c];
+        if (b < nint && t.count[b] > 3) { imask |= 1u << s; ++ninner; } else { ntris += t.count[b]; }
+    }
+    const uint32_t child_base = ninner ? atomicAdd(a.node_counter, static_cast<uint32_t>(ninner)) : 0u;
+    const uint32_t tri_base = ntris ? atomicAdd(a.tri_counter, static_cast<uint32_t>(ntris)) : 0u;
+    if (ninner && child_base + ninner > a.max_nodes) { *a.error = 1; return; }
+    Node8 node;
+    node.px = plo[0]; node.py = plo[1]; node.pz = plo[2];
+    node.ex = static_cast<uint8_t>(e8[0]); node.ey = static_cast<uint8_t>(e8[1]); node.ez = static_cast<uint8_t>(e8[2]);
+    node.imask = static_cast<uint8_t>(imask);
+    node.child_base = child_base; node.tri_base = tri_base;
+    int inner_rank = 0, tri_off = 0;
+    uint32_t out_base = 0;
+    if (ninner) { out_base = atomicAdd(a.n_out, static_cast<uint32_t>(ninner)); }
+    for (int s = 0; s < 8; ++s) {
+        const int c = child_in_slot[s];
+        uint8_t q[6] = {0, 0, 0, 0, 0, 0};
+        if (c < 0) {
+            node.meta[s] = 0;
+        } else {
+            const int b = kids[c];
+            for (int k = 0; k < 3; ++k) {
+                const float clo = t.lo[3ll * b + k], chi = t.hi[3ll * b + k];
+                int ql = static_cast<int>(floorf((clo - plo[k]) / scale[k]));
+                int qh = static_cast<int>(ceilf((chi - plo[k]) / scale[k]));
+                ql = max(0, min(255, ql)); qh = max(0, min(255, qh));
+                while (ql > 0 && plo[k] + static_cast<float>(ql) * scale[k] > clo) { --ql; }
+                while (qh < 255 && plo[k] + static_cast<float>(qh) * scale[k] < chi) { ++qh; }
+                q[k] = static_cast<uint8_t>(ql); q[3 + k] = static_cast<uint8_t>(qh);
+            }
+            if (imask & (1u << s)) {
+                node.meta[s] = static_cast<uint8_t>((1u << 5) | (24u + s));
+                a.out[out_base + inner_rank] = WorkItem{b, static_cast<int>(child_base) + inner_rank};
+                ++inner_rank;
+            } else {
+                const int cnt = t.count[b];
+                node.meta[s] = static_cast<uint8_t>((((1u << cnt) - 1u) << 5) | static_cast<uint32_t>(tri_off));
+                const int first = t.first[b];
+                for (int j = 0; j < cnt; ++j) {
+                    const uint32_t prim = a.sorted[first + j];
+                    const float *tr = a.tris9 + 9ll * prim;
+                    TriGeom g;
+                    g.g0 = make_float4(tr[0], tr[1], tr[2], tr[3]);
+                    g.g1 = make_float4(tr[4], tr[5], tr[6], tr[7]);
+                    g.g2 = make_float4(tr[8], __uint_as_float(prim), 0.0f, 0.0f);
+                    a.tri_geom[tri_base + tri_off + j] = g;
+                }
+                tri_off += cnt;
+            }
+        }
+        node.qlox[s] = q[0]; node.qloy[s] = q[1]; node.qloz[s] = q[2];
+        node.qhix[s] = q[3]; node.qhiy[s] = q[4]; node.qhiz[s] = q[5];
+    }
+    a.nodes[item.wide] = node;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// host driver
+// ---------------------------------------------------------------------------------------------------------
+namespace {
+struct DevBuf {
+    void *p = nullptr;
+    ~DevBuf() { if (p) { cudaFree(p); } }
+    cudaError_t alloc(size_t bytes) { return cudaMalloc(&p, bytes ? bytes : 16); }
+    template <typename T> T *as() { return static_cast<T *>(p); }
+};
+}  // namespace
+
+void free_bvh8(Bvh8 *b) {
+    if (b->nodes) { cudaFree(b->nodes); }
+    if (b->tri_geom) { cudaFree(b->tri_geom); }
+    *b = Bvh8{};
+}
+
+cudaError_t build_bvh8(const float *d_tris9, int n, uint32_t flags, cudaStream_t stream, Bvh8 *out) {
+    (void)flags;
+    *out = Bvh8{};
+    cudaEvent_t ev0, ev1;
+    CUDA_TRY(cudaEventCreate(&ev0));
+    CUDA_TRY(cudaEventCreate(&ev1));
+    CUDA_TRY(cudaEventRecord(ev0, stream));
+    const uint32_t max_nodes = static_cast<uint32_t>(n > 16 ? n : 16);
+    CUDA_TRY(cudaMalloc(&out->nodes, static_cast<size_t>(max_nodes) * sizeof(Node8)));
+    CUDA_TRY(cudaMalloc(&out->tri_geom, static_cast<size_t>(n > 0 ? n : 1) * sizeof(TriGeom)));
+    out->n_prims = static_cast<uint32_t>(n);
+    if (n == 0) {
+        // empty root: no child is ever hit
+        CUDA_TRY(cudaMemsetAsync(out->nodes, 0, sizeof(Node8), stream));
+        out->n_nodes = 1;
+        CUDA_TRY(cudaStreamSynchronize(stream));
+        cudaEventDestroy(ev0); cudaEventDestroy(ev1);
+        return cudaSuccess;
+    }
+    const int T = 256;
+    const int nb = (n + T - 1) / T;
+    DevBuf plo, phi, cb, keys0, keys1, vals0, vals1, hist, misc;
+    DevBuf tl, tr, tp, tf, tc, tlo, thi, tflags, q0, q1;
+    CUDA_TRY(plo.alloc(sizeof(float) * 3ull * n)); CUDA_TRY(phi.alloc(sizeof(float) * 3ull * n));
+    CUDA_TRY(cb.alloc(sizeof(int) * 6));
+    CUDA_TRY(keys0.alloc(8ull * n)); CUDA_TRY(keys1.alloc(8ull * n));
+    CUDA_TRY(vals0.alloc(4ull * n)); CUDA_TRY(vals1.alloc(4ull * n));
+    const int rs_blocks = (n + RS_TILE - 1) / RS_TILE;
+    CUDA_TRY(hist.alloc(sizeof(uint32_t) * 256ull * rs_blocks));
+    {
+        const int init[6] = {0x7fffffff, 0x7fffffff, 0x7fffffff, static_cast<int>(0x80000000), static_cast<int>(0x80000000), static_cast<int>(0x80000000)};
+        CUDA_TRY(cudaMemcpyAsync(cb.p, init, sizeof(init), cudaMemcpyHostToDevice, stream));
+    }
+    k_prim_bounds<<<nb, T, 0, stream>>>(d_tris9, n, plo.as<float>(), phi.as<float>(), cb.as<int>());
+    k_morton<<<nb, T, 0, stream>>>(plo.as<float>(), phi.as<float>(), n, cb.as<int>(), keys0.as<unsigned long long>(), vals0.as<uint32_t>());
+    unsigned long long *ka = keys0.as<unsigned long long>(), *kb = keys1.as<unsigned long long>();
+    uint32_t *va = vals0.as<uint32_t>(), *vb = vals1.as<uint32_t>();
+    for (int pass = 0; pass < 8; ++pass) {
+        const int shift = pass * 8;
+        k_rs_hist<<<rs_blocks, RS_THREADS, 0, stream>>>(ka, n, shift, hist.as<uint32_t>(), rs_blocks);
+        k_rs_scan<<<1, 1024, 0, stream>>>(hist.as<uint32_t>(), 256ll * rs_blocks);
+        k_rs_scatter<<<rs_blocks, RS_THREADS, 0, stream>>>(ka, va, kb, vb, n, shift, hist.as<uint32_t>(), rs_blocks);
+        unsigned long long *tk = ka; ka = kb; kb = tk;
+        uint32_t *tv = va; va = vb; vb = tv;
+    }
+    // ka/va now hold the sorted keys / primitive ids
+    const int nn = 2 * n - 1;
+    BinTree t;
+    CUDA_TRY(tl.alloc(4ull * nn)); CUDA_TRY(tr.alloc(4ull * nn)); CUDA_TRY(tp.alloc(4ull * nn));
+    CUDA_TRY(tf.alloc(4ull * nn)); CUDA_TRY(tc.alloc(4ull * nn));
+    CUDA_TRY(tlo.alloc(12ull * nn)); CUDA_TRY(thi.alloc(12ull * nn)); CUDA_TRY(tflags.alloc(4ull * n));
+    t.left = tl.as<int>(); t.right = tr.as<int>(); t.parent = tp.as<int>(); t.first = tf.as<int>(); t.count = tc.as<int>();
+    t.lo = tlo.as<float>(); t.hi = thi.as<float>(); t.flags = tflags.as<int>();
+    CUDA_TRY(cudaMemsetAsync(t.flags, 0, 4ull * n, stream));
+    if (n > 1) { k_hierarchy<<<(n - 1 + T - 1) / T, T, 0, stream>>>(ka, n, t); }
+    k_refit<<<nb, T, 0, stream>>>(va, plo.as<float>(), phi.as<float>(), n, t);
+    // collapse, level by level
+    CUDA_TRY(misc.alloc(sizeof(uint32_t) * 8));
+    uint32_t *d_node_counter = misc.as<uint32_t>(), *d_tri_counter = d_node_counter + 1, *d_nout = d_node_counter + 2;
+    int *d_error = reinterpret_cast<int *>(d_node_counter + 3);
+    {
+        const uint32_t init[4] = {1u, 0u, 0u, 0u};
+        CUDA_TRY(cudaMemcpyAsync(misc.p, init, sizeof(init), cudaMemcpyHostToDevice, stream));
+    }
+    CUDA_TRY(q0.alloc(sizeof(WorkItem) * static_cast<size_t>(max_nodes)));
+    CUDA_TRY(q1.alloc(sizeof(WorkItem) * static_cast<size_t>(max_nodes)));
+    {
+        const WorkItem root{n == 1 ? 0 : 0, 0};  // node 0 is the root (internal 0, or the only leaf when n == 1)
+        CUDA_TRY(cudaMemcpyAsync(q0.p, &root, sizeof(root), cudaMemcpyHostToDevice, stream));
+    }
+    CollapseArgs a;
+    a.t = t; a.n = n; a.sorted = va; a.tris9 = d_tris9; a.nodes = out->nodes; a.tri_geom = out->tri_geom;
+    a.node_counter = d_node_counter; a.tri_counter = d_tri_counter; a.n_out = d_nout; a.max_nodes = max_nodes; a.error = d_error;
+    WorkItem *qi = q0.as<WorkItem>(), *qo = q1.as<WorkItem>();
+    uint32_t n_in = 1, levels = 0;
+    while (n_in > 0) {
+        a.in = qi; a.n_in = static_cast<int>(n_in); a.out = qo;
+        CUDA_TRY(cudaMemsetAsync(d_nout, 0, sizeof(uint32_t), stream));
+        k_collapse8<<<(n_in + 127) / 128, 128, 0, stream>>>(a);
+        uint32_t h[4];
+        CUDA_TRY(cudaMemcpyAsync(h, misc.p, sizeof(h), cudaMemcpyDeviceToHost, stream));
+        CUDA_TRY(cudaStreamSynchronize(stream));
+        if (h[3] != 0u) { return cudaErrorMemoryAllocation; }
+        n_in = h[2];
+        out->n_nodes = h[0];
+        WorkItem *tq = qi; qi = qo; qo = tq;
+        ++levels;
+        if (levels > 256) { return cudaErrorUnknown; }
+    }
+    out->levels = levels;
+    CUDA_TRY(cudaEventRecord(ev1, stream));
+    CUDA_TRY(cudaEventSynchronize(ev1));
+    CUDA_TRY(cudaEventElapsedTime(&out->build_ms, ev0, ev1));
+    cudaEventDestroy(ev0); cudaEventDestroy(ev1);
+    CUDA_TRY(cudaGetLastError());
+    return cudaSuccess;
+}
+
+}  // namespace mrt

@@ -1,0 +1,228 @@
+// Render kernels. Built with -fmad=false (see mrt_math.cuh).
+#include "mrt_render.h"
+#include "mrt_shade.cuh"
+
+namespace mrt {
+
+MRT_D void flush_counters(const RayCounters &rc, DeviceCounters *dc) {
+    const uint32_t p = __reduce_add_sync(0xffffffffu, rc.primary);
+    const uint32_t sh = __reduce_add_sync(0xffffffffu, rc.shadow);
+    const uint32_t se = __reduce_add_sync(0xffffffffu, rc.secondary);
+    if ((threadIdx.x & 31) == 0) {
+        if (p) { atomicAdd(&dc->rays_primary, static_cast<unsigned long long>(p)); }
+        if (sh) { atomicAdd(&dc->rays_shadow, static_cast<unsigned long long>(sh)); }
+        if (se) { atomicAdd(&dc->rays_secondary, static_cast<unsigned long long>(se)); }
+    }
+}
+
+// Renderer::renderScene's pixel body (Renderer.cpp:130-157) for one sample of every pixel: jitter, camera ray,
+// Shader::rayTrace, incrementalAvg. A warp covers an 8x4 pixel patch so that its rays stay coherent.
+template <int SHADER>
+__global__ void __launch_bounds__(128) k_render_sample(SceneDev s, CameraRec cam, RenderParams rp, const int32_t *__restrict__ inv_tile,
+                                                       int sample, int avg_n, FrameTargets tg, DeviceCounters *dc) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int patches_x = (rp.width + 7) >> 3;
+    const int patch = blockIdx.x * 4 + warp;
+    const int x = (patch % patches_x) * 8 + (lane & 7);
+    const int y = (patch / patches_x) * 4 + (lane >> 3);
+    RayCounters rc = {0u, 0u, 0u};
+    int overflow = 0;
+    uint32_t q = 0;
+    if (x < rp.width && y < rp.height && pixel_sequence(rp, inv_tile, x, y, sample, q)) {
+        const float invImgWidth = 1.0f / static_cast<float>(rp.width), invImgHeight = 1.0f / static_cast<float>(rp.height);
+        const float pixelWidth = 0.5f / static_cast<float>(rp.width), pixelHeight = 0.5f / static_cast<float>(rp.height);
+        const float u = static_cast<float>(x) * invImgWidth, v = static_cast<float>(y) * invImgHeight;
+        float r1 = 0.5f, r2 = 0.5f;
+        if (s.pixel_table != nullptr) {
+            r1 = __ldg(s.pixel_table + ((2u * q) & kArrayMask));
+            r2 = __ldg(s.pixel_table + ((2u * q + 1u) & kArrayMask));
+        }
+        const float deviationU = (r1 - 0.5f) * 2.0f * pixelWidth;
+        const float deviationV = (r2 - 0.5f) * 2.0f * pixelHeight;
+        v3 o, d;
+        generate_ray(cam, u, v, deviationU, deviationV, o, d);
+        rc.primary = 1u;
+        DrawState ds = {q, 0u, rp.seed};
+        const v3 rgb = ray_trace<SHADER>(s, rp, o, d, 1, ds, rc, &overflow);
+        const int pix = y * rp.width + x;
+        if (tg.bitmap != nullptr) { tg.bitmap[pix] = incremental_avg(rgb, tg.bitmap[pix], avg_n); }
+        if (tg.accum != nullptr) {
+            float4 a = tg.accum[pix];
+            a.x += static_cast<float>(f2u_x86(rgb.x * 255.0f)); a.y += static_cast<float>(f2u_x86(rgb.y * 255.0f));
+            a.z += static_cast<float>(f2u_x86(rgb.z * 255.0f)); a.w += 1.0f;
+            tg.accum[pix] = a;
+        }
+    }
+    flush_counters(rc, dc);
+    if (overflow) { dc->overflow = 1; }
+}
+
+// fp32 accumulator -> ABGR8888: the mean of the per-sample integer values, truncated, clamped (Utils.cpp:78-86)
+__global__ void k_resolve(const float4 *__restrict__ accum, int32_t *__restrict__ bitmap, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) { return; }
+    const float4 a = accum[i];
+    if (!(a.w > 0.0f)) { return; }   // pixel never rendered (F8): leave the caller's content
+    const uint32_t r = min(static_cast<uint32_t>(a.x / a.w), 255u), g = min(static_cast<uint32_t>(a.y / a.w), 255u), b = min(static_cast<uint32_t>(a.z / a.w), 255u);
+    bitmap[i] = static_cast<int32_t>(0xFF000000u | b << 16 | g << 8 | r);
+}
+
+__global__ void __launch_bounds__(128) k_trace_rays(SceneDev s, int64_t n, const float *__restrict__ o, const float *__restrict__ d,
+                                                    const int32_t *__restrict__ okind, const int32_t *__restrict__ oidx,
+                                                    const float *__restrict__ sdist, float *out_t, int32_t *out_kind, int32_t *out_idx,
+                                                    int32_t *out_mat, float *out_normal, DeviceCounters *dc) {
+    const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) { return; }
+    const v3 ro = mk3(o[3 * i], o[3 * i + 1], o[3 * i + 2]), rd = mk3(d[3 * i], d[3 * i + 1], d[3 * i + 2]);
+    const int sk = okind ? okind[i] : HIT_NONE, si = oidx ? oidx[i] : -1;
+    int overflow = 0;
+    if (sdist != nullptr && sdist[i] >= 0.0f) {
+        const bool occluded = trace_shadow(s, ro, rd, sdist[i], sk, si, &overflow);
+        out_t[i] = occluded ? 0.0f : sdist[i];
+        out_kind[i] = occluded ? 1 : 0; out_idx[i] = -1; out_mat[i] = -1;
+    } else {
+        HitRec h;
+        trace_closest(s, ro, rd, sk, si, h, &overflow);
+        out_t[i] = h.t; out_kind[i] = h.kind;
+        int idx = h.idx, mat = -1;
+        v3 nrm = mk3(0.0f, 1.0f, 0.0f);
+        if (h.kind != HIT_NONE) {
+            Surface sf;
+            resolve_surface(s, ro, rd, h, sf);
+            nrm = sf.normal;
+            if (h.kind == HIT_PLANE) { idx = s.planes[h.idx].id; mat = s.planes[h.idx].material; }
+            else if (h.kind == HIT_SPHERE) { idx = s.spheres[h.idx].id; mat = s.spheres[h.idx].material; }
+            else if (h.kind == HIT_TRIANGLE) { mat = __float_as_int(reinterpret_cast<const float4 *>(s.tri_shade + h.idx)[3].w); }
+        }
+        out_idx[i] = idx; out_mat[i] = mat;
+        if (out_normal) { out_normal[3 * i] = nrm.x; out_normal[3 * i + 1] = nrm.y; out_normal[3 * i + 2] = nrm.z; }
+    }
+    if (overflow) { dc->overflow = 1; }
+}
+
+__global__ void k_generate_rays(CameraRec cam, int64_t n, const float *__restrict__ uvdd, float *o, float *d) {
+    const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) { return; }
+    v3 ro, rd;
+    generate_ray(cam, uvdd[4 * i], uvdd[4 * i + 1], uvdd[4 * i + 2], uvdd[4 * i + 3], ro, rd);
+    o[3 * i] = ro.x; o[3 * i + 1] = ro.y; o[3 * i + 2] = ro.z;
+    d[3 * i] = rd.x; d[3 * i + 1] = rd.y; d[3 * i + 2] = rd.z;
+}
+
+template <int SHADER>
+__global__ void __launch_bounds__(128) k_shade_rays(SceneDev s, RenderParams rp, int64_t n, const float *__restrict__ o,
+                                                    const float *__restrict__ d, int depth, float *rgb, DeviceCounters *dc) {
+    const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) { return; }
+    RayCounters rc = {0u, 0u, 0u};
+    int overflow = 0;
+    DrawState ds = {static_cast<uint32_t>(i), 0u, rp.seed};
+    const v3 c = ray_trace<SHADER>(s, rp, mk3(o[3 * i], o[3 * i + 1], o[3 * i + 2]), mk3(d[3 * i], d[3 * i + 1], d[3 * i + 2]), depth, ds, rc, &overflow);
+    rgb[3 * i] = c.x; rgb[3 * i + 1] = c.y; rgb[3 * i + 2] = c.z;
+    if (overflow) { dc->overflow = 1; }
+}
+
+// ---- one-thread test kernels ----------------------------------------------------------------------------------
+__global__ void k_test_triangle(const float *t, const float *o, const float *d, float tmax, int self_skip, float *out) {
+    // t = the reference's 100-byte record: AC, AB, A, nA, nB, nC, tA, tB, tC, mat
+    const v3 AC = mk3(t[0], t[1], t[2]), AB = mk3(t[3], t[4], t[5]), A = mk3(t[6], t[7], t[8]);
+    const v3 ro = mk3(o[0], o[1], o[2]), rd = mk3(d[0], d[1], d[2]);
+    float tt, u, v;
+    out[0] = tmax;
+    out[1] = 0.0f; out[2] = 1.0f; out[3] = 0.0f; out[4] = -1.0f; out[5] = -1.0f; out[6] = 0.0f; out[7] = 0.0f; out[8] = 0.0f;
+    if (self_skip) { return; }
+    if (triangle_intersect(A, AB, AC, ro, rd, tt, u, v) && tt < tmax) {
+        const float w = 1.0f - u - v;
+        const v3 nA = mk3(t[9], t[10], t[11]), nB = mk3(t[12], t[13], t[14]), nC = mk3(t[15], t[16], t[17]);
+        const v3 nrm = normalize((nA * w + nB * u) + nC * v);
+        const v3 p = ro + rd * tt;
+        out[0] = tt; out[1] = nrm.x; out[2] = nrm.y; out[3] = nrm.z;
+        out[4] = (t[18] * w + t[20] * u) + t[22] * v; out[5] = (t[19] * w + t[21] * u) + t[23] * v;
+        out[6] = p.x; out[7] = p.y; out[8] = p.z;
+    }
+}
+__global__ void k_test_sphere(const float *s4, const float *o, const float *d, float tmax, float *out) {
+    const v3 ro = mk3(o[0], o[1], o[2]), rd = mk3(d[0], d[1], d[2]), c = mk3(s4[0], s4[1], s4[2]);
+    float t;
+    out[0] = tmax; out[1] = 0.0f; out[2] = 1.0f; out[3] = 0.0f;
+    if (sphere_intersect(c, s4[3], ro, rd, t) && t < tmax) {
+        const v3 n = normalize((ro + rd * t) - c);
+        out[0] = t; out[1] = n.x; out[2] = n.y; out[3] = n.z;
+    }
+}
+__global__ void k_test_plane(const float *p6, const float *o, const float *d, float tmax, float *out) {
+    float t;
+    out[0] = tmax;
+    if (plane_intersect(mk3(p6[0], p6[1], p6[2]), mk3(p6[3], p6[4], p6[5]), mk3(o[0], o[1], o[2]), mk3(d[0], d[1], d[2]), t) && t < tmax) { out[0] = t; }
+}
+__global__ void k_test_aabb(const float *b, const float *o, const float *d, int32_t *out) {
+    out[0] = aabb_intersect_exact(mk3(b[0], b[1], b[2]), mk3(b[3], b[4], b[5]), mk3(o[0], o[1], o[2]), mk3(d[0], d[1], d[2])) ? 1 : 0;
+}
+__global__ void k_test_incavg(const float *rgb, int32_t avg, int32_t n, int32_t *out) { out[0] = incremental_avg(mk3(rgb[0], rgb[1], rgb[2]), avg, n); }
+__global__ void k_test_halton(uint32_t first, int64_t n, uint32_t base, float *out) {
+    const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i < n) { out[i] = halton_sequence(first + static_cast<uint32_t>(i), base); }
+}
+
+// ---- launchers ------------------------------------------------------------------------------------------------
+cudaError_t launch_render_sample(const SceneDev &s, const CameraRec &cam, const RenderParams &rp, const int32_t *d_inv_tile,
+                                 int sample, int avg_n, FrameTargets tg, DeviceCounters *dc, cudaStream_t st) {
+    const int patches = ((rp.width + 7) / 8) * ((rp.height + 3) / 4);
+    const int blocks = (patches + 3) / 4;
+    switch (rp.shader) {
+        case 1: k_render_sample<1><<<blocks, 128, 0, st>>>(s, cam, rp, d_inv_tile, sample, avg_n, tg, dc); break;
+        case 3: k_render_sample<3><<<blocks, 128, 0, st>>>(s, cam, rp, d_inv_tile, sample, avg_n, tg, dc); break;
+        case 4: k_render_sample<4><<<blocks, 128, 0, st>>>(s, cam, rp, d_inv_tile, sample, avg_n, tg, dc); break;
+        default: k_render_sample<0><<<blocks, 128, 0, st>>>(s, cam, rp, d_inv_tile, sample, avg_n, tg, dc); break;
+    }
+    return cudaGetLastError();
+}
+cudaError_t launch_resolve(const float4 *accum, int32_t *bitmap, int n, cudaStream_t st) {
+    k_resolve<<<(n + 255) / 256, 256, 0, st>>>(accum, bitmap, n);
+    return cudaGetLastError();
+}
+cudaError_t launch_trace_rays(const SceneDev &s, int64_t n, const float *o, const float *d, const int32_t *okind, const int32_t *oidx,
+                              const float *sdist, float *out_t, int32_t *out_kind, int32_t *out_idx, int32_t *out_mat, float *out_normal,
+                              DeviceCounters *dc, cudaStream_t st) {
+    if (n == 0) { return cudaSuccess; }
+    k_trace_rays<<<static_cast<unsigned>((n + 127) / 128), 128, 0, st>>>(s, n, o, d, okind, oidx, sdist, out_t, out_kind, out_idx, out_mat, out_normal, dc);
+    return cudaGetLastError();
+}
+cudaError_t launch_generate_rays(const CameraRec &cam, int64_t n, const float *uvdd, float *o, float *d, cudaStream_t st) {
+    if (n == 0) { return cudaSuccess; }
+    k_generate_rays<<<static_cast<unsigned>((n + 127) / 128), 128, 0, st>>>(cam, n, uvdd, o, d);
+    return cudaGetLastError();
+}
+cudaError_t launch_shade_rays(const SceneDev &s, const RenderParams &rp, int64_t n, const float *o, const float *d, int depth,
+                              float *rgb, DeviceCounters *dc, cudaStream_t st) {
+    if (n == 0) { return cudaSuccess; }
+    const unsigned blocks = static_cast<unsigned>((n + 127) / 128);
+    switch (rp.shader) {
+        case 1: k_shade_rays<1><<<blocks, 128, 0, st>>>(s, rp, n, o, d, depth, rgb, dc); break;
+        case 3: k_shade_rays<3><<<blocks, 128, 0, st>>>(s, rp, n, o, d, depth, rgb, dc); break;
+        case 4: k_shade_rays<4><<<blocks, 128, 0, st>>>(s, rp, n, o, d, depth, rgb, dc); break;
+        default: k_shade_rays<0><<<blocks, 128, 0, st>>>(s, rp, n, o, d, depth, rgb, dc); break;
+    }
+    return cudaGetLastError();
+}
+cudaError_t launch_test_triangle(const float *tri25, const float *o, const float *d, float tmax, int self_skip, float *out9, cudaStream_t st) {
+    k_test_triangle<<<1, 1, 0, st>>>(tri25, o, d, tmax, self_skip, out9); return cudaGetLastError();
+}
+cudaError_t launch_test_sphere(const float *sph4, const float *o, const float *d, float tmax, float *out4, cudaStream_t st) {
+    k_test_sphere<<<1, 1, 0, st>>>(sph4, o, d, tmax, out4); return cudaGetLastError();
+}
+cudaError_t launch_test_plane(const float *pl6, const float *o, const float *d, float tmax, float *out1, cudaStream_t st) {
+    k_test_plane<<<1, 1, 0, st>>>(pl6, o, d, tmax, out1); return cudaGetLastError();
+}
+cudaError_t launch_test_aabb(const float *box6, const float *o, const float *d, int32_t *out, cudaStream_t st) {
+    k_test_aabb<<<1, 1, 0, st>>>(box6, o, d, out); return cudaGetLastError();
+}
+cudaError_t launch_test_incavg(const float *rgb, int32_t avg, int32_t n, int32_t *out, cudaStream_t st) {
+    k_test_incavg<<<1, 1, 0, st>>>(rgb, avg, n, out); return cudaGetLastError();
+}
+cudaError_t launch_test_halton(uint32_t first, int64_t n, uint32_t base, float *out, cudaStream_t st) {
+    if (n == 0) { return cudaSuccess; }
+    k_test_halton<<<static_cast<unsigned>((n + 255) / 256), 256, 0, st>>>(first, n, base, out); return cudaGetLastError();
+}
+
+}  // namespace mrt

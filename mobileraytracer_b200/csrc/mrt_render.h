@@ -1,0 +1,38 @@
+// Host launchers of the render / traversal kernels (mrt_render.cu).
+#pragma once
+#include "mrt_types.h"
+
+namespace mrt {
+
+struct FrameTargets {
+    int32_t *bitmap;      // device ABGR8888, updated in place with the reference's integer running average, or null
+    float4 *accum;        // device fp32 RGBA accumulator (adds trunc(255*c) per channel, .w += 1), or null
+};
+
+struct DeviceCounters {   // device memory, zeroed per frame
+    unsigned long long rays_primary, rays_shadow, rays_secondary;
+    int overflow;
+    int pad;
+};
+
+// One sample of every pixel through the fused megakernel (deterministic shaders: NoShadows, Whitted, DepthMap, Diffuse).
+cudaError_t launch_render_sample(const SceneDev &s, const CameraRec &cam, const RenderParams &rp, const int32_t *d_inv_tile,
+                                 int sample, int sample_number_for_avg, FrameTargets tg, DeviceCounters *d_counters, cudaStream_t st);
+cudaError_t launch_resolve(const float4 *accum, int32_t *bitmap, int n_pixels, cudaStream_t st);
+
+cudaError_t launch_trace_rays(const SceneDev &s, int64_t n, const float *o, const float *d, const int32_t *okind, const int32_t *oidx,
+                              const float *shadow_dist, float *out_t, int32_t *out_kind, int32_t *out_idx, int32_t *out_mat,
+                              float *out_normal, DeviceCounters *d_counters, cudaStream_t st);
+cudaError_t launch_generate_rays(const CameraRec &cam, int64_t n, const float *uvdd, float *o, float *d, cudaStream_t st);
+cudaError_t launch_shade_rays(const SceneDev &s, const RenderParams &rp, int64_t n, const float *o, const float *d, int depth,
+                              float *rgb, DeviceCounters *d_counters, cudaStream_t st);
+
+// one-thread kernels behind the mrt_test_* entry points; all pointers are device pointers
+cudaError_t launch_test_triangle(const float *tri25, const float *o, const float *d, float tmax, int self_skip, float *out9, cudaStream_t st);
+cudaError_t launch_test_sphere(const float *sph4, const float *o, const float *d, float tmax, float *out4, cudaStream_t st);
+cudaError_t launch_test_plane(const float *pl6, const float *o, const float *d, float tmax, float *out1, cudaStream_t st);
+cudaError_t launch_test_aabb(const float *box6, const float *o, const float *d, int32_t *out, cudaStream_t st);
+cudaError_t launch_test_incavg(const float *rgb, int32_t avg, int32_t n, int32_t *out, cudaStream_t st);
+cudaError_t launch_test_halton(uint32_t first, int64_t n, uint32_t base, float *out, cudaStream_t st);
+
+}  // namespace mrt

@@ -1,0 +1,241 @@
+// Camera rays, sampler draws and the shading functions of the deterministic shaders, in the reference's operation order.
+#pragma once
+#include "mrt_traverse.cuh"
+
+namespace mrt {
+
+// Perspective::generateRay (Components/Cameras/Perspective.cpp:16-28) / Orthographic::generateRay (Orthographic.cpp:15-23)
+MRT_D void generate_ray(const CameraRec &c, float u, float v, float du, float dv, v3 &o, v3 &d) {
+    if (c.kind == 0) {
+        const float tanValueRight = c.a * (u - 0.5f);
+        const float rightFactor = fast_arctan(tanValueRight) + du;
+        const v3 right = c.right * rightFactor;
+        const float tanValueUp = c.b * (0.5f - v);
+        const float upFactor = fast_arctan(tanValueUp) + dv;
+        const v3 up = c.up * upFactor;
+        const v3 dest = ((c.position + c.direction) + right) + up;
+        d = normalize(dest - c.position);
+        o = c.position;
+    } else {
+        const float rightFactor = (u - 0.5f) * c.a;
+        const v3 right = c.right * rightFactor + c.right * du;
+        const float upFactor = (0.5f - v) * c.b;
+        const v3 up = c.up * upFactor + c.up * dv;
+        d = c.direction;
+        o = (c.position + right) + up;
+    }
+}
+
+// Pixel -> (tile order position, jitter draw index): what a single-threaded Renderer::renderScene (Renderer.cpp:117-141)
+// would have consumed from the pixel sampler before reaching this pixel of this sample. inv_tile[rb] = position of
+// tile rb in the shuffled tile table (Renderer.cpp:189-197).
+struct PixelOrder {
+    int32_t inv_tile[kNumberOfTiles];
+};
+
+MRT_D bool pixel_sequence(const RenderParams &rp, const int32_t *inv_tile, int x, int y, int sample, uint32_t &q) {
+    if (x >= rp.bsx * 16 || y >= rp.bsy * 16) { return false; }   // remainder rows/cols are never rendered (F8)
+    const int tx = x / rp.bsx, ty = y / rp.bsy;
+    const int k = inv_tile[ty * 16 + tx];
+    const uint32_t perTile = static_cast<uint32_t>(rp.bsx * rp.bsy);
+    q = (static_cast<uint32_t>(sample) * kNumberOfTiles + static_cast<uint32_t>(k)) * perTile +
+        static_cast<uint32_t>((y - ty * rp.bsy) * rp.bsx + (x - tx * rp.bsx));
+    return true;
+}
+
+MRT_D uint32_t hash_u32(uint32_t a, uint32_t b, uint32_t c) {
+    uint32_t h = a * 0x9E3779B1u ^ (b + 0x7F4A7C15u) * 0x85EBCA77u ^ (c + 0x165667B1u) * 0xC2B2AE3Du;
+    h ^= h >> 16; h *= 0x85EBCA6Bu; h ^= h >> 13; h *= 0xC2B2AE35u; h ^= h >> 16;
+    return h;
+}
+
+// Where a draw of the shared tables comes from. The reference hands out table[counter++ & mask] in execution order
+// (Shader.cpp:188-233, Sampler.hpp:58-63). In replay mode the exact counters are supplied; otherwise every
+// (pixel-sample q, event e, stream) gets its own decorrelated slot of the same table.
+struct DrawState {
+    uint32_t q;         // pixel-sample sequence id
+    uint32_t e;         // running event counter of this pixel-sample
+    uint32_t seed;
+};
+enum DrawStream : uint32_t { DS_LIGHT_INDEX = 1, DS_LIGHT_POS = 2, DS_HEMI = 3, DS_RR = 4 };
+
+MRT_D float draw(const float *table, DrawState &ds, uint32_t stream) {
+    const uint32_t i = hash_u32(ds.q, ds.e++, stream ^ ds.seed) & kArrayMask;
+    return __ldg(table + i);
+}
+
+struct Surface {
+    v3 point, normal;
+    v3 Le, Kd, Ks, Kt;
+    float ior;
+    int32_t skipKind, skipIdx;   // the primitive a ray leaving this surface must skip (Ray::primitive_)
+};
+
+MRT_D void load_material(const SceneDev &s, int m, Surface &sf) {
+    const float4 *mp = reinterpret_cast<const float4 *>(s.materials + m);
+    const float4 a = __ldg(mp), b = __ldg(mp + 1), c = __ldg(mp + 2), d = __ldg(mp + 3);
+    sf.Le = mk3(a.x, a.y, a.z); sf.Kd = mk3(a.w, b.x, b.y); sf.Ks = mk3(b.z, b.w, c.x); sf.Kt = mk3(c.y, c.z, c.w); sf.ior = d.x;
+}
+
+// What the primitive's intersect() stores in the Intersection (Triangle.cpp:100-108, Sphere.cpp:69-78, Plane.cpp:64-70)
+// plus Shader::rayTrace's material lookup (Shader.cpp:112-121; AreaLight.cpp:32-41 for lights).
+MRT_D void resolve_surface(const SceneDev &s, v3 o, v3 d, const HitRec &h, Surface &sf) {
+    sf.point = o + d * h.t;
+    sf.skipKind = HIT_NONE; sf.skipIdx = -1;
+    if (h.kind == HIT_TRIANGLE) {
+        const float4 *sp = reinterpret_cast<const float4 *>(s.tri_shade + h.idx);
+        const float4 s0 = __ldg(sp), s1 = __ldg(sp + 1), s2 = __ldg(sp + 2), s3 = __ldg(sp + 3);
+        const float w = 1.0f - h.u - h.v;
+        const v3 nA = mk3(s0.x, s0.y, s0.z), nB = mk3(s0.w, s1.x, s1.y), nC = mk3(s1.z, s1.w, s2.x);
+        sf.normal = normalize((nA * w + nB * h.u) + nC * h.v);
+        load_material(s, __float_as_int(s3.w), sf);
+        sf.skipKind = HIT_TRIANGLE; sf.skipIdx = h.idx;
+    } else if (h.kind == HIT_SPHERE) {
+        const SphereRec sp = s.spheres[h.idx];
+        sf.normal = normalize(sf.point - mk3(sp.cx, sp.cy, sp.cz));
+        load_material(s, sp.material, sf);
+    } else if (h.kind == HIT_PLANE) {
+        const PlaneRec p = s.planes[h.idx];
+        sf.normal = mk3(p.nx, p.ny, p.nz);
+        load_material(s, p.material, sf);
+        sf.skipKind = HIT_PLANE; sf.skipIdx = h.idx;
+    } else {  // HIT_LIGHT: material = the light's radiance_ (Le only)
+        const LightRec &l = s.lights[h.idx];
+        sf.normal = mk3(0.0f, 1.0f, 0.0f);
+        sf.Le = mk3(l.Le[0], l.Le[1], l.Le[2]);
+        sf.Kd = sf.Ks = sf.Kt = mk3(0.0f, 0.0f, 0.0f);
+        sf.ior = 1.0f;
+    }
+}
+
+// Shader::getLightIndex (Shader.cpp:223-233)
+MRT_D uint32_t light_index(const SceneDev &s, DrawState &ds) {
+    const float r = draw(s.shader_table, ds, DS_LIGHT_INDEX);
+    return static_cast<uint32_t>(floorf(r * static_cast<float>(static_cast<uint32_t>(s.n_lights)) * 0.99999f));
+}
+// PointLight::getPosition (PointLight.cpp:16-18) / AreaLight::getPosition (AreaLight.cpp:17-26)
+MRT_D v3 light_position(const SceneDev &s, const LightRec &l, DrawState &ds) {
+    if (l.kind == 0) { return mk3(l.A[0], l.A[1], l.A[2]); }
+    float r = draw(s.static_halton, ds, DS_LIGHT_POS);
+    float q = draw(s.static_halton, ds, DS_LIGHT_POS);
+    if (r + q >= 1.0f) { r = 1.0f - r; q = 1.0f - q; }
+    return (mk3(l.A[0], l.A[1], l.A[2]) + r * mk3(l.AB[0], l.AB[1], l.AB[2])) + q * mk3(l.AC[0], l.AC[1], l.AC[2]);
+}
+
+struct RayCounters { uint32_t primary, shadow, secondary; };
+
+// Direct lighting term shared by Whitted (Whitted.cpp:37-64) and NoShadows (NoShadows.cpp:25-43); SHADOWS selects which.
+template <bool SHADOWS>
+MRT_D v3 direct_light(const SceneDev &s, const RenderParams &rp, const Surface &sf, DrawState &ds, RayCounters &rc, int *overflow) {
+    v3 rgb = mk3(0.0f, 0.0f, 0.0f);
+    if (has_positive(sf.Kd) && s.n_lights > 0) {
+        for (int i = 0; i < rp.spl; ++i) {
+            const uint32_t chosen = light_index(s, ds);
+            const LightRec &l = s.lights[chosen];
+            const v3 lightPosition = light_position(s, l, ds);
+            v3 vectorToLight = lightPosition - sf.point;
+            const float distanceToLight = length(vectorToLight);
+            vectorToLight = normalize(vectorToLight);
+            const float cosNl = dot(sf.normal, vectorToLight);
+            if (cosNl > 0.0f) {
+                bool lit = true;
+                if (SHADOWS) {
+                    ++rc.shadow;
+                    lit = !trace_shadow(s, sf.point, vectorToLight, distanceToLight, sf.skipKind, sf.skipIdx, overflow);
+                }
+                if (lit) { rgb = rgb + mk3(l.Le[0], l.Le[1], l.Le[2]) * cosNl; }
+            }
+        }
+        rgb = rgb * sf.Kd;
+        rgb = rgb / static_cast<float>(rp.spl);
+    }
+    return rgb;
+}
+
+// DepthMap::shade (DepthMap.cpp:12-17)
+MRT_D v3 shade_depthmap(const RenderParams &rp, v3 rayOrigin, float t) {
+    const float maxDist = length(rp.depth_max_point - rayOrigin) * 1.1f;
+    const float depth = std_max((maxDist - t) / maxDist, 0.0f);
+    return mk3(depth, depth, depth);
+}
+// DiffuseMaterial::shade (DiffuseMaterial.cpp:11-27)
+MRT_D v3 shade_diffuse(const Surface &sf) {
+    if (has_positive(sf.Kd)) { return sf.Kd; }
+    if (has_positive(sf.Ks)) { return sf.Ks; }
+    if (has_positive(sf.Kt)) { return sf.Kt; }
+    if (has_positive(sf.Le)) { return sf.Le; }
+    return mk3(0.0f, 0.0f, 0.0f);
+}
+
+// Whitted::shade driven by Shader::rayTrace (Whitted.cpp:13-93, Shader.cpp:86-123): the recursion is unrolled into an
+// explicit frame stack so that every partial sum is formed in the reference's order.
+struct WhittedFrame {
+    v3 rgb, Kd, Ks, Kt, P, N, D;
+    float ior;
+    int32_t skipKind, skipIdx, depth, stage;
+};
+
+template <int SHADER>
+MRT_D v3 ray_trace(const SceneDev &s, const RenderParams &rp, v3 o, v3 d, int depth0, DrawState &ds, RayCounters &rc, int *overflow) {
+    HitRec h;
+    Surface sf;
+    if (SHADER != 1) {
+        trace_closest(s, o, d, HIT_NONE, -1, h, overflow);
+        if (h.kind == HIT_NONE) { return mk3(0.0f, 0.0f, 0.0f); }
+        if (SHADER == 3) { return shade_depthmap(rp, o, h.t); }
+        resolve_surface(s, o, d, h, sf);
+        if (SHADER == 4) { return shade_diffuse(sf); }
+        // NoShadows (NoShadows.cpp:12-46)
+        if (has_positive(sf.Le)) { return sf.Le; }
+        v3 rgb = direct_light<false>(s, rp, sf, ds, rc, overflow);
+        return rgb + sf.Kd * 0.1f;
+    }
+    WhittedFrame fr[kRayDepthMax + 1];
+    int sp = 0;
+    int depth = depth0;
+    int skipKind = HIT_NONE, skipIdx = -1;
+    v3 result = mk3(0.0f, 0.0f, 0.0f);
+    bool calling = true;
+    while (true) {
+        if (calling) {
+            result = mk3(0.0f, 0.0f, 0.0f);
+            calling = false;
+            if (depth > kRayDepthMax) { continue; }   // Whitted.cpp:15-17: rgb stays 0 whatever the ray hits
+            trace_closest(s, o, d, skipKind, skipIdx, h, overflow);
+            if (h.kind == HIT_NONE) { continue; }
+            resolve_surface(s, o, d, h, sf);
+            if (has_positive(sf.Le)) { result = sf.Le; continue; }
+            v3 rgb = direct_light<true>(s, rp, sf, ds, rc, overflow);
+            const bool spec = has_positive(sf.Ks), trans = has_positive(sf.Kt);
+            if (!spec && !trans) { result = rgb + sf.Kd * 0.1f; continue; }
+            WhittedFrame &f = fr[sp++];
+            f.rgb = rgb; f.Kd = sf.Kd; f.Ks = sf.Ks; f.Kt = sf.Kt; f.P = sf.point; f.N = sf.normal; f.D = d;
+            f.ior = sf.ior; f.skipKind = sf.skipKind; f.skipIdx = sf.skipIdx; f.depth = depth;
+            ++rc.secondary;
+            if (spec) { f.stage = 0; d = reflect(f.D, f.N); }
+            else { f.stage = 1; d = refract(f.D, f.N, 1.0f / f.ior); }
+            o = f.P; depth = f.depth + 1; skipKind = f.skipKind; skipIdx = f.skipIdx;
+            calling = true;
+        } else {
+            if (sp == 0) { return result; }
+            WhittedFrame &f = fr[sp - 1];
+            if (f.stage == 0) {
+                f.rgb = f.rgb + f.Ks * result;
+                if (has_positive(f.Kt)) {
+                    f.stage = 1;
+                    ++rc.secondary;
+                    d = refract(f.D, f.N, 1.0f / f.ior);
+                    o = f.P; depth = f.depth + 1; skipKind = f.skipKind; skipIdx = f.skipIdx;
+                    calling = true;
+                    continue;
+                }
+            } else {
+                f.rgb = f.rgb + f.Kt * result;
+            }
+            result = f.rgb + f.Kd * 0.1f;
+            --sp;
+        }
+    }
+}
+
+}  // namespace mrt

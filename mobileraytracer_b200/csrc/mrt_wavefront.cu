@@ -1,0 +1,420 @@
+// Wavefront path tracer: PathTracer::shade (Components/Shaders/PathTracer.cpp:22-142) driven by Shader::rayTrace
+// (MobileRT/Shader.cpp:86-123), re-expressed as generate / extend / shade / shadow / finalize kernels over compacted
+// ray queues in HBM. Built with -fmad=false (see mrt_math.cuh).
+//
+// The reference's recursion has one non-local rule: at a vertex with direct light (Ld > 0) the WHOLE indirect diffuse
+// term is dropped when the diffuse chain below it ends on an emitter (PathTracer.cpp:99-110, the bool returned up the
+// recursion). A "chain" is therefore the unit of bookkeeping: a maximal sequence of diffuse bounces. Every chain owns a
+// record with one radiance sum per depth, a bit mask of depths that saw direct light and an "ended on an emitter" flag;
+// specular / transmission rays start child chains that are folded into the parent's sum of the spawning depth.
+// After the last level the chains are finalised deepest-first, which reproduces the recursion's result exactly:
+//   not ended on emitter : total = sum over all depths
+//   ended on emitter     : total = sum over depths <= first depth with direct light (+ the emitter term if there is none)
+#include "mrt_wavefront.h"
+#include "mrt_shade.cuh"
+#include <vector>
+
+namespace mrt {
+
+constexpr int kLevels = kRayDepthMax;          // depths 1..6 are traced; a depth-7 ray contributes nothing (PathTracer.cpp:24-26)
+constexpr int kWfThreads = 128;
+
+struct __align__(16) Chain {
+    float sum[kLevels][3];   // [depth-1]: throughput-weighted Ld and folded child chains of that vertex
+    float emit[3];           // throughput-weighted Le when the chain ends on an emitter
+    uint32_t ldmask;         // bit (depth-1): direct light at that vertex was > 0
+    uint32_t ended_on_light;
+    int32_t parent;          // parent chain, -1 for a camera path
+    int32_t parent_depth;    // depth of the vertex that spawned this chain; root: pixel index
+    uint32_t pad[7];
+};
+static_assert(sizeof(Chain) == 128, "Chain must be 128 bytes");
+
+struct Queues {
+    // ray queue (SoA of float4): r0 = o.xyz d.x | r1 = d.y d.z skip depth | r2 = T.xyz chain | r3 = q branch - -
+    float4 *r0[2], *r1[2], *r2[2], *r3[2];
+    float4 *hit;                 // t u v (kind << 28 | idx)
+    float4 *s0, *s1, *s2;        // shadow queue: o.xyz d.x | d.y d.z dist skip | c.xyz (chain | depth << 28)
+    Chain *chains;
+    uint32_t *counts;            // [0..7] ray count per level, [8] shadow count, [9] chain pool size, [10..17] chain pool size after each level
+    uint32_t cap_rays, cap_shadow, cap_chains;
+};
+
+struct WfMark { cudaEvent_t ev; int cls; };
+
+struct Wavefront {
+    Queues q {};
+    int width = 0, height = 0;
+    int sm_count = 148;
+    std::vector<void *> allocs;
+    std::vector<WfMark> marks;        // one event after every launch; the class says what ran before it
+    std::vector<cudaEvent_t> pool;
+    size_t used = 0;
+};
+
+MRT_D uint32_t pack_skip(int kind, int idx) { return kind == HIT_NONE ? 0u : (static_cast<uint32_t>(kind) << 28) | (static_cast<uint32_t>(idx) & 0x0fffffffu); }
+MRT_D void unpack_skip(uint32_t s, int &kind, int &idx) { kind = static_cast<int>(s >> 28); idx = kind == HIT_NONE ? -1 : static_cast<int>(s & 0x0fffffffu); }
+
+// warp-aggregated slot allocation: one atomic per warp per push site
+MRT_D uint32_t queue_push(uint32_t *counter) {
+    const uint32_t mask = __activemask();
+    const int lane = threadIdx.x & 31;
+    const int leader = __ffs(mask) - 1;
+    uint32_t base = 0;
+    if (lane == leader) { base = atomicAdd(counter, static_cast<uint32_t>(__popc(mask))); }
+    base = __shfl_sync(mask, base, leader);
+    return base + __popc(mask & ((1u << lane) - 1u));
+}
+
+// ---- generate: Renderer::renderScene's jitter + Camera::generateRay (Renderer.cpp:130-141) ---------------------------
+__global__ void __launch_bounds__(kWfThreads) k_wf_generate(Queues Q, CameraRec cam, RenderParams rp, const float *__restrict__ pixel_table,
+                                                            const int32_t *__restrict__ inv_tile, int sample, DeviceCounters *dc) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int patches_x = (rp.width + 7) >> 3;
+    const int patch = blockIdx.x * (kWfThreads / 32) + warp;
+    const int x = (patch % patches_x) * 8 + (lane & 7);
+    const int y = (patch / patches_x) * 4 + (lane >> 3);
+    uint32_t q = 0;
+    RayCounters rc = {0u, 0u, 0u};
+    if (x < rp.width && y < rp.height && pixel_sequence(rp, inv_tile, x, y, sample, q)) {
+        const float invImgWidth = 1.0f / static_cast<float>(rp.width), invImgHeight = 1.0f / static_cast<float>(rp.height);
+        const float pixelWidth = 0.5f / static_cast<float>(rp.width), pixelHeight = 0.5f / static_cast<float>(rp.height);
+        const float u = static_cast<float>(x) * invImgWidth, v = static_cast<float>(y) * invImgHeight;
+        float r1 = 0.5f, r2 = 0.5f;
+        if (pixel_table != nullptr) { r1 = __ldg(pixel_table + ((2u * q) & kArrayMask)); r2 = __ldg(pixel_table + ((2u * q + 1u) & kArrayMask)); }
+        v3 o, d;
+        generate_ray(cam, u, v, (r1 - 0.5f) * 2.0f * pixelWidth, (r2 - 0.5f) * 2.0f * pixelHeight, o, d);
+        const uint32_t slot = queue_push(&Q.counts[0]);
+        // the root chain of camera path `slot` is chain `slot`
+        Chain *c = Q.chains + slot;
+        float4 *cz = reinterpret_cast<float4 *>(c);
+#pragma unroll
+        for (int k = 0; k < 6; ++k) { cz[k] = make_float4(0.0f, 0.0f, 0.0f, 0.0f); }
+        c->parent = -1; c->parent_depth = y * rp.width + x;
+        Q.r0[0][slot] = make_float4(o.x, o.y, o.z, d.x);
+        Q.r1[0][slot] = make_float4(d.y, d.z, __uint_as_float(0u), __int_as_float(1));
+        Q.r2[0][slot] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(slot));
+        Q.r3[0][slot] = make_float4(__uint_as_float(q), __uint_as_float(1u), 0.0f, 0.0f);
+        rc.primary = 1u;
+    }
+    const uint32_t p = __reduce_add_sync(0xffffffffu, rc.primary);
+    if (lane == 0 && p) { atomicAdd(&dc->rays_primary, static_cast<unsigned long long>(p)); }
+}
+
+// the chain pool starts right after the root chains
+__global__ void k_wf_begin_levels(Queues Q) { Q.counts[9] = Q.counts[0]; }
+
+// ---- extend: closest hit for every ray of the level ------------------------------------------------------------------
+__global__ void __launch_bounds__(kWfThreads) k_wf_extend(SceneDev s, Queues Q, int level, DeviceCounters *dc) {
+    const int b = level & 1;
+    const uint32_t n = min(Q.counts[level], Q.cap_rays);
+    int overflow = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float4 a = Q.r0[b][i], c = Q.r1[b][i];
+        int sk, si;
+        unpack_skip(__float_as_uint(c.z), sk, si);
+        HitRec h;
+        trace_closest(s, mk3(a.x, a.y, a.z), mk3(a.w, c.x, c.y), sk, si, h, &overflow);
+        Q.hit[i] = make_float4(h.t, h.u, h.v, __uint_as_float((static_cast<uint32_t>(h.kind) << 28) | (static_cast<uint32_t>(h.idx) & 0x0fffffffu)));
+    }
+    if (overflow) { dc->overflow = 1; }
+}
+
+// Shader::getCosineSampleHemisphere (Shader.cpp:188-216)
+MRT_D v3 cosine_sample_hemisphere(v3 normal, float uniformRandom1, float uniformRandom2) {
+    const float phi = 6.28318530717958647692528676655900576f * uniformRandom1;
+    const float r2 = uniformRandom2;
+    const float cosTheta = sqrtf(r2);
+    v3 u = fabsf(normal.x) > 0.1f ? mk3(0.0f, 1.0f, 0.0f) : mk3(1.0f, 0.0f, 0.0f);
+    u = normalize(cross(u, normal));
+    const v3 v = cross(normal, u);
+    v3 direction = (u * (cosf(phi) * cosTheta) + v * (sinf(phi) * cosTheta)) + normal * sqrtf(1.0f - r2);
+    return normalize(direction);
+}
+
+// ---- shade: PathTracer::shade for every hit of the level; emits shadow rays and the next level's rays --------------
+__global__ void __launch_bounds__(kWfThreads) k_wf_shade(SceneDev s, RenderParams rp, Queues Q, int level, DeviceCounters *dc) {
+    const int b = level & 1, nb = b ^ 1;
+    const uint32_t n = min(Q.counts[level], Q.cap_rays);
+    RayCounters rc = {0u, 0u, 0u};
+    int overflow = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float4 hq = Q.hit[i];
+        const uint32_t packed = __float_as_uint(hq.w);
+        HitRec h;
+        h.t = hq.x; h.u = hq.y; h.v = hq.z; h.kind = static_cast<int>(packed >> 28); h.idx = static_cast<int>(packed & 0x0fffffffu);
+        if (h.kind == HIT_NONE) { continue; }                      // Shader.cpp:122: no intersection, rgb stays 0
+        const float4 a = Q.r0[b][i], c1 = Q.r1[b][i], c2 = Q.r2[b][i], c3 = Q.r3[b][i];
+        const v3 o = mk3(a.x, a.y, a.z), d = mk3(a.w, c1.x, c1.y), T = mk3(c2.x, c2.y, c2.z);
+        const int depth = __float_as_int(c1.w);
+        const uint32_t chain = __float_as_uint(c2.w);
+        const uint32_t q = __float_as_uint(c3.x), branch = __float_as_uint(c3.y);
+        Surface sf;
+        resolve_surface(s, o, d, h, sf);
+        Chain *ch = Q.chains + chain;
+        if (has_positive(sf.Le)) {                                  // PathTracer.cpp:28-33: stop on a light source
+            const v3 e = T * sf.Le;
+            ch->emit[0] = e.x; ch->emit[1] = e.y; ch->emit[2] = e.z;
+            ch->ended_on_light = 1u;
+            continue;
+        }
+        DrawState ds = {q, branch * 16u, rp.seed};
+        const bool diffuse = has_positive(sf.Kd);
+        if (diffuse && s.n_lights > 0) {                            // PathTracer.cpp:55-87: direct light, one shadow ray per light sample
+            for (int k = 0; k < rp.spl; ++k) {
+                const uint32_t chosen = light_index(s, ds);
+                const LightRec &l = s.lights[chosen];
+                const v3 lightPosition = light_position(s, l, ds);
+                v3 vectorToLight = lightPosition - sf.point;
+                const float distanceToLight = length(vectorToLight);
+                vectorToLight = normalize(vectorToLight);
+                const float cosNormalLight = dot(sf.normal, vectorToLight);
+                if (cosNormalLight > 0.0f) {
+                    ++rc.shadow;
+                    // Ld's share of this light sample: (Le * cos) * kD / samplesLight, times the path throughput
+                    const v3 ld = ((mk3(l.Le[0], l.Le[1], l.Le[2]) * cosNormalLight) * sf.Kd) / static_cast<float>(rp.spl);
+                    const v3 cc = T * ld;
+                    const uint32_t slot = queue_push(&Q.counts[8]);
+                    if (slot < Q.cap_shadow) {
+                        Q.s0[slot] = make_float4(sf.point.x, sf.point.y, sf.point.z, vectorToLight.x);
+                        Q.s1[slot] = make_float4(vectorToLight.y, vectorToLight.z, distanceToLight, __uint_as_float(pack_skip(sf.skipKind, sf.skipIdx)));
+                        const uint32_t tag = chain | (static_cast<uint32_t>(depth - 1) << 28) | (has_positive(ld) ? 0x80000000u : 0u);
+                        Q.s2[slot] = make_float4(cc.x, cc.y, cc.z, __uint_as_float(tag));
+                    } else { overflow = 1; }
+                }
+            }
+        }
+        const bool traceable = depth + 1 <= kRayDepthMax;           // deeper rays are constructed (counted) but add nothing
+        if (diffuse) {                                              // PathTracer.cpp:89-111: indirect diffuse with russian roulette
+            bool go = depth <= kRayDepthMin;
+            if (!go) { go = draw(s.static_halton, ds, DS_RR) > 0.5f; }
+            if (go) {
+                const float r1 = draw(s.shader_table, ds, DS_HEMI), r2 = draw(s.shader_table, ds, DS_HEMI);
+                const v3 nd = cosine_sample_hemisphere(sf.normal, r1, r2);
+                ++rc.secondary;
+                if (traceable) {
+                    v3 Tn = T * sf.Kd;
+                    if (depth > kRayDepthMin) { Tn = Tn / (0.5f * 0.5f); }
+                    const uint32_t slot = queue_push(&Q.counts[level + 1]);
+                    if (slot < Q.cap_rays) {
+                        Q.r0[nb][slot] = make_float4(sf.point.x, sf.point.y, sf.point.z, nd.x);
+                        Q.r1[nb][slot] = make_float4(nd.y, nd.z, __uint_as_float(pack_skip(sf.skipKind, sf.skipIdx)), __int_as_float(depth + 1));
+                        Q.r2[nb][slot] = make_float4(Tn.x, Tn.y, Tn.z, __uint_as_float(chain));
+                        Q.r3[nb][slot] = make_float4(__uint_as_float(q), __uint_as_float(branch * 4u + 1u), 0.0f, 0.0f);
+                    } else { overflow = 1; }
+                }
+            }
+        }
+#pragma unroll
+        for (int kind = 0; kind < 2; ++kind) {                      // PathTracer.cpp:113-134: specular reflection, then transmission
+            const v3 K = kind == 0 ? sf.Ks : sf.Kt;
+            if (!has_positive(K)) { continue; }
+            ++rc.secondary;
+            if (!traceable) { continue; }
+            const v3 nd = kind == 0 ? reflect(d, sf.normal) : refract(d, sf.normal, 1.0f / sf.ior);
+            const uint32_t cslot = queue_push(&Q.counts[9]);
+            const uint32_t slot = queue_push(&Q.counts[level + 1]);
+            if (cslot < Q.cap_chains && slot < Q.cap_rays) {
+                Chain *nc = Q.chains + cslot;
+                float4 *cz = reinterpret_cast<float4 *>(nc);
+#pragma unroll
+                for (int k = 0; k < 6; ++k) { cz[k] = make_float4(0.0f, 0.0f, 0.0f, 0.0f); }
+                nc->parent = static_cast<int32_t>(chain); nc->parent_depth = depth;
+                const v3 Tn = T * K;
+                Q.r0[nb][slot] = make_float4(sf.point.x, sf.point.y, sf.point.z, nd.x);
+                Q.r1[nb][slot] = make_float4(nd.y, nd.z, __uint_as_float(pack_skip(sf.skipKind, sf.skipIdx)), __int_as_float(depth + 1));
+                Q.r2[nb][slot] = make_float4(Tn.x, Tn.y, Tn.z, __uint_as_float(cslot));
+                Q.r3[nb][slot] = make_float4(__uint_as_float(q), __uint_as_float(branch * 4u + 2u + static_cast<uint32_t>(kind)), 0.0f, 0.0f);
+            } else { overflow = 1; }
+        }
+    }
+    const uint32_t sh = __reduce_add_sync(0xffffffffu, rc.shadow), se = __reduce_add_sync(0xffffffffu, rc.secondary);
+    if ((threadIdx.x & 31) == 0) {
+        if (sh) { atomicAdd(&dc->rays_shadow, static_cast<unsigned long long>(sh)); }
+        if (se) { atomicAdd(&dc->rays_secondary, static_cast<unsigned long long>(se)); }
+    }
+    if (overflow) { dc->overflow = 1; }
+}
+
+// ---- shadow: any-hit; an unoccluded sample adds its share of Ld to the chain ---------------------------------------
+__global__ void __launch_bounds__(kWfThreads) k_wf_shadow(SceneDev s, Queues Q, DeviceCounters *dc) {
+    const uint32_t n = min(Q.counts[8], Q.cap_shadow);
+    int overflow = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const float4 a = Q.s0[i], c = Q.s1[i];
+        int sk, si;
+        unpack_skip(__float_as_uint(c.w), sk, si);
+        if (trace_shadow(s, mk3(a.x, a.y, a.z), mk3(a.w, c.x, c.y), c.z, sk, si, &overflow)) { continue; }
+        const float4 cc = Q.s2[i];
+        const uint32_t tag = __float_as_uint(cc.w);
+        Chain *ch = Q.chains + (tag & 0x0fffffffu);
+        const uint32_t dz = (tag >> 28) & 7u;
+        atomicAdd(&ch->sum[dz][0], cc.x); atomicAdd(&ch->sum[dz][1], cc.y); atomicAdd(&ch->sum[dz][2], cc.z);
+        if (tag & 0x80000000u) { atomicOr(&ch->ldmask, 1u << dz); }
+    }
+    if (overflow) { dc->overflow = 1; }
+}
+
+__global__ void k_wf_end_level(Queues Q, int level) {
+    Q.counts[8] = 0u;                         // shadow queue consumed
+    Q.counts[10 + level] = min(Q.counts[9], Q.cap_chains);   // chain pool size after this level
+}
+
+MRT_D v3 chain_total(const Chain *ch) {
+    int last = kLevels - 1;
+    bool with_emit = true;
+    if (ch->ended_on_light) {
+        const uint32_t m = ch->ldmask;
+        if (m) { last = __ffs(m) - 1; with_emit = false; }
+    }
+    v3 t = mk3(0.0f, 0.0f, 0.0f);
+    for (int k = 0; k <= last; ++k) { t = t + mk3(ch->sum[k][0], ch->sum[k][1], ch->sum[k][2]); }
+    if (with_emit) { t = t + mk3(ch->emit[0], ch->emit[1], ch->emit[2]); }
+    return t;
+}
+
+// child chains created while shading `level` (pool range [counts[10+level-1], counts[10+level])) fold into their parents
+__global__ void k_wf_finalize_level(Queues Q, int level) {
+    const uint32_t begin = level == 0 ? Q.counts[0] : Q.counts[10 + level - 1], end = Q.counts[10 + level];
+    for (uint32_t i = begin + blockIdx.x * blockDim.x + threadIdx.x; i < end; i += gridDim.x * blockDim.x) {
+        const Chain *ch = Q.chains + i;
+        const v3 t = chain_total(ch);
+        Chain *p = Q.chains + ch->parent;
+        const int dz = ch->parent_depth - 1;
+        if (t.x != 0.0f) { atomicAdd(&p->sum[dz][0], t.x); }
+        if (t.y != 0.0f) { atomicAdd(&p->sum[dz][1], t.y); }
+        if (t.z != 0.0f) { atomicAdd(&p->sum[dz][2], t.z); }
+    }
+}
+
+// camera paths -> pixels (Renderer.cpp:149-157)
+__global__ void k_wf_resolve_roots(Queues Q, int avg_n, FrameTargets tg) {
+    const uint32_t n = min(Q.counts[0], Q.cap_rays);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const Chain *ch = Q.chains + i;
+        const v3 rgb = chain_total(ch);
+        const int pix = ch->parent_depth;
+        if (tg.bitmap != nullptr) { tg.bitmap[pix] = incremental_avg(rgb, tg.bitmap[pix], avg_n); }
+        if (tg.accum != nullptr) {
+            float4 a = tg.accum[pix];
+            a.x += static_cast<float>(f2u_x86(rgb.x * 255.0f)); a.y += static_cast<float>(f2u_x86(rgb.y * 255.0f));
+            a.z += static_cast<float>(f2u_x86(rgb.z * 255.0f)); a.w += 1.0f;
+            tg.accum[pix] = a;
+        }
+    }
+}
+
+// ---- host side -----------------------------------------------------------------------------------------------------
+namespace {
+template <typename T> cudaError_t wf_alloc(Wavefront *w, T **p, size_t count) {
+    void *v = nullptr;
+    cudaError_t e = cudaMalloc(&v, (count ? count : 1) * sizeof(T));
+    if (e == cudaSuccess) { w->allocs.push_back(v); *p = static_cast<T *>(v); }
+    return e;
+}
+enum WfClass { WF_OTHER = 0, WF_EXTEND = 1, WF_SHADE = 2, WF_SHADOW = 3 };
+}  // namespace
+
+typedef Wavefront WavefrontHost;
+static WavefrontHost *host_of(Wavefront *w) { return w; }
+
+#define WF_TRY(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { return e_; } } while (0)
+
+cudaError_t wavefront_create(int width, int height, Wavefront **out) {
+    Wavefront *w = new Wavefront;
+    *out = w;
+    w->width = width; w->height = height;
+    WavefrontHost *hst = w;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&hst->sm_count, cudaDevAttrMultiProcessorCount, dev);
+    const size_t P = static_cast<size_t>(width) * height;
+    Queues &q = w->q;
+    q.cap_rays = static_cast<uint32_t>(std::min<size_t>(2 * P + 1024, 0x0ffffff0u));
+    q.cap_shadow = q.cap_rays;
+    q.cap_chains = static_cast<uint32_t>(std::min<size_t>(3 * P + 1024, 0x0ffffff0u));
+    for (int b = 0; b < 2; ++b) {
+        WF_TRY(wf_alloc(w, &q.r0[b], q.cap_rays)); WF_TRY(wf_alloc(w, &q.r1[b], q.cap_rays));
+        WF_TRY(wf_alloc(w, &q.r2[b], q.cap_rays)); WF_TRY(wf_alloc(w, &q.r3[b], q.cap_rays));
+    }
+    WF_TRY(wf_alloc(w, &q.hit, q.cap_rays));
+    WF_TRY(wf_alloc(w, &q.s0, q.cap_shadow)); WF_TRY(wf_alloc(w, &q.s1, q.cap_shadow)); WF_TRY(wf_alloc(w, &q.s2, q.cap_shadow));
+    WF_TRY(wf_alloc(w, &q.chains, q.cap_chains));
+    WF_TRY(wf_alloc(w, &q.counts, 32));
+    return cudaSuccess;
+}
+
+void wavefront_destroy(Wavefront *w) {
+    if (!w) { return; }
+    WavefrontHost *hst = host_of(w);
+    for (cudaEvent_t e : hst->pool) { cudaEventDestroy(e); }
+    for (void *p : w->allocs) { cudaFree(p); }
+    delete w;
+}
+
+static cudaError_t wf_mark(WavefrontHost *hst, int cls, cudaStream_t st) {
+    if (hst->used == hst->pool.size()) {
+        if (hst->pool.size() >= 16384) { return cudaSuccess; }   // stop timing very long frames, keep rendering
+        cudaEvent_t e;
+        WF_TRY(cudaEventCreate(&e));
+        hst->pool.push_back(e);
+    }
+    cudaEvent_t e = hst->pool[hst->used++];
+    hst->marks.push_back(WfMark{e, cls});
+    return cudaEventRecord(e, st);
+}
+
+// to be called after the stream has been synchronised: adds the device time of every launch since the last call
+cudaError_t wavefront_collect_times(Wavefront *w, WavefrontTimes *t) {
+    WavefrontHost *hst = host_of(w);
+    for (size_t i = 1; i < hst->marks.size(); ++i) {
+        if (hst->marks[i].cls < 0) { continue; }   // a "begin" mark: nothing ran between it and its predecessor
+        float ms = 0.0f;
+        WF_TRY(cudaEventElapsedTime(&ms, hst->marks[i - 1].ev, hst->marks[i].ev));
+        switch (hst->marks[i].cls) {
+            case WF_EXTEND: t->extend_ms += ms; break;
+            case WF_SHADE: t->shade_ms += ms; break;
+            case WF_SHADOW: t->shadow_ms += ms; break;
+            default: t->other_ms += ms; break;
+        }
+    }
+    hst->marks.clear();
+    hst->used = 0;
+    return cudaSuccess;
+}
+
+cudaError_t wavefront_render_sample(Wavefront *w, const SceneDev &s, const CameraRec &cam, const RenderParams &rp, const int32_t *d_inv_tile,
+                                    int sample, int avg_n, FrameTargets tg, DeviceCounters *dc, bool sort_by_material,
+                                    WavefrontTimes *times, uint64_t *launches, cudaStream_t st) {
+    (void)sort_by_material; (void)times;
+    WavefrontHost *hst = host_of(w);
+    Queues &Q = w->q;
+    const int grid = hst->sm_count * 8;
+    WF_TRY(wf_mark(hst, -1, st));
+    WF_TRY(cudaMemsetAsync(Q.counts, 0, 32 * sizeof(uint32_t), st));
+    const int patches = ((rp.width + 7) / 8) * ((rp.height + 3) / 4);
+    k_wf_generate<<<(patches + kWfThreads / 32 - 1) / (kWfThreads / 32), kWfThreads, 0, st>>>(Q, cam, rp, s.pixel_table, d_inv_tile, sample, dc);
+    k_wf_begin_levels<<<1, 1, 0, st>>>(Q);
+    WF_TRY(wf_mark(hst, WF_OTHER, st));
+    *launches += 2;
+    for (int level = 0; level < kLevels; ++level) {
+        k_wf_extend<<<grid, kWfThreads, 0, st>>>(s, Q, level, dc);
+        WF_TRY(wf_mark(hst, WF_EXTEND, st));
+        k_wf_shade<<<grid, kWfThreads, 0, st>>>(s, rp, Q, level, dc);
+        WF_TRY(wf_mark(hst, WF_SHADE, st));
+        k_wf_shadow<<<grid, kWfThreads, 0, st>>>(s, Q, dc);
+        WF_TRY(wf_mark(hst, WF_SHADOW, st));
+        k_wf_end_level<<<1, 1, 0, st>>>(Q, level);
+        *launches += 4;
+    }
+    for (int level = kLevels - 1; level >= 0; --level) {
+        k_wf_finalize_level<<<grid, kWfThreads, 0, st>>>(Q, level);
+        *launches += 1;
+    }
+    k_wf_resolve_roots<<<grid, kWfThreads, 0, st>>>(Q, avg_n, tg);
+    *launches += 1;
+    WF_TRY(wf_mark(hst, WF_OTHER, st));
+    return cudaGetLastError();
+}
+
+}  // namespace mrt

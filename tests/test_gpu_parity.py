@@ -1,0 +1,165 @@
+"""GPU parity tests proper: the CUDA path, called through the C-ABI, against the compiled reference (oracle/_ref) on the
+same inputs. Bars: primitive id per primary ray >= 99.99 %, bitmap >= 99.9 % of channels within 1 LSB and
+RMSE <= 1.0 for the deterministic shaders. Integer helpers are bit exact."""
+import numpy as np
+import pytest
+
+from tests import helpers as H
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def mrt():
+    import mobileraytracer_b200 as m
+    if m.capi.lib().mrt_device_count() < 1:
+        pytest.fail("no CUDA device: the product path has no CPU fallback")
+    return m
+
+
+# ---- primitive level -------------------------------------------------------------------------------------------------
+def test_device_primitives_match_reference(mrt, ref):
+    import ctypes as C
+    capi = mrt.capi
+    L = capi.lib()
+    rng = np.random.default_rng(7)
+    n_hit = 0
+    for i in range(200):
+        A, B, Cc = (rng.uniform(-2, 2, 3).astype(np.float32) for _ in range(3))
+        tri = ref.triangle_build(A, B, Cc, 0)
+        # aim at a point inside (or slightly outside) the triangle
+        w = rng.uniform(-0.1, 1.1, 2)
+        target = A + w[0] * (B - A) * 0.5 + w[1] * (Cc - A) * 0.5
+        o = rng.uniform(-5, 5, 3).astype(np.float32)
+        d = (target - o).astype(np.float32)
+        d /= np.linalg.norm(d)
+        t_ref, out_ref = ref.triangle_intersect(tri, o, d)
+        t = C.c_float(0)
+        out = np.zeros(8, np.float32)
+        capi.check(L.mrt_test_triangle_intersect(capi.ptr(tri), capi.ptr(o), capi.ptr(d.astype(np.float32)), C.c_float(1e30), 0, C.byref(t), capi.ptr(out)))
+        assert np.float32(t.value) == np.float32(t_ref)
+        if t_ref < 1e29:
+            n_hit += 1
+            assert np.array_equal(out[:3], out_ref[:3]) and np.array_equal(out[5:], out_ref[5:])
+    assert n_hit > 50
+    for i in range(200):
+        c = rng.uniform(-2, 2, 3).astype(np.float32)
+        rad = np.float32(rng.uniform(0.1, 1.5))
+        o = rng.uniform(-5, 5, 3).astype(np.float32)
+        d = (c + rng.uniform(-1.2, 1.2, 3) * rad - o).astype(np.float32)
+        d /= np.linalg.norm(d)
+        t_ref, n_ref = ref.sphere_intersect(c, float(rad), o, d)
+        s = np.zeros(1, capi.SPHERE)
+        s["center"], s["sq_radius"] = c, rad * rad
+        t = C.c_float(0)
+        nrm = np.zeros(3, np.float32)
+        capi.check(L.mrt_test_sphere_intersect(capi.ptr(s), capi.ptr(o), capi.ptr(d), C.c_float(1e30), C.byref(t), capi.ptr(nrm)))
+        assert np.float32(t.value) == np.float32(t_ref)
+        if t_ref < 1e29:
+            assert np.array_equal(nrm, n_ref)
+    axes = np.eye(3, dtype=np.float32)
+    for i in range(100):
+        nrm = axes[i % 3] * (1 if i % 2 else -1)
+        p = rng.uniform(-2, 2, 3).astype(np.float32)
+        o = rng.uniform(-5, 5, 3).astype(np.float32)
+        d = rng.normal(size=3).astype(np.float32)
+        d /= np.linalg.norm(d)
+        t_ref = ref.plane_intersect(p, nrm, o, d)
+        pl = np.zeros(1, capi.PLANE)
+        pl["normal"], pl["point"] = nrm, p
+        t = C.c_float(0)
+        capi.check(L.mrt_test_plane_intersect(capi.ptr(pl), capi.ptr(o), capi.ptr(d), C.c_float(1e30), C.byref(t)))
+        assert np.float32(t.value) == np.float32(t_ref)
+        mn, mx = np.minimum(p, o * 0.3), np.maximum(p, o * 0.3) + np.float32(0.1)
+        hit = C.c_int32(0)
+        capi.check(L.mrt_test_aabb_intersect(capi.ptr(mn), capi.ptr(mx), capi.ptr(o), capi.ptr(d), C.byref(hit)))
+        assert bool(hit.value) == ref.aabb_intersect(mn, mx, o, d)
+    for i in range(300):
+        rgb = rng.uniform(-0.2, 3.0, 3).astype(np.float32)
+        avg = int(rng.integers(0, 2 ** 31 - 1)) | -16777216
+        avg = int(np.int32(np.uint32(avg & 0xFFFFFFFF)))
+        n = int(rng.integers(1, 200))
+        out = C.c_int32(0)
+        capi.check(L.mrt_test_incremental_avg(capi.ptr(rgb), avg, n, C.byref(out)))
+        assert out.value == ref.incremental_avg(rgb, avg, n)
+    h = np.zeros(4096, np.float32)
+    capi.check(L.mrt_test_halton(0, 4096, 2, capi.ptr(h)))
+    assert np.array_equal(h, np.array([ref.halton(i, 2) for i in range(4096)], np.float32))
+
+
+# ---- per-ray: camera rays, primitive ids, t ----------------------------------------------------------------------------
+@pytest.mark.parametrize("scene", [0, 1, 2, 3])
+def test_primary_rays_and_hits_match_reference(mrt, ref, scene):
+    w = h = 256
+    r = ref.RefRenderer(w, h, 3, scene)
+    g = H.gpu_from_ref(ref, r, scene, 3, w, h)
+    uvdd = H.primary_uvdd(w, h)
+    o_ref, d_ref = r.generate_rays(uvdd)
+    o, d = g.generateRays(uvdd)
+    assert np.array_equal(o, o_ref) and np.array_equal(d, d_ref), "camera rays must be bit identical"
+    a = r.trace(o_ref, d_ref)
+    b = g.traceRays(o, d)
+    same = (a["kind"] == b["kind"]) & (a["idx"] == b["idx"])
+    assert same.mean() >= 0.9999, "primitive id agreement %.6f" % same.mean()
+    assert np.array_equal(a["t"][same], b["t"][same]), "t must be bit identical on agreeing rays"
+    assert np.array_equal(a["normal"][same], b["normal"][same])
+    assert np.array_equal(a["mat"][same], b["mat"][same])
+    g.close()
+    r.close()
+
+
+@pytest.mark.parametrize("scene,shader", [(0, 1), (0, 0), (0, 3), (0, 4), (1, 1), (3, 1), (3, 0), (2, 3), (2, 4)])
+def test_frame_matches_reference_1spp(mrt, ref, scene, shader):
+    """BASELINE config 1 (scene 0, Whitted, 512x512, 1 spp) and its deterministic neighbours: bitmap equality."""
+    w = h = 512
+    r = ref.RefRenderer(w, h, shader, scene)
+    bm_ref, _ = r.render(threads=1)
+    rays_ref = r.casted_rays()
+    g = H.gpu_from_ref(ref, r, scene, shader, w, h)
+    bm = g.renderFrame()
+    c = H.compare_bitmaps(bm, bm_ref)
+    assert c["within1"] >= 0.999 and c["rmse"] <= 1.0, c
+    assert c["exact"] >= 0.999, c
+    if scene != 2:
+        assert g.getTotalCastedRays() == rays_ref, (g.getTotalCastedRays(), rays_ref)
+    g.close()
+    r.close()
+
+
+def test_builtin_scene_data_path_matches_reference(mrt, ref):
+    """The package's own scene builders (scene.py) + RayTrace entry, i.e. the drop-in path a front-end would use."""
+    for scene, shader in ((0, 1), (3, 1), (1, 4)):
+        bm_ref, _ = ref.raytrace(256, 256, shader, scene)
+        cfg = mrt.Config(width=256, height=256, shader=shader, sceneIndex=scene, printStdOut=False)
+        mrt.RayTrace(cfg)
+        c = H.compare_bitmaps(cfg.bitmap, bm_ref)
+        assert c["exact"] >= 0.999, (scene, shader, c)
+
+
+def test_config2_whitted_4spp_halton_jitter(mrt, ref):
+    """BASELINE config 2: scene 3, Whitted, 4 spp, 1024x1024, pixel jitter from the reference's shuffled Halton table,
+    accumulated with the reference's 8-bit running average."""
+    w = h = 1024
+    r = ref.RefRenderer(w, h, 1, 3, spp=4)
+    bm_ref, _ = r.render(threads=1)
+    g = H.gpu_from_ref(ref, r, 3, 1, w, h, spp=4)
+    bm = g.renderFrame()
+    c = H.compare_bitmaps(bm, bm_ref)
+    assert c["within1"] >= 0.999 and c["rmse"] <= 1.0 and c["exact"] >= 0.995, c
+    assert g.getTotalCastedRays() == r.casted_rays()
+    g.close()
+    r.close()
+
+
+def test_non_multiple_of_16_leaves_remainder_untouched(mrt, ref):
+    w, h = 200, 120   # 200 = 16*12 + 8, 120 = 16*7 + 8
+    r = ref.RefRenderer(w, h, 1, 0)
+    bm_ref = np.full(w * h, 0x11223344, np.int32)
+    bm_ref, _ = r.render(threads=1, bitmap=bm_ref)
+    g = H.gpu_from_ref(ref, r, 0, 1, w, h)
+    bm = g.renderFrame(np.full(w * h, 0x11223344, np.int32))
+    c = H.compare_bitmaps(bm, bm_ref)
+    assert c["exact"] >= 0.999, c
+    assert (bm[:, 192:] == 0x11223344).all() and (bm[112:, :] == 0x11223344).all()
+    g.close()
+    r.close()
