@@ -134,6 +134,17 @@ int upload_scene(mrt_handle *h, const mrt_scene_desc &sc) {
         s.s3 = make_float4(t.tB[1], t.tC[0], t.tC[1], matbits);
         if (t.material < 0 || t.material >= sc.n_materials) { return fail(h, MRT_ERR_INVALID, "triangle material index out of range"); }
     }
+    // root box of the reference's BVH<Triangle>: union of Triangle::getAABB (Triangle.cpp:116-123) over the scene triangles
+    float rmin[3] = {0, 0, 0}, rmax[3] = {0, 0, 0};
+    for (int64_t i = 0; i < nt; ++i) {
+        const mrt_triangle &t = sc.triangles[i];
+        for (int k = 0; k < 3; ++k) {
+            const float a = t.A[k], b = t.A[k] + t.AB[k], c = t.A[k] + t.AC[k];
+            const float lo = std::min(a, std::min(b, c)), hi = std::max(a, std::max(b, c));
+            rmin[k] = i == 0 ? lo : std::min(rmin[k], lo); rmax[k] = i == 0 ? hi : std::max(rmax[k], hi);
+        }
+    }
+    h->scene.tri_bmin = mk3(rmin[0], rmin[1], rmin[2]); h->scene.tri_bmax = mk3(rmax[0], rmax[1], rmax[2]);
     std::vector<LightRec> lights(static_cast<size_t>(nl > 0 ? nl : 1));
     for (int64_t i = 0; i < nl; ++i) {
         const mrt_light &l = sc.lights[i];
@@ -228,18 +239,26 @@ int upload_tables(mrt_handle *h, const mrt_render_desc &rd, const mrt_sampler_ta
     if (!p_sh) { make_halton_table(sh, kArraySize, rd.seed * 4u + 2u); p_sh = sh.data(); }
     const bool need_mt = rd.pixel_sampler == MRT_SAMPLER_STATIC_MT;
     if (need_mt && !p_smt) { make_mt_table(smt, kArraySize, rd.seed * 4u + 3u); p_smt = smt.data(); }
-    // inverse of the tile order: Renderer::renderScene maps table value -> tile roundf(value * 256) (Renderer.cpp:125)
-    std::vector<int32_t> inv(kNumberOfTiles, -1);
-    for (int k = 0; k < kNumberOfTiles; ++k) {
-        const int rb = static_cast<int>(::roundf(p_tile[k] * static_cast<float>(kNumberOfTiles)));
-        if (rb < 0 || rb >= kNumberOfTiles || inv[static_cast<size_t>(rb)] >= 0) { return fail(h, MRT_ERR_INVALID, "tile_order is not a permutation of k/256"); }
-        inv[static_cast<size_t>(rb)] = k;
+    // Renderer::renderScene's tile -> first pixel mapping (Renderer.cpp:125-133), integer for integer
+    std::vector<int2> origin(kNumberOfTiles, make_int2(0, 0));
+    {
+        const int w = rd.width, hgt = rd.height, bsx = h->rp.bsx, bsy = h->rp.bsy;
+        if (bsx > 0 && bsy > 0) {
+            const int domainSize = (w / bsx) * (hgt / bsy), resolution = w * hgt;
+            for (int k = 0; k < kNumberOfTiles; ++k) {
+                if (!(p_tile[k] >= 0.0f && p_tile[k] < 1.0f)) { return fail(h, MRT_ERR_INVALID, "tile_order values must lie in [0, 1)"); }
+                const int roundBlock = static_cast<int>(::roundf(p_tile[k] * static_cast<float>(domainSize)));
+                const int pixel = static_cast<int>((static_cast<long long>(roundBlock) * bsx) % resolution);
+                const int startY = ((pixel / w) * bsy) % hgt;
+                origin[static_cast<size_t>(k)] = make_int2(pixel % w, startY);   // startX = (pixel + y * w) % w
+            }
+        }
     }
     API_CUDA(h, h->d_tile.upload(p_tile, kNumberOfTiles * sizeof(float), st));
     API_CUDA(h, h->d_shader_table.upload(p_shader, kArraySize * sizeof(float), st));
     API_CUDA(h, h->d_static_halton.upload(p_sh, kArraySize * sizeof(float), st));
     if (need_mt) { API_CUDA(h, h->d_static_mt.upload(p_smt, kArraySize * sizeof(float), st)); }
-    API_CUDA(h, h->d_inv_tile.upload(inv.data(), inv.size() * sizeof(int32_t), st));
+    API_CUDA(h, h->d_inv_tile.upload(origin.data(), origin.size() * sizeof(int2), st));
     API_CUDA(h, cudaStreamSynchronize(st));
     SceneDev &s = h->scene;
     s.tile_order = h->d_tile.as<float>(); s.shader_table = h->d_shader_table.as<float>(); s.static_halton = h->d_static_halton.as<float>();
@@ -369,7 +388,7 @@ int render_samples(mrt_handle *h, int32_t *d_bitmap, float4 *d_accum, int sample
     if (h->rp.shader == MRT_SHADER_PATHTRACER) {
         for (int s = sample_begin, k = 0; s < spp; s += sample_stride, ++k) {
             if (h->stop.load()) { stopped = true; break; }
-            API_CUDA(h, wavefront_render_sample(h->wavefront, h->scene, h->camera, h->rp, h->d_inv_tile.as<int32_t>(), s, d_bitmap ? s + 1 : k + 1,
+            API_CUDA(h, wavefront_render_sample(h->wavefront, h->scene, h->camera, h->rp, h->d_inv_tile.as<int2>(), s, d_bitmap ? s + 1 : k + 1,
                                                 tg, h->d_counters.as<DeviceCounters>(), (h->flags & MRT_FLAG_SORT_BY_MATERIAL) != 0, &wt, &launches, st));
             h->sample.store(s + 1);
         }
@@ -382,7 +401,7 @@ int render_samples(mrt_handle *h, int32_t *d_bitmap, float4 *d_accum, int sample
                 h->sample.store(s - static_cast<int>(depth - 1) * sample_stride);
             }
             if (h->stop.load()) { stopped = true; break; }
-            API_CUDA(h, launch_render_sample(h->scene, h->camera, h->rp, h->d_inv_tile.as<int32_t>(), s, d_bitmap ? s + 1 : k + 1, tg,
+            API_CUDA(h, launch_render_sample(h->scene, h->camera, h->rp, h->d_inv_tile.as<int2>(), s, d_bitmap ? s + 1 : k + 1, tg,
                                              h->d_counters.as<DeviceCounters>(), st));
             ++launches;
             while (h->sample_events.size() < depth) { cudaEvent_t e; API_CUDA(h, cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); h->sample_events.push_back(e); }
@@ -435,14 +454,29 @@ int mrt_render_frame_device(mrt_handle *h, void *device_bitmap) {
 
 int mrt_render_frame(mrt_handle *h, int32_t *host_bitmap) {
     if (!h || !host_bitmap) { return fail(h, MRT_ERR_INVALID, "null argument"); }
+    API_CUDA(h, cudaSetDevice(h->device));
+    const size_t bytes = static_cast<size_t>(h->rp.width) * h->rp.height * sizeof(int32_t);
+    // a caller that hands in page-locked memory (cudaHostAlloc / cudaHostRegister) gets the DMA straight into it
+    cudaPointerAttributes attr {};
+    const bool pinned = cudaPointerGetAttributes(&attr, host_bitmap) == cudaSuccess && attr.type == cudaMemoryTypeHost;
+    cudaGetLastError();
+    // The frame is a read-modify-write of the caller's bitmap (Renderer.cpp:149-157). When the 16x16 tile grid covers the
+    // image exactly every pixel is overwritten at sample 1 (incrementalAvg weights the old value by n-1 = 0), so the old
+    // content is never needed; otherwise the pixels no tile reaches must keep the caller's content: upload it first.
+    const bool covers_all = h->rp.width % 16 == 0 && h->rp.height % 16 == 0;
+    if (!covers_all) {
+        if (pinned) { API_CUDA(h, cudaMemcpyAsync(h->d_bitmap.p, host_bitmap, bytes, cudaMemcpyHostToDevice, h->stream)); }
+        else { std::memcpy(h->h_pinned_bitmap, host_bitmap, bytes); API_CUDA(h, cudaMemcpyAsync(h->d_bitmap.p, h->h_pinned_bitmap, bytes, cudaMemcpyHostToDevice, h->stream)); }
+    }
     const int rc = render_to_device_bitmap(h, h->d_bitmap.as<int32_t>());
     if (rc != MRT_OK && rc != MRT_ERR_STOPPED) { return rc; }
-    // only the 16x16 tile grid is ever written (Renderer.cpp:33-34,125-135); remainder pixels keep the caller's content
-    const size_t w = static_cast<size_t>(h->rp.width), rw = static_cast<size_t>(h->rp.bsx) * 16, rh = static_cast<size_t>(h->rp.bsy) * 16;
-    if (rw > 0 && rh > 0) {
-        API_CUDA(h, cudaMemcpy2DAsync(h->h_pinned_bitmap, w * 4, h->d_bitmap.p, w * 4, rw * 4, rh, cudaMemcpyDeviceToHost, h->stream));
+    if (pinned) {
+        API_CUDA(h, cudaMemcpyAsync(host_bitmap, h->d_bitmap.p, bytes, cudaMemcpyDeviceToHost, h->stream));
         API_CUDA(h, cudaStreamSynchronize(h->stream));
-        for (size_t y = 0; y < rh; ++y) { std::memcpy(host_bitmap + y * w, h->h_pinned_bitmap + y * w, rw * 4); }
+    } else {
+        API_CUDA(h, cudaMemcpyAsync(h->h_pinned_bitmap, h->d_bitmap.p, bytes, cudaMemcpyDeviceToHost, h->stream));
+        API_CUDA(h, cudaStreamSynchronize(h->stream));
+        std::memcpy(host_bitmap, h->h_pinned_bitmap, bytes);
     }
     errno = 0;
     return rc;

@@ -16,19 +16,17 @@ MRT_D void flush_counters(const RayCounters &rc, DeviceCounters *dc) {
 }
 
 // Renderer::renderScene's pixel body (Renderer.cpp:130-157) for one sample of every pixel: jitter, camera ray,
-// Shader::rayTrace, incrementalAvg. A warp covers an 8x4 pixel patch so that its rays stay coherent.
+// Shader::rayTrace, incrementalAvg. A warp covers an 8x4 pixel patch of one tile so that its rays stay coherent.
 template <int SHADER>
-__global__ void __launch_bounds__(128) k_render_sample(SceneDev s, CameraRec cam, RenderParams rp, const int32_t *__restrict__ inv_tile,
+__global__ void __launch_bounds__(128) k_render_sample(SceneDev s, CameraRec cam, RenderParams rp, const int2 *__restrict__ tile_origin,
                                                        int sample, int avg_n, FrameTargets tg, DeviceCounters *dc) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int patches_x = (rp.width + 7) >> 3;
     const int patch = blockIdx.x * 4 + warp;
-    const int x = (patch % patches_x) * 8 + (lane & 7);
-    const int y = (patch / patches_x) * 4 + (lane >> 3);
     RayCounters rc = {0u, 0u, 0u};
     int overflow = 0;
     uint32_t q = 0;
-    if (x < rp.width && y < rp.height && pixel_sequence(rp, inv_tile, x, y, sample, q)) {
+    int x, y, pix;
+    if (tile_pixel(rp, tile_origin, patch, lane, sample, x, y, pix, q)) {
         const float invImgWidth = 1.0f / static_cast<float>(rp.width), invImgHeight = 1.0f / static_cast<float>(rp.height);
         const float pixelWidth = 0.5f / static_cast<float>(rp.width), pixelHeight = 0.5f / static_cast<float>(rp.height);
         const float u = static_cast<float>(x) * invImgWidth, v = static_cast<float>(y) * invImgHeight;
@@ -44,7 +42,6 @@ __global__ void __launch_bounds__(128) k_render_sample(SceneDev s, CameraRec cam
         rc.primary = 1u;
         DrawState ds = {q, 0u, rp.seed};
         const v3 rgb = ray_trace<SHADER>(s, rp, o, d, 1, ds, rc, &overflow);
-        const int pix = y * rp.width + x;
         if (tg.bitmap != nullptr) { tg.bitmap[pix] = incremental_avg(rgb, tg.bitmap[pix], avg_n); }
         if (tg.accum != nullptr) {
             float4 a = tg.accum[pix];
@@ -165,15 +162,16 @@ __global__ void k_test_halton(uint32_t first, int64_t n, uint32_t base, float *o
 }
 
 // ---- launchers ------------------------------------------------------------------------------------------------
-cudaError_t launch_render_sample(const SceneDev &s, const CameraRec &cam, const RenderParams &rp, const int32_t *d_inv_tile,
+cudaError_t launch_render_sample(const SceneDev &s, const CameraRec &cam, const RenderParams &rp, const int2 *d_tile_origin,
                                  int sample, int avg_n, FrameTargets tg, DeviceCounters *dc, cudaStream_t st) {
-    const int patches = ((rp.width + 7) / 8) * ((rp.height + 3) / 4);
+    const int patches = kNumberOfTiles * ((rp.bsx + 7) / 8) * ((rp.bsy + 3) / 4);
+    if (patches == 0) { return cudaSuccess; }
     const int blocks = (patches + 3) / 4;
     switch (rp.shader) {
-        case 1: k_render_sample<1><<<blocks, 128, 0, st>>>(s, cam, rp, d_inv_tile, sample, avg_n, tg, dc); break;
-        case 3: k_render_sample<3><<<blocks, 128, 0, st>>>(s, cam, rp, d_inv_tile, sample, avg_n, tg, dc); break;
-        case 4: k_render_sample<4><<<blocks, 128, 0, st>>>(s, cam, rp, d_inv_tile, sample, avg_n, tg, dc); break;
-        default: k_render_sample<0><<<blocks, 128, 0, st>>>(s, cam, rp, d_inv_tile, sample, avg_n, tg, dc); break;
+        case 1: k_render_sample<1><<<blocks, 128, 0, st>>>(s, cam, rp, d_tile_origin, sample, avg_n, tg, dc); break;
+        case 3: k_render_sample<3><<<blocks, 128, 0, st>>>(s, cam, rp, d_tile_origin, sample, avg_n, tg, dc); break;
+        case 4: k_render_sample<4><<<blocks, 128, 0, st>>>(s, cam, rp, d_tile_origin, sample, avg_n, tg, dc); break;
+        default: k_render_sample<0><<<blocks, 128, 0, st>>>(s, cam, rp, d_tile_origin, sample, avg_n, tg, dc); break;
     }
     return cudaGetLastError();
 }

@@ -16,7 +16,7 @@ struct DeviceCounters {   // device memory, zeroed per frame
 };
 
 // One sample of every pixel through the fused megakernel (deterministic shaders: NoShadows, Whitted, DepthMap, Diffuse).
-cudaError_t launch_render_sample(const SceneDev &s, const CameraRec &cam, const RenderParams &rp, const int32_t *d_inv_tile,
+cudaError_t launch_render_sample(const SceneDev &s, const CameraRec &cam, const RenderParams &rp, const int2 *d_tile_origin,
                                  int sample, int sample_number_for_avg, FrameTargets tg, DeviceCounters *d_counters, cudaStream_t st);
 cudaError_t launch_resolve(const float4 *accum, int32_t *bitmap, int n_pixels, cudaStream_t st);
 

@@ -26,20 +26,27 @@ MRT_D void generate_ray(const CameraRec &c, float u, float v, float du, float dv
     }
 }
 
-// Pixel -> (tile order position, jitter draw index): what a single-threaded Renderer::renderScene (Renderer.cpp:117-141)
-// would have consumed from the pixel sampler before reaching this pixel of this sample. inv_tile[rb] = position of
-// tile rb in the shuffled tile table (Renderer.cpp:189-197).
-struct PixelOrder {
-    int32_t inv_tile[kNumberOfTiles];
-};
-
-MRT_D bool pixel_sequence(const RenderParams &rp, const int32_t *inv_tile, int x, int y, int sample, uint32_t &q) {
-    if (x >= rp.bsx * 16 || y >= rp.bsy * 16) { return false; }   // remainder rows/cols are never rendered (F8)
-    const int tx = x / rp.bsx, ty = y / rp.bsy;
-    const int k = inv_tile[ty * 16 + tx];
-    const uint32_t perTile = static_cast<uint32_t>(rp.bsx * rp.bsy);
-    q = (static_cast<uint32_t>(sample) * kNumberOfTiles + static_cast<uint32_t>(k)) * perTile +
-        static_cast<uint32_t>((y - ty * rp.bsy) * rp.bsx + (x - tx * rp.bsx));
+// Renderer::renderScene's tile walk (Renderer.cpp:119-141) in tile space. tile_origin[k] = (startX, startY) of the k-th
+// tile of the shuffled tile table, computed on the host with the reference's own integer formula (mrt_api.cu), so odd
+// image sizes (where the reference's tiles wrap and overlap) map to the same pixels. A warp covers an 8x4 patch of one
+// tile. q = how many pixel-samples a single-threaded reference has rendered before this one: its pixel sampler has
+// handed out 2q draws by then (Renderer.cpp:137-138).
+MRT_D int tile_patches_x(const RenderParams &rp) { return (rp.bsx + 7) >> 3; }
+MRT_D int tile_patches_y(const RenderParams &rp) { return (rp.bsy + 3) >> 2; }
+MRT_D bool tile_pixel(const RenderParams &rp, const int2 *__restrict__ tile_origin, int patch, int lane, int sample,
+                      int &x, int &y, int &pix, uint32_t &q) {
+    const int ptx = tile_patches_x(rp), per_tile = ptx * tile_patches_y(rp);
+    const int k = patch / per_tile;
+    if (k >= kNumberOfTiles) { return false; }
+    const int r = patch - k * per_tile;
+    const int lx = (r % ptx) * 8 + (lane & 7), ly = (r / ptx) * 4 + (lane >> 3);
+    if (lx >= rp.bsx || ly >= rp.bsy) { return false; }
+    const int2 org = __ldg(tile_origin + k);
+    x = org.x + lx; y = org.y + ly;
+    pix = y * rp.width + x;                                   // Renderer.cpp:149: x may run past the row end, as in the reference
+    if (pix >= rp.width * rp.height) { return false; }        // the reference writes out of bounds here; this library does not
+    q = (static_cast<uint32_t>(sample) * kNumberOfTiles + static_cast<uint32_t>(k)) * static_cast<uint32_t>(rp.bsx * rp.bsy) +
+        static_cast<uint32_t>(ly * rp.bsx + lx);
     return true;
 }
 

@@ -180,6 +180,25 @@ MRT_D bool trace_bvh8(const SceneDev &s, v3 o, v3 d, int skipPrim, float &tbest,
     return false;
 }
 
+// The reference tests the root box of BVH<Triangle> with AABB::intersect before anything else (BVH.hpp:341-342); that
+// test is topology independent, and its NaN rule (an axis-parallel ray whose origin lies exactly on a box plane
+// misses, AABB.cpp:34-54) is visible in images of the orthographic scenes, so it is reproduced exactly here.
+MRT_D bool triangles_root_hit(const SceneDev &s, v3 o, v3 d) {
+    return s.n_triangles > 0 && aabb_intersect_exact(s.tri_bmin, s.tri_bmax, o, d);
+}
+
+// Shader::traceLights (Shader.cpp:166-171) as a plain loop: only used for the rare rays that fail the root test above.
+MRT_D void trace_lights_linear(const SceneDev &s, v3 o, v3 d, HitRec &h) {
+    for (int i = 0; i < s.n_lights; ++i) {
+        const LightRec &l = s.lights[i];
+        if (l.kind == 0) { continue; }
+        float t, u, v;
+        if (triangle_intersect(mk3(l.A[0], l.A[1], l.A[2]), mk3(l.AB[0], l.AB[1], l.AB[2]), mk3(l.AC[0], l.AC[1], l.AC[2]), o, d, t, u, v) && t < h.t) {
+            h.t = t; h.kind = HIT_LIGHT; h.idx = i; h.u = u; h.v = v;
+        }
+    }
+}
+
 // Shader::rayTrace's geometric part (Shader.cpp:86-111): planes, then spheres, then triangles share one running t;
 // area lights are tested last with the same strict "<" rule, which the tie rule of trace_bvh8 reproduces because
 // light primitive ids come after all scene triangles.
@@ -187,6 +206,11 @@ MRT_D void trace_closest(const SceneDev &s, v3 o, v3 d, int skipKind, int skipId
     h.t = kRayLengthMax; h.kind = HIT_NONE; h.idx = -1; h.u = 0.0f; h.v = 0.0f;
     trace_ref_bvh<0>(s, o, d, false, skipKind, skipIdx, h, overflow);
     trace_ref_bvh<1>(s, o, d, false, skipKind, skipIdx, h, overflow);
+    if (s.n_bvh_prims == 0) { return; }
+    if (!triangles_root_hit(s, o, d)) {
+        if (s.n_bvh_prims > s.n_triangles) { trace_lights_linear(s, o, d, h); }
+        return;
+    }
     int bestPrim = -1;
     trace_bvh8<false>(s, o, d, skipKind == HIT_TRIANGLE ? skipIdx : -1, h.t, bestPrim, h.u, h.v, overflow);
     if (bestPrim >= 0) {
@@ -201,6 +225,7 @@ MRT_D bool trace_shadow(const SceneDev &s, v3 o, v3 d, float distance, int skipK
     h.t = distance; h.kind = HIT_NONE; h.idx = -1; h.u = 0.0f; h.v = 0.0f;
     if (trace_ref_bvh<0>(s, o, d, true, skipKind, skipIdx, h, overflow)) { return true; }
     if (trace_ref_bvh<1>(s, o, d, true, skipKind, skipIdx, h, overflow)) { return true; }
+    if (!triangles_root_hit(s, o, d)) { return false; }
     int bestPrim = -1;
     return trace_bvh8<true>(s, o, d, skipKind == HIT_TRIANGLE ? skipIdx : -1, h.t, bestPrim, h.u, h.v, overflow);
 }

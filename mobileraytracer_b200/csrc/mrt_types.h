@@ -59,6 +59,7 @@ struct SceneDev {
     const TriShade *tri_shade; // caller order (scene triangles only)
     int32_t n_triangles;       // scene triangles (prim ids >= n_triangles are lights)
     int32_t n_bvh_prims;       // scene triangles + area-light triangles
+    v3 tri_bmin, tri_bmax;     // exact box of the scene triangles = the root box of the reference's BVH<Triangle>
     const RefNode *sphere_nodes; const SphereRec *spheres; int32_t n_spheres;
     const RefNode *plane_nodes;  const PlaneRec *planes;   int32_t n_planes;
     const MaterialRec *materials; int32_t n_materials;

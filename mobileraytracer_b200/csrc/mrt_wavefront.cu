@@ -68,15 +68,13 @@ MRT_D uint32_t queue_push(uint32_t *counter) {
 
 // ---- generate: Renderer::renderScene's jitter + Camera::generateRay (Renderer.cpp:130-141) ---------------------------
 __global__ void __launch_bounds__(kWfThreads) k_wf_generate(Queues Q, CameraRec cam, RenderParams rp, const float *__restrict__ pixel_table,
-                                                            const int32_t *__restrict__ inv_tile, int sample, DeviceCounters *dc) {
+                                                            const int2 *__restrict__ tile_origin, int sample, DeviceCounters *dc) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int patches_x = (rp.width + 7) >> 3;
     const int patch = blockIdx.x * (kWfThreads / 32) + warp;
-    const int x = (patch % patches_x) * 8 + (lane & 7);
-    const int y = (patch / patches_x) * 4 + (lane >> 3);
     uint32_t q = 0;
+    int x, y, pix;
     RayCounters rc = {0u, 0u, 0u};
-    if (x < rp.width && y < rp.height && pixel_sequence(rp, inv_tile, x, y, sample, q)) {
+    if (tile_pixel(rp, tile_origin, patch, lane, sample, x, y, pix, q)) {
         const float invImgWidth = 1.0f / static_cast<float>(rp.width), invImgHeight = 1.0f / static_cast<float>(rp.height);
         const float pixelWidth = 0.5f / static_cast<float>(rp.width), pixelHeight = 0.5f / static_cast<float>(rp.height);
         const float u = static_cast<float>(x) * invImgWidth, v = static_cast<float>(y) * invImgHeight;
@@ -90,7 +88,7 @@ __global__ void __launch_bounds__(kWfThreads) k_wf_generate(Queues Q, CameraRec 
         float4 *cz = reinterpret_cast<float4 *>(c);
 #pragma unroll
         for (int k = 0; k < 6; ++k) { cz[k] = make_float4(0.0f, 0.0f, 0.0f, 0.0f); }
-        c->parent = -1; c->parent_depth = y * rp.width + x;
+        c->parent = -1; c->parent_depth = pix;
         Q.r0[0][slot] = make_float4(o.x, o.y, o.z, d.x);
         Q.r1[0][slot] = make_float4(d.y, d.z, __uint_as_float(0u), __int_as_float(1));
         Q.r2[0][slot] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(slot));
@@ -383,7 +381,7 @@ cudaError_t wavefront_collect_times(Wavefront *w, WavefrontTimes *t) {
     return cudaSuccess;
 }
 
-cudaError_t wavefront_render_sample(Wavefront *w, const SceneDev &s, const CameraRec &cam, const RenderParams &rp, const int32_t *d_inv_tile,
+cudaError_t wavefront_render_sample(Wavefront *w, const SceneDev &s, const CameraRec &cam, const RenderParams &rp, const int2 *d_tile_origin,
                                     int sample, int avg_n, FrameTargets tg, DeviceCounters *dc, bool sort_by_material,
                                     WavefrontTimes *times, uint64_t *launches, cudaStream_t st) {
     (void)sort_by_material; (void)times;
@@ -392,8 +390,9 @@ cudaError_t wavefront_render_sample(Wavefront *w, const SceneDev &s, const Camer
     const int grid = hst->sm_count * 8;
     WF_TRY(wf_mark(hst, -1, st));
     WF_TRY(cudaMemsetAsync(Q.counts, 0, 32 * sizeof(uint32_t), st));
-    const int patches = ((rp.width + 7) / 8) * ((rp.height + 3) / 4);
-    k_wf_generate<<<(patches + kWfThreads / 32 - 1) / (kWfThreads / 32), kWfThreads, 0, st>>>(Q, cam, rp, s.pixel_table, d_inv_tile, sample, dc);
+    const int patches = kNumberOfTiles * ((rp.bsx + 7) / 8) * ((rp.bsy + 3) / 4);
+    if (patches == 0) { return cudaSuccess; }
+    k_wf_generate<<<(patches + kWfThreads / 32 - 1) / (kWfThreads / 32), kWfThreads, 0, st>>>(Q, cam, rp, s.pixel_table, d_tile_origin, sample, dc);
     k_wf_begin_levels<<<1, 1, 0, st>>>(Q);
     WF_TRY(wf_mark(hst, WF_OTHER, st));
     *launches += 2;

@@ -12,7 +12,7 @@ struct WavefrontTimes { double extend_ms = 0, shadow_ms = 0, shade_ms = 0, other
 cudaError_t wavefront_create(int width, int height, Wavefront **out);
 void wavefront_destroy(Wavefront *w);
 // One sample of every pixel. avg_n = the sample number used by the integer running average (bitmap target).
-cudaError_t wavefront_render_sample(Wavefront *w, const SceneDev &s, const CameraRec &cam, const RenderParams &rp, const int32_t *d_inv_tile,
+cudaError_t wavefront_render_sample(Wavefront *w, const SceneDev &s, const CameraRec &cam, const RenderParams &rp, const int2 *d_tile_origin,
                                     int sample, int avg_n, FrameTargets tg, DeviceCounters *d_counters, bool sort_by_material,
                                     WavefrontTimes *times, uint64_t *launches, cudaStream_t st);
 
