@@ -114,6 +114,9 @@ typedef struct mrt_stats {
     double extend_ms, shadow_ms, shade_ms, other_ms; /* last frame, device time per kernel class */
     uint64_t rays_primary, rays_shadow, rays_secondary; /* last frame; their sum is the reference's "Casted rays" (MobileRT/Ray.cpp:11,26) */
     uint64_t launches;          /* kernels launched by the last frame */
+    uint64_t extend_launches, shadow_launches, shade_launches; /* wavefront path tracer: launches per kernel class, last frame */
+    uint64_t rays_extend_traced, rays_shadow_traced; /* wavefront: rays the extend / shadow kernels actually traversed
+                                                        (a depth-7 ray is constructed and counted but never traced) */
     uint64_t bvh_nodes, bvh_bytes, scene_bytes;
     int64_t  n_primitives;      /* JNI rtInitialize's return value (JNI_layer.cpp:676-680) */
 } mrt_stats;
@@ -143,6 +146,12 @@ int mrt_resolve_device(mrt_handle *h, const void *device_accum_rgba32f, void *de
 
 /* Replaces: the camera_ member the front-ends rebuild between frames (JNI_layer.cpp:164; C_wrapper.cpp:76-141). */
 int mrt_set_camera(mrt_handle *h, const mrt_camera_desc *camera);
+
+/* Makes every later call on this handle enqueue its kernels and copies on the caller's CUDA stream (a cudaStream_t passed
+ * as void*; NULL restores the handle's own stream), so that a host runtime that owns streams and events (the JNI layer's
+ * render thread has none; a PyTorch / NCCL host does) can order and time the frame with its own events. Calls stay
+ * blocking: they synchronise that stream before returning. */
+int mrt_set_stream(mrt_handle *h, void *cuda_stream);
 
 /* Replaces: Renderer::stopRender (Renderer.cpp:93-99), Renderer::getSample (:176-178),
  * Renderer::getTotalCastedRays (:204-207). Thread-safe; may be called while mrt_render_frame runs. */

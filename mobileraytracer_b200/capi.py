@@ -52,7 +52,8 @@ class Stats(C.Structure):
     _fields_ = [("build_ms", C.c_double), ("upload_ms", C.c_double), ("frame_ms", C.c_double), ("extend_ms", C.c_double),
                 ("shadow_ms", C.c_double), ("shade_ms", C.c_double), ("other_ms", C.c_double),
                 ("rays_primary", C.c_uint64), ("rays_shadow", C.c_uint64), ("rays_secondary", C.c_uint64),
-                ("launches", C.c_uint64), ("bvh_nodes", C.c_uint64), ("bvh_bytes", C.c_uint64), ("scene_bytes", C.c_uint64),
+                ("launches", C.c_uint64), ("extend_launches", C.c_uint64), ("shadow_launches", C.c_uint64),
+                ("shade_launches", C.c_uint64), ("rays_extend_traced", C.c_uint64), ("rays_shadow_traced", C.c_uint64), ("bvh_nodes", C.c_uint64), ("bvh_bytes", C.c_uint64), ("scene_bytes", C.c_uint64),
                 ("n_primitives", C.c_int64)]
 
     def as_dict(self):
@@ -61,7 +62,7 @@ class Stats(C.Structure):
 
 # every symbol include/mobilert_b200.h declares
 SYMBOLS = ["mrt_create", "mrt_destroy", "mrt_render_frame", "mrt_render_frame_device", "mrt_render_accumulate_device",
-           "mrt_resolve_device", "mrt_set_camera", "mrt_stop", "mrt_get_sample", "mrt_get_total_rays", "mrt_get_stats",
+           "mrt_resolve_device", "mrt_set_camera", "mrt_set_stream", "mrt_stop", "mrt_get_sample", "mrt_get_total_rays", "mrt_get_stats",
            "mrt_last_error", "mrt_trace_rays", "mrt_generate_rays", "mrt_shade_rays", "mrt_test_triangle_intersect",
            "mrt_test_sphere_intersect", "mrt_test_plane_intersect", "mrt_test_aabb_intersect", "mrt_test_incremental_avg",
            "mrt_test_halton", "mrt_device_count", "mrt_version"]
@@ -92,6 +93,7 @@ def lib():
         L.mrt_render_accumulate_device.argtypes = [vp, vp, i32, i32]
         L.mrt_resolve_device.argtypes = [vp, vp, vp]
         L.mrt_set_camera.argtypes = [vp, C.POINTER(CameraDesc)]
+        L.mrt_set_stream.argtypes = [vp, vp]
         L.mrt_stop.argtypes = [vp]
         L.mrt_get_sample.argtypes = [vp, C.POINTER(i32)]
         L.mrt_get_total_rays.argtypes = [vp, C.POINTER(C.c_uint64)]

@@ -38,7 +38,8 @@ struct DevMem {
 
 struct mrt_handle {
     int device = 0;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;       // stream in use (own_stream unless mrt_set_stream installed the caller's)
+    cudaStream_t own_stream = nullptr;
     cudaEvent_t ev0 = nullptr, ev1 = nullptr;
     std::vector<cudaEvent_t> sample_events;
     SceneDev scene {};
@@ -293,7 +294,7 @@ void mrt_destroy(mrt_handle *h) {
     if (h->ev0) { cudaEventDestroy(h->ev0); }
     if (h->ev1) { cudaEventDestroy(h->ev1); }
     if (h->h_pinned_bitmap) { cudaFreeHost(h->h_pinned_bitmap); }
-    cudaStream_t st = h->stream;
+    cudaStream_t st = h->own_stream;
     delete h;   // DevMem destructors free the device arrays
     if (st) { cudaStreamDestroy(st); }
     errno = 0;
@@ -317,7 +318,7 @@ int mrt_create(const mrt_scene_desc *scene, const mrt_camera_desc *camera, const
     do {
         if (render->device >= 0) { h->device = render->device; } else { cudaGetDevice(&h->device); }
         cudaError_t e = cudaSetDevice(h->device);
-        if (e == cudaSuccess) { e = cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking); }
+        if (e == cudaSuccess) { e = cudaStreamCreateWithFlags(&h->own_stream, cudaStreamNonBlocking); h->stream = h->own_stream; }
         if (e == cudaSuccess) { e = cudaEventCreate(&h->ev0); }
         if (e == cudaSuccess) { e = cudaEventCreate(&h->ev1); }
         if (e != cudaSuccess) { rc = cuda_fail(h, e, "device setup"); break; }
@@ -351,6 +352,15 @@ int mrt_set_camera(mrt_handle *h, const mrt_camera_desc *camera) {
     if (!h || !camera) { return fail(h, MRT_ERR_INVALID, "null argument"); }
     std::lock_guard<std::mutex> lock(h->mutex);
     h->camera = make_camera(*camera);
+    errno = 0;
+    return MRT_OK;
+}
+
+int mrt_set_stream(mrt_handle *h, void *cuda_stream) {
+    if (!h) { return MRT_ERR_INVALID; }
+    std::lock_guard<std::mutex> lock(h->mutex);
+    cudaStreamSynchronize(h->stream);
+    h->stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : h->own_stream;
     errno = 0;
     return MRT_OK;
 }
@@ -421,6 +431,9 @@ int render_samples(mrt_handle *h, int32_t *d_bitmap, float4 *d_accum, int sample
         h->stats.extend_ms = wt.extend_ms; h->stats.shadow_ms = wt.shadow_ms; h->stats.shade_ms = wt.shade_ms; h->stats.other_ms = wt.other_ms;
         h->stats.rays_primary = hc.rays_primary; h->stats.rays_shadow = hc.rays_shadow; h->stats.rays_secondary = hc.rays_secondary;
         h->stats.launches = launches;
+        h->stats.rays_extend_traced = hc.extend_traced; h->stats.rays_shadow_traced = hc.shadow_traced;
+        const uint64_t per_class = h->rp.shader == MRT_SHADER_PATHTRACER ? launches / 33u * 6u : 0u;   // 33 launches per sample, of which 6 levels x (extend, shade, shadow)
+        h->stats.extend_launches = per_class; h->stats.shade_launches = per_class; h->stats.shadow_launches = per_class;
     }
     h->total_rays.store(hc.rays_primary + hc.rays_shadow + hc.rays_secondary);
     if (!stopped) { h->sample.store(spp); }

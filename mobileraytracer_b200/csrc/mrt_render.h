@@ -11,6 +11,7 @@ struct FrameTargets {
 
 struct DeviceCounters {   // device memory, zeroed per frame
     unsigned long long rays_primary, rays_shadow, rays_secondary;
+    unsigned long long extend_traced, shadow_traced;   // wavefront: queue sizes the traversal kernels consumed
     int overflow;
     int pad;
 };

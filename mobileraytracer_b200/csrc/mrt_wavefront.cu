@@ -253,7 +253,9 @@ __global__ void __launch_bounds__(kWfThreads) k_wf_shadow(SceneDev s, Queues Q, 
     if (overflow) { dc->overflow = 1; }
 }
 
-__global__ void k_wf_end_level(Queues Q, int level) {
+__global__ void k_wf_end_level(Queues Q, int level, DeviceCounters *dc) {
+    dc->extend_traced += min(Q.counts[level], Q.cap_rays);
+    dc->shadow_traced += min(Q.counts[8], Q.cap_shadow);
     Q.counts[8] = 0u;                         // shadow queue consumed
     Q.counts[10 + level] = min(Q.counts[9], Q.cap_chains);   // chain pool size after this level
 }
@@ -403,7 +405,7 @@ cudaError_t wavefront_render_sample(Wavefront *w, const SceneDev &s, const Camer
         WF_TRY(wf_mark(hst, WF_SHADE, st));
         k_wf_shadow<<<grid, kWfThreads, 0, st>>>(s, Q, dc);
         WF_TRY(wf_mark(hst, WF_SHADOW, st));
-        k_wf_end_level<<<1, 1, 0, st>>>(Q, level);
+        k_wf_end_level<<<1, 1, 0, st>>>(Q, level, dc);
         *launches += 4;
     }
     for (int level = kLevels - 1; level >= 0; --level) {

@@ -120,6 +120,10 @@ class Renderer:
         cd = camera.desc()
         capi.check(capi.lib().mrt_set_camera(self._h, C.byref(cd)), self._h)
 
+    def setStream(self, cuda_stream):
+        """Run this renderer's kernels on the caller's CUDA stream (an integer cudaStream_t, e.g. torch's `cuda_stream`)."""
+        capi.check(capi.lib().mrt_set_stream(self._h, C.c_void_p(cuda_stream)), self._h)
+
     def stats(self):
         st = capi.Stats()
         capi.lib().mrt_get_stats(self._h, C.byref(st))

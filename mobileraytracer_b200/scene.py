@@ -27,6 +27,14 @@ def _normalize(a):
     return (a * inv).astype(f32)
 
 
+def normalize_rows(a):
+    """glm::normalize over the rows of an (n, 3) float32 array, in glm's operation order."""
+    a = np.ascontiguousarray(a, f32)
+    d = ((a[:, 0] * a[:, 0] + a[:, 1] * a[:, 1]).astype(f32) + a[:, 2] * a[:, 2]).astype(f32)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        return (a * (f32(1.0) / np.sqrt(d, dtype=f32))[:, None]).astype(f32)
+
+
 def make_triangle(A, B, Cc, material=-1, normals=None, texcoords=None):
     """Triangle::Builder(pointA, pointB, pointC)[.withNormals][.withTexCoords].withMaterialIndex().build()"""
     A, B, Cc = _v(A), _v(B), _v(Cc)
@@ -37,7 +45,8 @@ def make_triangle(A, B, Cc, material=-1, normals=None, texcoords=None):
     if normals is None:
         n = _normalize(_cross(t["AC"], t["AB"]))
         normals = (n, n, n)
-    t["nA"], t["nB"], t["nC"] = _v(normals[0]), _v(normals[1]), _v(normals[2])
+    # the Triangle ctor normalises whatever the builder holds once more (Triangle.cpp:18-20)
+    t["nA"], t["nB"], t["nC"] = _normalize(_v(normals[0])), _normalize(_v(normals[1])), _normalize(_v(normals[2]))
     tc = texcoords if texcoords is not None else ((-1, -1), (-1, -1), (-1, -1))
     t["tA"], t["tB"], t["tC"] = _v(tc[0]), _v(tc[1]), _v(tc[2])
     t["material"] = material

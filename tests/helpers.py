@@ -60,3 +60,14 @@ def compare_bitmaps(gpu, ref):
     d = np.abs(unpack(gpu) - unpack(ref))
     return {"exact": float((d == 0).all(axis=-1).mean()), "within1": float((d <= 1).mean()), "max": int(d.max()),
             "rmse": float(np.sqrt((d.astype(np.float64) ** 2).mean()))}
+
+
+def resolve_reference(accum):
+    """numpy statement of mrt_resolve_device (mrt_render.cu k_resolve) for checking the multi-GPU reduce + resolve."""
+    a = np.asarray(accum, np.float32).reshape(-1, 4)
+    out = np.zeros(len(a), np.uint32)
+    ok = a[:, 3] > 0
+    q = np.zeros((len(a), 3), np.uint32)
+    q[ok] = np.minimum((a[ok, :3] / a[ok, 3:4]).astype(np.float32).astype(np.uint32), 255)
+    out[ok] = 0xFF000000 | (q[ok, 2] << 16) | (q[ok, 1] << 8) | q[ok, 0]
+    return out.view(np.int32)
