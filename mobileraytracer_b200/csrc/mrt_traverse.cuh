@@ -78,113 +78,214 @@ MRT_D bool trace_ref_bvh(const SceneDev &s, v3 o, v3 d, bool shadow, int skipKin
 }
 
 // ---- compressed 8-wide BVH ----------------------------------------------------------------------------------
-MRT_D float u8f(uint32_t word, int byte) { return static_cast<float>((word >> (8 * byte)) & 0xffu); }
+// Traversal state of one ray, advanced in steps so that the same code serves the per-thread callers (megakernel, tests)
+// and the persistent wavefront kernels that refill idle lanes between steps (mrt_wavefront.cu).
+// Instruction budget (ncu, profiles/): the node test is issue bound, split between the ALU pipe (PRMT, FMNMX, FSETP)
+// and the FMA pipe (FADD, FFMA); the 8-bit plane coordinates are turned into floats with PRMT + a magic-number FADD
+// instead of I2F (I2F.U8 runs on the quarter-rate XU pipe and was the top stall), and everything is branch free per child.
+struct Trav8 {
+    v3 o, d;
+    float idx, idy, idz;       // approximate reciprocals (slab tests are widened below, so 1 ulp does not matter)
+    uint32_t oct, octinv4;     // direction octant; (7 - oct) replicated into four bytes
+    int skipPrim;
+    float tbest; int bestPrim; float bu, bv;
+    uint2 ngroup, tgroup;      // x = base index, y = pending bits (node group: inner hits in 31..24, imask in 7..0)
+    int sp;
+#ifdef MRT_TRAVERSAL_STATS
+    uint32_t n_nodes, n_tris;  // diagnostic build only (libmobilert_b200_stats.so): node visits / triangle tests of this ray
+#endif
+    uint2 stack[kStack8];
+};
 
-// ANY: stop at the first hit with t < h.t (shadow rays; area-light triangles are not occluders, Shader.cpp:132-158).
-// skipPrim: primitive id the ray leaves (Triangle.cpp:64), or -1.  bestPrim: in/out, -1 when the current best hit
-// is not a BVH8 primitive.
+#ifdef MRT_TRAVERSAL_STATS
+__device__ unsigned long long g_stat_nodes, g_stat_tris, g_stat_rays;
+#define MRT_STAT(x) x
+#else
+#define MRT_STAT(x)
+#endif
+
+MRT_D float rcp_robust(float d) {
+    // a zero component becomes a huge finite slope so that slabs stay well defined
+    const float big = 1.0e20f;
+    return fabsf(d) > 1.0e-20f ? __frcp_rn(d) : (d < 0.0f ? -big : big);
+}
+
+MRT_D void trav8_init(Trav8 &t, v3 o, v3 d, int skipPrim, float tbest) {
+    t.o = o; t.d = d;
+    t.idx = rcp_robust(d.x); t.idy = rcp_robust(d.y); t.idz = rcp_robust(d.z);
+    t.oct = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
+    t.octinv4 = (7u - t.oct) * 0x01010101u;
+    t.skipPrim = skipPrim;
+    t.tbest = tbest; t.bestPrim = -1; t.bu = 0.0f; t.bv = 0.0f;
+    t.ngroup = make_uint2(0u, 0x80000000u);   // the root
+    t.tgroup = make_uint2(0u, 0u);
+    t.sp = 0;
+    MRT_STAT(t.n_nodes = 0u; t.n_tris = 0u;)
+}
+
+// byte b of w -> float, via 0x4B0000bb = 2^23 + bb
+template <int B> MRT_D float u8_to_float(uint32_t w) {
+    return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7440u | B)) - 8388608.0f;
+}
+
+// Four children (bytes 0..3 of the quantised plane words) against the ray; returns their contribution to the hit mask.
+template <int B>
+MRT_D uint32_t child_hit(uint32_t nx, uint32_t ny, uint32_t nz, uint32_t fx, uint32_t fy, uint32_t fz, float ax, float ay, float az,
+                         float ox0, float oy0, float oz0, float ox1, float oy1, float oz1, float tbest, uint32_t bits4, uint32_t index4) {
+    const float t0x = __fmaf_rn(u8_to_float<B>(nx), ax, ox0), t0y = __fmaf_rn(u8_to_float<B>(ny), ay, oy0), t0z = __fmaf_rn(u8_to_float<B>(nz), az, oz0);
+    const float t1x = __fmaf_rn(u8_to_float<B>(fx), ax, ox1), t1y = __fmaf_rn(u8_to_float<B>(fy), ay, oy1), t1z = __fmaf_rn(u8_to_float<B>(fz), az, oz1);
+    const float tmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, 0.0f));
+    const float tmax = fminf(fminf(t1x, t1y), fminf(t1z, tbest));
+    const uint32_t bits = (bits4 >> (8 * B)) & 0xffu, index = (index4 >> (8 * B)) & 0x1fu;
+    return tmin <= tmax * 1.000001f ? bits << index : 0u;
+}
+
+// Visits the next pending inner node of t.ngroup: afterwards t.ngroup holds that node's hit children and
+// `tnew` the hit leaf triangles (the previous group, if it still has pending nodes, goes to the stack).
+MRT_D bool trav8_node_step(const SceneDev &s, Trav8 &t, uint2 &tnew, int *overflow) {
+    MRT_STAT(++t.n_nodes;)
+    const uint32_t bit = 31u - __clz(t.ngroup.y);
+    t.ngroup.y &= ~(1u << bit);
+    if (t.ngroup.y & 0xff000000u) {
+        if (t.sp >= kStack8) { *overflow = 1; return false; }
+        t.stack[t.sp++] = t.ngroup;
+    }
+    const uint32_t slot = (bit - 24u) ^ (t.octinv4 & 0xffu);
+    const uint32_t rel = __popc(t.ngroup.y & ((1u << slot) - 1u) & 0xffu);
+    const float4 *np = reinterpret_cast<const float4 *>(s.nodes) + 5ull * (t.ngroup.x + rel);
+    const float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+    // n0 = px py pz (ex ey ez imask) | n1 = child_base tri_base meta[0..3] meta[4..7]
+    // n2 = qlox[0..7] qloy[0..7] | n3 = qloz[0..7] qhix[0..7] | n4 = qhiy[0..7] qhiz[0..7]
+    const uint32_t e = __float_as_uint(n0.w);
+    const float ax = __uint_as_float((e & 0xffu) << 23) * t.idx, ay = __uint_as_float(((e >> 8) & 0xffu) << 23) * t.idy,
+                az = __uint_as_float(((e >> 16) & 0xffu) << 23) * t.idz;
+    const float ox = (n0.x - t.o.x) * t.idx, oy = (n0.y - t.o.y) * t.idy, oz = (n0.z - t.o.z) * t.idz;
+    // conservative slabs: the offsets are widened by their own rounding error (relative 1e-6), the final comparison
+    // by the rounding of the fused multiply-adds
+    const float sxo = 1.0e-6f * fabsf(ox), syo = 1.0e-6f * fabsf(oy), szo = 1.0e-6f * fabsf(oz);
+    const float ox0 = ox - sxo, ox1 = ox + sxo, oy0 = oy - syo, oy1 = oy + syo, oz0 = oz - szo, oz1 = oz + szo;
+    // near / far plane words per axis, chosen once per node by the ray octant
+    const bool fx_ = t.oct & 1u, fy_ = t.oct & 2u, fz_ = t.oct & 4u;
+    const uint32_t qlx0 = __float_as_uint(n2.x), qlx1 = __float_as_uint(n2.y), qly0 = __float_as_uint(n2.z), qly1 = __float_as_uint(n2.w);
+    const uint32_t qlz0 = __float_as_uint(n3.x), qlz1 = __float_as_uint(n3.y), qhx0 = __float_as_uint(n3.z), qhx1 = __float_as_uint(n3.w);
+    const uint32_t qhy0 = __float_as_uint(n4.x), qhy1 = __float_as_uint(n4.y), qhz0 = __float_as_uint(n4.z), qhz1 = __float_as_uint(n4.w);
+    const uint32_t nx0 = fx_ ? qhx0 : qlx0, nx1 = fx_ ? qhx1 : qlx1, fx0 = fx_ ? qlx0 : qhx0, fx1 = fx_ ? qlx1 : qhx1;
+    const uint32_t ny0 = fy_ ? qhy0 : qly0, ny1 = fy_ ? qhy1 : qly1, fy0 = fy_ ? qly0 : qhy0, fy1 = fy_ ? qly1 : qhy1;
+    const uint32_t nz0 = fz_ ? qhz0 : qlz0, nz1 = fz_ ? qhz1 : qlz1, fz0 = fz_ ? qlz0 : qhz0, fz1 = fz_ ? qlz1 : qhz1;
+    const uint32_t imask = e >> 24;
+    uint32_t hitmask = 0u;
+#pragma unroll
+    for (int w = 0; w < 2; ++w) {
+        const uint32_t meta4 = __float_as_uint(w == 0 ? n1.z : n1.w);
+        // per byte: inner children carry (1 << 5) | (24 + slot); their bit index is XORed with the inverse octant so that the
+        // highest pending bit is always the nearest child along the ray. Leaves carry (unary count << 5) | triangle offset.
+        const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
+        const uint32_t inner_mask4 = (is_inner4 >> 4) * 0xffu;
+        const uint32_t index4 = (meta4 ^ (t.octinv4 & inner_mask4)) & 0x1f1f1f1fu;
+        const uint32_t bits4 = (meta4 >> 5) & 0x07070707u;
+        const uint32_t nx = w == 0 ? nx0 : nx1, ny = w == 0 ? ny0 : ny1, nz = w == 0 ? nz0 : nz1;
+        const uint32_t fx = w == 0 ? fx0 : fx1, fy = w == 0 ? fy0 : fy1, fz = w == 0 ? fz0 : fz1;
+        hitmask |= child_hit<0>(nx, ny, nz, fx, fy, fz, ax, ay, az, ox0, oy0, oz0, ox1, oy1, oz1, t.tbest, bits4, index4);
+        hitmask |= child_hit<1>(nx, ny, nz, fx, fy, fz, ax, ay, az, ox0, oy0, oz0, ox1, oy1, oz1, t.tbest, bits4, index4);
+        hitmask |= child_hit<2>(nx, ny, nz, fx, fy, fz, ax, ay, az, ox0, oy0, oz0, ox1, oy1, oz1, t.tbest, bits4, index4);
+        hitmask |= child_hit<3>(nx, ny, nz, fx, fy, fz, ax, ay, az, ox0, oy0, oz0, ox1, oy1, oz1, t.tbest, bits4, index4);
+    }
+    t.ngroup.x = __float_as_uint(n1.x);
+    t.ngroup.y = (hitmask & 0xff000000u) | imask;
+    tnew.x = __float_as_uint(n1.y);
+    tnew.y = hitmask & 0x00ffffffu;
+    return true;
+}
+
+// Tests the next pending triangle of t.tgroup. Returns true when an ANY-hit ray found its occluder.
+// Triangle::intersect (Triangle.cpp:63-99) with a sound prefilter: the sign / magnitude tests below only reject what the
+// reference's own comparisons reject for certain; survivors run the reference's exact arithmetic (one IEEE division).
+template <bool ANY>
+MRT_D bool trav8_triangle_step(const SceneDev &s, Trav8 &t) {
+    const uint32_t i = __ffs(t.tgroup.y) - 1u;
+    t.tgroup.y &= t.tgroup.y - 1u;
+    const float4 *tp = reinterpret_cast<const float4 *>(s.tri_geom) + 3ull * (t.tgroup.x + i);
+    const float4 g0 = __ldg(tp), g1 = __ldg(tp + 1), g2 = __ldg(tp + 2);
+    const int prim = static_cast<int>(__float_as_uint(g2.y));
+    if (prim == t.skipPrim) { return false; }
+    if (ANY && prim >= s.n_triangles) { return false; }      // area lights do not occlude (Shader.cpp:132-158)
+    MRT_STAT(++t.n_tris;)
+    const v3 A = mk3(g0.x, g0.y, g0.z), AB = mk3(g0.w, g1.x, g1.y), AC = mk3(g1.z, g1.w, g2.x);
+    const v3 perpendicularVector = cross(t.d, AC);
+    const float det = dot(AB, perpendicularVector);
+    const float adet = fabsf(det);
+    if (adet < kEpsilon) { return false; }
+    const uint32_t sgn = __float_as_uint(det) & 0x80000000u;
+    const float hi = adet * 1.00001f;
+    const v3 vectorToCamera = t.o - A;
+    const float du = dot(vectorToCamera, perpendicularVector);
+    const float su = __uint_as_float(__float_as_uint(du) ^ sgn);
+    if (su < -1.0e-25f || su > hi) { return false; }
+    const v3 upPerpendicularVector = cross(vectorToCamera, AB);
+    const float dv = dot(t.d, upPerpendicularVector);
+    const float sv = __uint_as_float(__float_as_uint(dv) ^ sgn);
+    if (sv < -1.0e-25f || su + sv > hi) { return false; }
+    const float dt = dot(AC, upPerpendicularVector);
+    const float st = __uint_as_float(__float_as_uint(dt) ^ sgn);
+    if (st < -1.0e-25f || st > hi * fminf(t.tbest, 1.0e25f)) { return false; }
+    // exact path
+    const float inv = 1.0f / det;
+    const float u = inv * du;
+    if (u < 0.0f || u > 1.0f) { return false; }
+    const float v = inv * dv;
+    if (v < 0.0f || (u + v) > 1.0f) { return false; }
+    const float tt = inv * dt;
+    if (tt < kEpsilon) { return false; }
+    if (tt < t.tbest || (!ANY && tt == t.tbest && t.bestPrim >= 0 && prim < t.bestPrim)) {
+        t.tbest = tt; t.bestPrim = prim; t.bu = u; t.bv = v;
+        return ANY;
+    }
+    return false;
+}
+
+// One scheduling step for this lane: a node visit when inner children are pending, else the pending triangles.
+// Returns false when the ray is finished (t.tbest / t.bestPrim hold the result; ANY: occluded iff bestPrim >= 0).
+template <bool ANY>
+MRT_D bool trav8_step(const SceneDev &s, Trav8 &t, int *overflow) {
+    if (t.ngroup.y & 0xff000000u) {
+        uint2 tnew;
+        if (!trav8_node_step(s, t, tnew, overflow)) { return false; }
+        t.tgroup = tnew;
+    } else {
+        t.tgroup = t.ngroup;
+        t.ngroup = make_uint2(0u, 0u);
+    }
+    while (t.tgroup.y) {
+        if (trav8_triangle_step<ANY>(s, t)) { return false; }
+    }
+    if (!(t.ngroup.y & 0xff000000u)) {
+        if (t.sp == 0) { return false; }
+        t.ngroup = t.stack[--t.sp];
+    }
+    return true;
+}
+
+// ANY: stop at the first hit with t < tbest (shadow rays). skipPrim: primitive id the ray leaves (Triangle.cpp:64), or -1.
+// bestPrim: out, -1 when nothing nearer than the incoming tbest was found.
 template <bool ANY>
 MRT_D bool trace_bvh8(const SceneDev &s, v3 o, v3 d, int skipPrim, float &tbest, int &bestPrim, float &bu, float &bv, int *overflow) {
     if (s.n_bvh_prims == 0) { return false; }
-    // robust reciprocal: a zero component becomes a huge finite slope so that slabs stay well defined
-    const float big = 1.0e20f;
-    const float idx = fabsf(d.x) > 1.0e-20f ? 1.0f / d.x : (d.x < 0.0f ? -big : big);
-    const float idy = fabsf(d.y) > 1.0e-20f ? 1.0f / d.y : (d.y < 0.0f ? -big : big);
-    const float idz = fabsf(d.z) > 1.0e-20f ? 1.0f / d.z : (d.z < 0.0f ? -big : big);
-    const uint32_t oct = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
-    const uint32_t octinv = 7u - oct;
-
-    uint2 stack[kStack8];
-    int sp = 0;
-    uint2 ngroup = make_uint2(0u, 0x80000000u);
-    const float4 *nodes4 = reinterpret_cast<const float4 *>(s.nodes);
-    const float4 *tris4 = reinterpret_cast<const float4 *>(s.tri_geom);
-
-    while (true) {
-        uint2 tgroup = make_uint2(0u, 0u);
-        if (ngroup.y & 0xff000000u) {
-            const uint32_t bit = 31u - __clz(ngroup.y);
-            ngroup.y &= ~(1u << bit);
-            if (ngroup.y & 0xff000000u) {
-                if (sp >= kStack8) { *overflow = 1; return false; }
-                stack[sp++] = ngroup;
-            }
-            const uint32_t slot = (bit - 24u) ^ octinv;
-            const uint32_t rel = __popc(ngroup.y & ((1u << slot) - 1u) & 0xffu);
-            const float4 *np = nodes4 + 5ull * (ngroup.x + rel);
-            const float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
-            // n0 = px py pz (ex ey ez imask) | n1 = child_base tri_base meta[0..3] meta[4..7]
-            // n2 = qlox[0..7] qloy[0..7] | n3 = qloz[0..7] qhix[0..7] | n4 = qhiy[0..7] qhiz[0..7]
-            const uint32_t e = __float_as_uint(n0.w);
-            const float sx = __uint_as_float((e & 0xffu) << 23), sy = __uint_as_float(((e >> 8) & 0xffu) << 23), sz = __uint_as_float(((e >> 16) & 0xffu) << 23);
-            const uint32_t imask = e >> 24;
-            const float ax = sx * idx, ay = sy * idy, az = sz * idz;
-            const float ox = (n0.x - o.x) * idx, oy = (n0.y - o.y) * idy, oz = (n0.z - o.z) * idz;
-            // conservative slabs: the offsets are widened by their own rounding error (relative 1e-6), the final
-            // comparison by the rounding of the fused multiply-add itself
-            const float sxo = 1.0e-6f * fabsf(ox), syo = 1.0e-6f * fabsf(oy), szo = 1.0e-6f * fabsf(oz);
-            const float ox0 = ox - sxo, ox1 = ox + sxo, oy0 = oy - syo, oy1 = oy + syo, oz0 = oz - szo, oz1 = oz + szo;
-            const uint32_t meta[2] = {__float_as_uint(n1.z), __float_as_uint(n1.w)};
-            const uint32_t qlx[2] = {__float_as_uint(n2.x), __float_as_uint(n2.y)}, qly[2] = {__float_as_uint(n2.z), __float_as_uint(n2.w)};
-            const uint32_t qlz[2] = {__float_as_uint(n3.x), __float_as_uint(n3.y)}, qhx[2] = {__float_as_uint(n3.z), __float_as_uint(n3.w)};
-            const uint32_t qhy[2] = {__float_as_uint(n4.x), __float_as_uint(n4.y)}, qhz[2] = {__float_as_uint(n4.z), __float_as_uint(n4.w)};
-            uint32_t hitmask = 0u;
-#pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                const int w = c >> 2, b = c & 3;
-                const uint32_t m = (meta[w] >> (8 * b)) & 0xffu;
-                if (m == 0u) { continue; }
-                const float lx = u8f(qlx[w], b), hx = u8f(qhx[w], b);
-                const float ly = u8f(qly[w], b), hy = u8f(qhy[w], b);
-                const float lz = u8f(qlz[w], b), hz = u8f(qhz[w], b);
-                const float t0x = __fmaf_rn(oct & 1u ? hx : lx, ax, ox0), t1x = __fmaf_rn(oct & 1u ? lx : hx, ax, ox1);
-                const float t0y = __fmaf_rn(oct & 2u ? hy : ly, ay, oy0), t1y = __fmaf_rn(oct & 2u ? ly : hy, ay, oy1);
-                const float t0z = __fmaf_rn(oct & 4u ? hz : lz, az, oz0), t1z = __fmaf_rn(oct & 4u ? lz : hz, az, oz1);
-                const float tmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, 0.0f));
-                const float tmax = fminf(fminf(t1x, t1y), fminf(t1z, tbest));
-                if (tmin <= tmax * 1.000001f) {
-                    const uint32_t inner = (m & 0x18u) == 0x18u ? 1u : 0u;   // low 5 bits >= 24
-                    const uint32_t bitIndex = inner ? (24u + (static_cast<uint32_t>(c) ^ octinv)) : (m & 0x1fu);
-                    hitmask |= (inner ? 1u : (m >> 5)) << bitIndex;
-                }
-            }
-            ngroup.x = __float_as_uint(n1.x);
-            ngroup.y = (hitmask & 0xff000000u) | imask;
-            tgroup.x = __float_as_uint(n1.y);
-            tgroup.y = hitmask & 0x00ffffffu;
-        } else {
-            tgroup = ngroup;
-            ngroup = make_uint2(0u, 0u);
-        }
-        while (tgroup.y) {
-            const uint32_t i = __ffs(tgroup.y) - 1u;
-            tgroup.y &= tgroup.y - 1u;
-            const float4 *tp = tris4 + 3ull * (tgroup.x + i);
-            const float4 g0 = __ldg(tp), g1 = __ldg(tp + 1), g2 = __ldg(tp + 2);
-            const int prim = static_cast<int>(__float_as_uint(g2.y));
-            if (prim == skipPrim) { continue; }
-            if (ANY && prim >= s.n_triangles) { continue; }
-            float t, u, v;
-            if (triangle_intersect(mk3(g0.x, g0.y, g0.z), mk3(g0.w, g1.x, g1.y), mk3(g1.z, g1.w, g2.x), o, d, t, u, v)) {
-                if (t < tbest || (!ANY && t == tbest && bestPrim >= 0 && prim < bestPrim)) {
-                    tbest = t; bestPrim = prim; bu = u; bv = v;
-                    if (ANY) { return true; }
-                }
-            }
-        }
-        if (!(ngroup.y & 0xff000000u)) {
-            if (sp == 0) { break; }
-            ngroup = stack[--sp];
-        }
-    }
-    return false;
+    Trav8 t;
+    trav8_init(t, o, d, skipPrim, tbest);
+    while (trav8_step<ANY>(s, t, overflow)) { }
+    MRT_STAT(atomicAdd(&g_stat_nodes, t.n_nodes); atomicAdd(&g_stat_tris, t.n_tris); atomicAdd(&g_stat_rays, 1ull);)
+    if (t.bestPrim >= 0) { tbest = t.tbest; bestPrim = t.bestPrim; bu = t.bu; bv = t.bv; }
+    return ANY && t.bestPrim >= 0;
 }
 
 // The reference tests the root box of BVH<Triangle> with AABB::intersect before anything else (BVH.hpp:341-342); that
 // test is topology independent, and its NaN rule (an axis-parallel ray whose origin lies exactly on a box plane
 // misses, AABB.cpp:34-54) is visible in images of the orthographic scenes, so it is reproduced exactly here.
 MRT_D bool triangles_root_hit(const SceneDev &s, v3 o, v3 d) {
-    return s.n_triangles > 0 && aabb_intersect_exact(s.tri_bmin, s.tri_bmax, o, d);
+    if (s.n_triangles <= 0) { return false; }
+    // without a zero direction component the test has no NaN case and only rejects rays that cannot hit anything inside
+    if (d.x != 0.0f && d.y != 0.0f && d.z != 0.0f) { return true; }
+    return aabb_intersect_exact(s.tri_bmin, s.tri_bmax, o, d);
 }
 
 // Shader::traceLights (Shader.cpp:166-171) as a plain loop: only used for the rare rays that fail the root test above.
