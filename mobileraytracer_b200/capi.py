@@ -5,7 +5,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libmobilert_b200.so")
+LIB_PATH = os.environ.get("MRT_B200_LIB") or os.path.join(_HERE, "libmobilert_b200.so")   # MRT_B200_LIB: diagnostic builds only
 
 MRT_OK, MRT_ERR_INVALID, MRT_ERR_CUDA, MRT_ERR_OOM, MRT_ERR_STOPPED, MRT_ERR_OVERFLOW = range(6)
 SHADER_NOSHADOWS, SHADER_WHITTED, SHADER_PATHTRACER, SHADER_DEPTHMAP, SHADER_DIFFUSE = range(5)

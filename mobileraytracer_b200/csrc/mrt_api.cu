@@ -7,6 +7,7 @@
 #include "mrt_wavefront.h"
 #include <atomic>
 #include <cerrno>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <new>
@@ -213,7 +214,10 @@ int upload_scene(mrt_handle *h, const mrt_scene_desc &sc) {
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     h->stats.upload_ms = ms;
     // acceleration structure over triangles + light triangles, on the GPU
-    API_CUDA(h, build_bvh8(h->d_tris9.as<float>(), static_cast<int>(nprims), 1u, st, &h->bvh));
+    // binned-SAH hierarchy by default; MRT_B200_BVH=lbvh selects the Morton-order hierarchy (build-speed / quality experiments)
+    const char *bvh_env = std::getenv("MRT_B200_BVH");
+    const uint32_t build_flags = (bvh_env && std::strcmp(bvh_env, "lbvh") == 0) ? 0u : 1u;
+    API_CUDA(h, build_bvh8(h->d_tris9.as<float>(), static_cast<int>(nprims), build_flags, st, &h->bvh));
     h->stats.build_ms = h->bvh.build_ms;
     h->stats.bvh_nodes = h->bvh.n_nodes;
     h->stats.bvh_bytes = h->bvh.bytes();

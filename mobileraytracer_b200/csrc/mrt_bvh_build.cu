@@ -4,6 +4,7 @@
 //   k_prim_bounds -> k_morton -> radix sort (hist/scan/scatter x 8) -> k_hierarchy (Karras 2012) -> k_refit
 //   -> [k_top_* : binned-SAH rebuild of the upper tree over LBVH clusters] -> k_collapse8 (level-synchronous)
 #include "mrt_build.h"
+#include <algorithm>
 #include <cstdio>
 #include <vector>
 
@@ -235,6 +236,218 @@ __global__ void k_refit(const uint32_t *__restrict__ sorted, const float *__rest
 }
 
 // ---------------------------------------------------------------------------------------------------------
+// 5b. binned-SAH hierarchy (default). Top-down, level-synchronous, no physical partitioning: every primitive carries the
+//     id of the node it currently belongs to and a 64-bit root-to-leaf path key; per level
+//       k_sah_bin    each primitive adds its box to one of 16 bins per axis of its node (atomics on ordered ints)
+//       k_sah_split  each open node sweeps its 3 x 16 bins, picks the cheapest SAH plane, creates two children
+//                    (boxes and counts come straight from the bins)
+//       k_sah_assign each primitive moves to its child and widens that child's centroid bounds
+//     until every node holds one primitive. Sorting the primitives by path key then makes every subtree contiguous
+//     (left before right), which is all the 8-wide collapse needs. Replaces the reference's single-threaded
+//     10-bucket + full-sweep SAH build (BVH.hpp:160-283, 396-439); the topology differs, the hit results do not.
+// ---------------------------------------------------------------------------------------------------------
+constexpr int SAH_BINS = 16;
+constexpr int SAH_BIN_WORDS = 7;                      // ordered min xyz, ordered max xyz, count
+constexpr int SAH_NODE_WORDS = 3 * SAH_BINS * SAH_BIN_WORDS;
+constexpr int SAH_RANK_SPLIT_DEPTH = 36;              // from this depth on, halve by arrival order so that depth stays < 64
+
+struct SahState {
+    int *node_of;                 // [n] current node of each primitive
+    unsigned long long *path;     // [n] path key: bit (63 - depth) = went right at that depth
+    int *cb;                      // [2n-1][6] ordered centroid bounds of each node
+    int *split;                   // [2n-1] axis << 8 | bin (axis 3 = split by arrival rank)
+    int *depth;                   // [2n-1]
+    int *bins;                    // [capacity][SAH_NODE_WORDS]
+    int *rank;                    // [2n-1] arrival counters for rank splits
+    int *ctl;                     // [0] level begin, [1] level end, [2] node counter, [3] open nodes in the level
+};
+
+__device__ __forceinline__ int sah_bin_of(float c, float cmin, float cmax) {
+    const float ext = cmax - cmin;
+    if (!(ext > 0.0f)) { return 0; }
+    const int b = static_cast<int>((c - cmin) * (static_cast<float>(SAH_BINS) / ext));
+    return min(max(b, 0), SAH_BINS - 1);
+}
+
+__global__ void k_iota(uint32_t *v, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) { v[i] = static_cast<uint32_t>(i); }
+}
+
+__global__ void k_sah_init(int n, const float *__restrict__ plo, const float *__restrict__ phi, BinTree t, SahState st) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) { return; }
+    st.node_of[i] = 0;
+    st.path[i] = 0ull;
+    for (int k = 0; k < 3; ++k) {
+        const float lo = plo[3ll * i + k], hi = phi[3ll * i + k];
+        const float c = 0.5f * lo + 0.5f * hi;
+        atomicMin(&st.cb[k], f2ord(c)); atomicMax(&st.cb[3 + k], f2ord(c));
+        atomicMin(reinterpret_cast<int *>(&t.lo[k]), f2ord(lo)); atomicMax(reinterpret_cast<int *>(&t.hi[k]), f2ord(hi));
+    }
+}
+// root box was accumulated as ordered ints: turn it back into floats
+__global__ void k_sah_fix_root(int n, BinTree t, SahState st) {
+    for (int k = 0; k < 3; ++k) { t.lo[k] = ord2f(reinterpret_cast<int *>(t.lo)[k]); t.hi[k] = ord2f(reinterpret_cast<int *>(t.hi)[k]); }
+    t.count[0] = n; t.parent[0] = -1; st.depth[0] = 0;
+    st.ctl[0] = 0; st.ctl[1] = 1; st.ctl[2] = 1; st.ctl[3] = n > 1 ? 1 : 0;
+}
+
+__global__ void k_sah_clear_bins(SahState st) {
+    const long long words = static_cast<long long>(st.ctl[1] - st.ctl[0]) * SAH_NODE_WORDS;
+    for (long long j = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; j < words; j += static_cast<long long>(gridDim.x) * blockDim.x) {
+        const int w = static_cast<int>(j % SAH_BIN_WORDS);
+        st.bins[j] = w < 3 ? 0x7fffffff : (w < 6 ? static_cast<int>(0x80000000) : 0);
+    }
+}
+
+__global__ void k_sah_bin(int n, const float *__restrict__ plo, const float *__restrict__ phi, BinTree t, SahState st) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) { return; }
+    const int nd = st.node_of[i];
+    if (nd < st.ctl[0] || t.count[nd] <= 1) { return; }
+    float lo[3], hi[3];
+    for (int k = 0; k < 3; ++k) { lo[k] = plo[3ll * i + k]; hi[k] = phi[3ll * i + k]; }
+    int *nb = st.bins + static_cast<long long>(nd - st.ctl[0]) * SAH_NODE_WORDS;
+    for (int k = 0; k < 3; ++k) {
+        const float c = 0.5f * lo[k] + 0.5f * hi[k];
+        const int b = sah_bin_of(c, ord2f(st.cb[6ll * nd + k]), ord2f(st.cb[6ll * nd + 3 + k]));
+        int *w = nb + (k * SAH_BINS + b) * SAH_BIN_WORDS;
+        atomicMin(&w[0], f2ord(lo[0])); atomicMin(&w[1], f2ord(lo[1])); atomicMin(&w[2], f2ord(lo[2]));
+        atomicMax(&w[3], f2ord(hi[0])); atomicMax(&w[4], f2ord(hi[1])); atomicMax(&w[5], f2ord(hi[2]));
+        atomicAdd(&w[6], 1);
+    }
+}
+
+struct SahBox { float lo[3], hi[3]; };
+__device__ __forceinline__ void sah_box_reset(SahBox &b) { for (int k = 0; k < 3; ++k) { b.lo[k] = 3.0e38f; b.hi[k] = -3.0e38f; } }
+__device__ __forceinline__ void sah_box_add(SahBox &b, const int *w) {
+    for (int k = 0; k < 3; ++k) { b.lo[k] = fminf(b.lo[k], ord2f(w[k])); b.hi[k] = fmaxf(b.hi[k], ord2f(w[3 + k])); }
+}
+__device__ __forceinline__ float sah_box_area(const SahBox &b) {
+    const float dx = b.hi[0] - b.lo[0], dy = b.hi[1] - b.lo[1], dz = b.hi[2] - b.lo[2];
+    return dx * dy + dy * dz + dz * dx;
+}
+
+// one thread per open node of the level
+__global__ void k_sah_split(BinTree t, SahState st) {
+    const int begin = st.ctl[0], end = st.ctl[1];
+    for (int nd = begin + blockIdx.x * blockDim.x + threadIdx.x; nd < end; nd += gridDim.x * blockDim.x) {
+        const int cnt = t.count[nd];
+        if (cnt <= 1) { continue; }
+        const int *nb = st.bins + static_cast<long long>(nd - begin) * SAH_NODE_WORDS;
+        float best = 3.0e38f; int bestAxis = 3, bestBin = 0, bestLeft = 0;
+        if (st.depth[nd] < SAH_RANK_SPLIT_DEPTH) {
+            for (int k = 0; k < 3; ++k) {
+                float rightArea[SAH_BINS]; int rightCnt[SAH_BINS];
+                SahBox rb; sah_box_reset(rb);
+                int rc = 0;
+                for (int b = SAH_BINS - 1; b >= 1; --b) {
+                    const int *w = nb + (k * SAH_BINS + b) * SAH_BIN_WORDS;
+                    if (w[6] > 0) { sah_box_add(rb, w); rc += w[6]; }
+                    rightArea[b] = rc > 0 ? sah_box_area(rb) : 0.0f; rightCnt[b] = rc;
+                }
+                SahBox lb; sah_box_reset(lb);
+                int lc = 0;
+                for (int b = 0; b < SAH_BINS - 1; ++b) {       // plane between bin b and b + 1
+                    const int *w = nb + (k * SAH_BINS + b) * SAH_BIN_WORDS;
+                    if (w[6] > 0) { sah_box_add(lb, w); lc += w[6]; }
+                    const int rcn = rightCnt[b + 1];
+                    if (lc == 0 || rcn == 0) { continue; }
+                    const float cost = sah_box_area(lb) * static_cast<float>(lc) + rightArea[b + 1] * static_cast<float>(rcn);
+                    if (cost < best) { best = cost; bestAxis = k; bestBin = b; bestLeft = lc; }
+                }
+            }
+        }
+        const int left = atomicAdd(&st.ctl[2], 2), right = left + 1;
+        t.left[nd] = left; t.right[nd] = right;
+        t.parent[left] = nd; t.parent[right] = nd;
+        st.depth[left] = st.depth[nd] + 1; st.depth[right] = st.depth[nd] + 1;
+        st.split[nd] = (bestAxis << 8) | bestBin;
+        if (bestAxis == 3) { bestLeft = cnt / 2; }
+        t.count[left] = bestLeft; t.count[right] = cnt - bestLeft;
+        st.rank[nd] = 0;
+        SahBox lb, rb; sah_box_reset(lb); sah_box_reset(rb);
+        if (bestAxis < 3) {
+            for (int b = 0; b < SAH_BINS; ++b) {
+                const int *w = nb + (bestAxis * SAH_BINS + b) * SAH_BIN_WORDS;
+                if (w[6] > 0) { sah_box_add(b <= bestBin ? lb : rb, w); }
+            }
+            for (int k = 0; k < 3; ++k) { t.lo[3ll * left + k] = lb.lo[k]; t.hi[3ll * left + k] = lb.hi[k]; t.lo[3ll * right + k] = rb.lo[k]; t.hi[3ll * right + k] = rb.hi[k]; }
+        } else {
+            // rank split: the boxes are accumulated by k_sah_assign (as ordered ints, fixed up by k_sah_next_level)
+            for (int k = 0; k < 3; ++k) {
+                reinterpret_cast<int *>(t.lo)[3ll * left + k] = 0x7fffffff; reinterpret_cast<int *>(t.hi)[3ll * left + k] = static_cast<int>(0x80000000);
+                reinterpret_cast<int *>(t.lo)[3ll * right + k] = 0x7fffffff; reinterpret_cast<int *>(t.hi)[3ll * right + k] = static_cast<int>(0x80000000);
+            }
+        }
+        for (int c = left; c <= right; ++c) {
+            for (int k = 0; k < 3; ++k) { st.cb[6ll * c + k] = 0x7fffffff; st.cb[6ll * c + 3 + k] = static_cast<int>(0x80000000); }
+        }
+    }
+}
+
+__global__ void k_sah_assign(int n, const float *__restrict__ plo, const float *__restrict__ phi, BinTree t, SahState st) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) { return; }
+    const int nd = st.node_of[i];
+    if (nd < st.ctl[0] || t.count[nd] <= 1) { return; }
+    const int sp = st.split[nd], axis = sp >> 8, bin = sp & 0xff;
+    float c[3], lo[3], hi[3];
+    for (int k = 0; k < 3; ++k) { lo[k] = plo[3ll * i + k]; hi[k] = phi[3ll * i + k]; c[k] = 0.5f * lo[k] + 0.5f * hi[k]; }
+    bool goRight;
+    if (axis < 3) {
+        goRight = sah_bin_of(c[axis], ord2f(st.cb[6ll * nd + axis]), ord2f(st.cb[6ll * nd + 3 + axis])) > bin;
+    } else {
+        goRight = atomicAdd(&st.rank[nd], 1) >= t.count[t.left[nd]];
+    }
+    const int child = goRight ? t.right[nd] : t.left[nd];
+    st.node_of[i] = child;
+    if (goRight) { st.path[i] |= 1ull << (63 - st.depth[nd]); }
+    for (int k = 0; k < 3; ++k) { atomicMin(&st.cb[6ll * child + k], f2ord(c[k])); atomicMax(&st.cb[6ll * child + 3 + k], f2ord(c[k])); }
+    if (axis == 3) {
+        for (int k = 0; k < 3; ++k) {
+            atomicMin(reinterpret_cast<int *>(&t.lo[3ll * child + k]), f2ord(lo[k])); atomicMax(reinterpret_cast<int *>(&t.hi[3ll * child + k]), f2ord(hi[k]));
+        }
+    }
+}
+
+// advances the level window to the children just created; fixes up the boxes of rank-split children
+__global__ void k_sah_next_level(BinTree t, SahState st) {
+    __shared__ int open;
+    const int begin = st.ctl[1], end = st.ctl[2];
+    if (threadIdx.x == 0) { open = 0; }
+    __syncthreads();
+    int mine = 0;
+    for (int c = begin + threadIdx.x; c < end; c += blockDim.x) {
+        const int p = t.parent[c];
+        if ((st.split[p] >> 8) == 3) {
+            for (int k = 0; k < 3; ++k) { t.lo[3ll * c + k] = ord2f(reinterpret_cast<int *>(t.lo)[3ll * c + k]); t.hi[3ll * c + k] = ord2f(reinterpret_cast<int *>(t.hi)[3ll * c + k]); }
+        }
+        if (t.count[c] > 1) { ++mine; }
+    }
+    if (mine) { atomicAdd(&open, mine); }
+    __syncthreads();
+    if (threadIdx.x == 0) { st.ctl[0] = begin; st.ctl[1] = end; st.ctl[3] = open; }
+}
+
+// after the path-key sort: leaf node of sorted position j
+__global__ void k_sah_leaves(int n, const uint32_t *__restrict__ sorted, BinTree t, SahState st) {
+    const int j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) { return; }
+    const int leaf = st.node_of[sorted[j]];
+    t.first[leaf] = j;
+}
+// first primitive of every inner node = first of its leftmost leaf (subtrees are contiguous, left before right)
+__global__ void k_sah_first(int nodes, BinTree t) {
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= nodes || t.count[b] <= 1) { return; }
+    int c = b;
+    while (t.count[c] > 1) { c = t.left[c]; }
+    t.first[b] = t.first[c];
+}
+
+// ---------------------------------------------------------------------------------------------------------
 // 6. collapse to 8-wide + quantise + pack triangles. One thread per wide node, level by level.
 // ---------------------------------------------------------------------------------------------------------
 struct WorkItem { int bin; int wide; };
@@ -259,16 +472,15 @@ __global__ void k_collapse8(CollapseArgs a) {
     if (w >= a.n_in) { return; }
     const WorkItem item = a.in[w];
     const BinTree &t = a.t;
-    const int nint = a.n - 1;  // nodes >= nint are leaves
     int kids[8]; int nk = 0;
-    // a binary subtree with <= 3 primitives can live in one leaf slot
-    if (item.bin >= nint || t.count[item.bin] <= 3) { kids[nk++] = item.bin; }
+    // a binary subtree with <= 3 primitives can live in one leaf slot (leaves have count 1 in both hierarchies)
+    if (t.count[item.bin] <= 3) { kids[nk++] = item.bin; }
     else { kids[nk++] = t.left[item.bin]; kids[nk++] = t.right[item.bin]; }
     while (nk < 8) {
         int best = -1; float bestA = -1.0f;
         for (int k = 0; k < nk; ++k) {
             const int b = kids[k];
-            if (b >= nint) { continue; }
+            if (t.count[b] <= 1) { continue; }   // a single primitive cannot be opened
             const float A = box_area(&t.lo[3ll * b], &t.hi[3ll * b]);
             // prefer opening subtrees that would need their own wide node; ties by area
             const float key = (t.count[b] > 3 ? 1.0e30f : 0.0f) + A;
@@ -325,7 +537,7 @@ __global__ void k_collapse8(CollapseArgs a) {
         const int c = child_in_slot[s];
         if (c < 0) { continue; }
         const int b = kids[c];
-        if (b < nint && t.count[b] > 3) { imask |= 1u << s; ++ninner; } else { ntris += t.count[b]; }
+        if (t.count[b] > 3) { imask |= 1u << s; ++ninner; } else { ntris += t.count[b]; }
     }
     const uint32_t child_base = ninner ? atomicAdd(a.node_counter, static_cast<uint32_t>(ninner)) : 0u;
     const uint32_t tri_base = ntris ? atomicAdd(a.tri_counter, static_cast<uint32_t>(ntris)) : 0u;
@@ -399,7 +611,6 @@ void free_bvh8(Bvh8 *b) {
 }
 
 cudaError_t build_bvh8(const float *d_tris9, int n, uint32_t flags, cudaStream_t stream, Bvh8 *out) {
-    (void)flags;
     *out = Bvh8{};
     cudaEvent_t ev0, ev1;
     CUDA_TRY(cudaEventCreate(&ev0));
@@ -431,19 +642,8 @@ cudaError_t build_bvh8(const float *d_tris9, int n, uint32_t flags, cudaStream_t
         const int init[6] = {0x7fffffff, 0x7fffffff, 0x7fffffff, static_cast<int>(0x80000000), static_cast<int>(0x80000000), static_cast<int>(0x80000000)};
         CUDA_TRY(cudaMemcpyAsync(cb.p, init, sizeof(init), cudaMemcpyHostToDevice, stream));
     }
-    k_prim_bounds<<<nb, T, 0, stream>>>(d_tris9, n, plo.as<float>(), phi.as<float>(), cb.as<int>());
-    k_morton<<<nb, T, 0, stream>>>(plo.as<float>(), phi.as<float>(), n, cb.as<int>(), keys0.as<unsigned long long>(), vals0.as<uint32_t>());
     unsigned long long *ka = keys0.as<unsigned long long>(), *kb = keys1.as<unsigned long long>();
     uint32_t *va = vals0.as<uint32_t>(), *vb = vals1.as<uint32_t>();
-    for (int pass = 0; pass < 8; ++pass) {
-        const int shift = pass * 8;
-        k_rs_hist<<<rs_blocks, RS_THREADS, 0, stream>>>(ka, n, shift, hist.as<uint32_t>(), rs_blocks);
-        k_rs_scan<<<1, 1024, 0, stream>>>(hist.as<uint32_t>(), 256ll * rs_blocks);
-        k_rs_scatter<<<rs_blocks, RS_THREADS, 0, stream>>>(ka, va, kb, vb, n, shift, hist.as<uint32_t>(), rs_blocks);
-        unsigned long long *tk = ka; ka = kb; kb = tk;
-        uint32_t *tv = va; va = vb; vb = tv;
-    }
-    // ka/va now hold the sorted keys / primitive ids
     const int nn = 2 * n - 1;
     BinTree t;
     CUDA_TRY(tl.alloc(4ull * nn)); CUDA_TRY(tr.alloc(4ull * nn)); CUDA_TRY(tp.alloc(4ull * nn));
@@ -451,9 +651,66 @@ cudaError_t build_bvh8(const float *d_tris9, int n, uint32_t flags, cudaStream_t
     CUDA_TRY(tlo.alloc(12ull * nn)); CUDA_TRY(thi.alloc(12ull * nn)); CUDA_TRY(tflags.alloc(4ull * n));
     t.left = tl.as<int>(); t.right = tr.as<int>(); t.parent = tp.as<int>(); t.first = tf.as<int>(); t.count = tc.as<int>();
     t.lo = tlo.as<float>(); t.hi = thi.as<float>(); t.flags = tflags.as<int>();
-    CUDA_TRY(cudaMemsetAsync(t.flags, 0, 4ull * n, stream));
-    if (n > 1) { k_hierarchy<<<(n - 1 + T - 1) / T, T, 0, stream>>>(ka, n, t); }
-    k_refit<<<nb, T, 0, stream>>>(va, plo.as<float>(), phi.as<float>(), n, t);
+    DevBuf s_node, s_cb, s_split, s_depth, s_bins, s_rank, s_ctl;
+    const bool sah = (flags & 1u) != 0u && n > 1;
+    if (sah) {
+        SahState st;
+        CUDA_TRY(s_node.alloc(4ull * n)); CUDA_TRY(s_cb.alloc(24ull * nn)); CUDA_TRY(s_split.alloc(4ull * nn)); CUDA_TRY(s_depth.alloc(4ull * nn));
+        CUDA_TRY(s_rank.alloc(4ull * nn)); CUDA_TRY(s_ctl.alloc(16));
+        CUDA_TRY(s_bins.alloc(4ull * SAH_NODE_WORDS * static_cast<size_t>(n)));
+        st.node_of = s_node.as<int>(); st.path = ka; st.cb = s_cb.as<int>(); st.split = s_split.as<int>(); st.depth = s_depth.as<int>();
+        st.bins = s_bins.as<int>(); st.rank = s_rank.as<int>(); st.ctl = s_ctl.as<int>();
+        {
+            const int init[6] = {0x7fffffff, 0x7fffffff, 0x7fffffff, static_cast<int>(0x80000000), static_cast<int>(0x80000000), static_cast<int>(0x80000000)};
+            CUDA_TRY(cudaMemcpyAsync(st.cb, init, sizeof(init), cudaMemcpyHostToDevice, stream));
+            CUDA_TRY(cudaMemcpyAsync(t.lo, init, 12, cudaMemcpyHostToDevice, stream));
+            CUDA_TRY(cudaMemcpyAsync(t.hi, init + 3, 12, cudaMemcpyHostToDevice, stream));
+        }
+        k_prim_bounds<<<nb, T, 0, stream>>>(d_tris9, n, plo.as<float>(), phi.as<float>(), cb.as<int>());
+        k_sah_init<<<nb, T, 0, stream>>>(n, plo.as<float>(), phi.as<float>(), t, st);
+        k_sah_fix_root<<<1, 1, 0, stream>>>(n, t, st);
+        int ctl[4] = {0, 1, 1, 1};
+        for (int level = 0; level < 64; ++level) {
+            const int window = ctl[1] - ctl[0];
+            const int gridw = (window + 127) / 128;
+            k_sah_clear_bins<<<std::max(1, std::min(4096, window)), 256, 0, stream>>>(st);
+            k_sah_bin<<<nb, T, 0, stream>>>(n, plo.as<float>(), phi.as<float>(), t, st);
+            k_sah_split<<<gridw, 128, 0, stream>>>(t, st);
+            k_sah_assign<<<nb, T, 0, stream>>>(n, plo.as<float>(), phi.as<float>(), t, st);
+            k_sah_next_level<<<1, 1024, 0, stream>>>(t, st);
+            CUDA_TRY(cudaMemcpyAsync(ctl, st.ctl, sizeof(ctl), cudaMemcpyDeviceToHost, stream));
+            CUDA_TRY(cudaStreamSynchronize(stream));
+            if (ctl[3] == 0) { break; }
+        }
+        if (ctl[3] != 0) { return cudaErrorUnknown; }   // deeper than 64 levels: cannot happen with the rank-split rule
+        // path-key sort -> subtrees contiguous, left before right
+        k_iota<<<nb, T, 0, stream>>>(va, n);
+        for (int pass = 0; pass < 8; ++pass) {
+            const int shift = pass * 8;
+            k_rs_hist<<<rs_blocks, RS_THREADS, 0, stream>>>(ka, n, shift, hist.as<uint32_t>(), rs_blocks);
+            k_rs_scan<<<1, 1024, 0, stream>>>(hist.as<uint32_t>(), 256ll * rs_blocks);
+            k_rs_scatter<<<rs_blocks, RS_THREADS, 0, stream>>>(ka, va, kb, vb, n, shift, hist.as<uint32_t>(), rs_blocks);
+            unsigned long long *tk = ka; ka = kb; kb = tk;
+            uint32_t *tv = va; va = vb; vb = tv;
+        }
+        k_sah_leaves<<<nb, T, 0, stream>>>(n, va, t, st);
+        k_sah_first<<<(ctl[2] + T - 1) / T, T, 0, stream>>>(ctl[2], t);
+    } else {
+        k_prim_bounds<<<nb, T, 0, stream>>>(d_tris9, n, plo.as<float>(), phi.as<float>(), cb.as<int>());
+        k_morton<<<nb, T, 0, stream>>>(plo.as<float>(), phi.as<float>(), n, cb.as<int>(), ka, va);
+        for (int pass = 0; pass < 8; ++pass) {
+            const int shift = pass * 8;
+            k_rs_hist<<<rs_blocks, RS_THREADS, 0, stream>>>(ka, n, shift, hist.as<uint32_t>(), rs_blocks);
+            k_rs_scan<<<1, 1024, 0, stream>>>(hist.as<uint32_t>(), 256ll * rs_blocks);
+            k_rs_scatter<<<rs_blocks, RS_THREADS, 0, stream>>>(ka, va, kb, vb, n, shift, hist.as<uint32_t>(), rs_blocks);
+            unsigned long long *tk = ka; ka = kb; kb = tk;
+            uint32_t *tv = va; va = vb; vb = tv;
+        }
+        // ka/va now hold the sorted keys / primitive ids
+        CUDA_TRY(cudaMemsetAsync(t.flags, 0, 4ull * n, stream));
+        if (n > 1) { k_hierarchy<<<(n - 1 + T - 1) / T, T, 0, stream>>>(ka, n, t); }
+        k_refit<<<nb, T, 0, stream>>>(va, plo.as<float>(), phi.as<float>(), n, t);
+    }
     // collapse, level by level
     CUDA_TRY(misc.alloc(sizeof(uint32_t) * 8));
     uint32_t *d_node_counter = misc.as<uint32_t>(), *d_tri_counter = d_node_counter + 1, *d_nout = d_node_counter + 2;

@@ -98,7 +98,7 @@ struct Trav8 {
 };
 
 #ifdef MRT_TRAVERSAL_STATS
-__device__ unsigned long long g_stat_nodes, g_stat_tris, g_stat_rays;
+static __device__ unsigned long long g_stat_nodes, g_stat_tris, g_stat_rays;   // one copy per translation unit
 #define MRT_STAT(x) x
 #else
 #define MRT_STAT(x)
@@ -244,7 +244,11 @@ MRT_D bool trav8_triangle_step(const SceneDev &s, Trav8 &t) {
 }
 
 // One scheduling step for this lane: a node visit when inner children are pending, else the pending triangles.
+// Triangle postponing (Ylitie et al. 2017): a triangle test costs about a third of a node test but, per step, only a few
+// lanes of a warp have hit a leaf; when fewer than kPostponeLanes lanes are inside the triangle loop the group is parked
+// on the stack (a group with an empty inner byte) and retried later together with other lanes' groups.
 // Returns false when the ray is finished (t.tbest / t.bestPrim hold the result; ANY: occluded iff bestPrim >= 0).
+constexpr int kPostponeLanes = 7;
 template <bool ANY>
 MRT_D bool trav8_step(const SceneDev &s, Trav8 &t, int *overflow) {
     if (t.ngroup.y & 0xff000000u) {
@@ -256,6 +260,10 @@ MRT_D bool trav8_step(const SceneDev &s, Trav8 &t, int *overflow) {
         t.ngroup = make_uint2(0u, 0u);
     }
     while (t.tgroup.y) {
+        if (__popc(__activemask()) < kPostponeLanes && (t.ngroup.y & 0xff000000u) && t.sp < kStack8) {
+            t.stack[t.sp++] = t.tgroup;      // there is node work left for this lane: park the triangles
+            break;
+        }
         if (trav8_triangle_step<ANY>(s, t)) { return false; }
     }
     if (!(t.ngroup.y & 0xff000000u)) {

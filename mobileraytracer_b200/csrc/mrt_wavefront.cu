@@ -102,18 +102,73 @@ __global__ void __launch_bounds__(kWfThreads) k_wf_generate(Queues Q, CameraRec 
 // the chain pool starts right after the root chains
 __global__ void k_wf_begin_levels(Queues Q) { Q.counts[9] = Q.counts[0]; }
 
-// ---- extend: closest hit for every ray of the level ------------------------------------------------------------------
+// ---- extend / shadow: persistent traversal kernels --------------------------------------------------------------
+// One CTA of 4 warps per scheduling slot, resident for the whole launch. A lane that has finished its ray fetches the
+// next one from the level's work counter (one warp-aggregated atomic per refill), so the lanes of a warp stay busy although
+// their rays need very different numbers of steps; refills happen when fewer than kRefillLanes lanes still hold a ray.
+constexpr int kRefillLanes = 22;
+constexpr int kCounterExtend = 20, kCounterShadow = 21;   // Queues::counts slots used as work counters
+
+MRT_D uint32_t pack_hit(const HitRec &h) { return (static_cast<uint32_t>(h.kind) << 28) | (static_cast<uint32_t>(h.idx) & 0x0fffffffu); }
+
+// extend: closest hit for every ray of the level (Shader::rayTrace's geometric part, Shader.cpp:86-111)
 __global__ void __launch_bounds__(kWfThreads) k_wf_extend(SceneDev s, Queues Q, int level, DeviceCounters *dc) {
     const int b = level & 1;
     const uint32_t n = min(Q.counts[level], Q.cap_rays);
+    const int lane = threadIdx.x & 31;
     int overflow = 0;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const float4 a = Q.r0[b][i], c = Q.r1[b][i];
-        int sk, si;
-        unpack_skip(__float_as_uint(c.z), sk, si);
-        HitRec h;
-        trace_closest(s, mk3(a.x, a.y, a.z), mk3(a.w, c.x, c.y), sk, si, h, &overflow);
-        Q.hit[i] = make_float4(h.t, h.u, h.v, __uint_as_float((static_cast<uint32_t>(h.kind) << 28) | (static_cast<uint32_t>(h.idx) & 0x0fffffffu)));
+    bool has = false, exhausted = false;
+    uint32_t cur = 0;
+    HitRec h;
+    Trav8 t;
+    while (true) {
+        // refill the idle lanes
+        const uint32_t idle = __ballot_sync(0xffffffffu, !has);
+        if (!exhausted && __popc(idle) > 32 - kRefillLanes) {
+            uint32_t base = 0;
+            if (lane == 0) { base = atomicAdd(&Q.counts[kCounterExtend], static_cast<uint32_t>(__popc(idle))); }
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (base + __popc(idle) >= n) { exhausted = true; }
+            if (!has) {
+                cur = base + __popc(idle & ((1u << lane) - 1u));
+                if (cur < n) {
+                    const float4 a = Q.r0[b][cur], c = Q.r1[b][cur];
+                    const v3 o = mk3(a.x, a.y, a.z), d = mk3(a.w, c.x, c.y);
+                    int sk, si;
+                    unpack_skip(__float_as_uint(c.z), sk, si);
+                    h.t = kRayLengthMax; h.kind = HIT_NONE; h.idx = -1; h.u = 0.0f; h.v = 0.0f;
+                    trace_ref_bvh<0>(s, o, d, false, sk, si, h, &overflow);
+                    trace_ref_bvh<1>(s, o, d, false, sk, si, h, &overflow);
+                    if (s.n_bvh_prims > 0 && triangles_root_hit(s, o, d)) {
+                        trav8_init(t, o, d, sk == HIT_TRIANGLE ? si : -1, h.t);
+                        has = true;
+                    } else {
+                        if (s.n_bvh_prims > s.n_triangles) { trace_lights_linear(s, o, d, h); }
+                        Q.hit[cur] = make_float4(h.t, h.u, h.v, __uint_as_float(pack_hit(h)));
+                    }
+                }
+            }
+        }
+        if (__ballot_sync(0xffffffffu, has) == 0u) {
+            if (exhausted) { break; }
+            continue;
+        }
+        if (has) {
+            while (true) {
+                if (!trav8_step<false>(s, t, &overflow)) {
+                    if (t.bestPrim >= 0) {
+                        h.t = t.tbest; h.u = t.bu; h.v = t.bv;
+                        if (t.bestPrim < s.n_triangles) { h.kind = HIT_TRIANGLE; h.idx = t.bestPrim; }
+                        else { h.kind = HIT_LIGHT; h.idx = t.bestPrim - s.n_triangles; }
+                    }
+                    Q.hit[cur] = make_float4(h.t, h.u, h.v, __uint_as_float(pack_hit(h)));
+                    MRT_STAT(atomicAdd(&g_stat_nodes, t.n_nodes); atomicAdd(&g_stat_tris, t.n_tris); atomicAdd(&g_stat_rays, 1ull);)
+                    has = false;
+                    break;
+                }
+                if (!exhausted && __popc(__activemask()) < kRefillLanes) { break; }
+            }
+        }
     }
     if (overflow) { dc->overflow = 1; }
 }
@@ -234,21 +289,66 @@ __global__ void __launch_bounds__(kWfThreads) k_wf_shade(SceneDev s, RenderParam
     if (overflow) { dc->overflow = 1; }
 }
 
-// ---- shadow: any-hit; an unoccluded sample adds its share of Ld to the chain ---------------------------------------
+// ---- shadow: any-hit (Shader::shadowTrace, Shader.cpp:132-158); an unoccluded sample adds its share of Ld to the chain
+MRT_D void shadow_unoccluded(const Queues &Q, uint32_t i) {
+    const float4 cc = Q.s2[i];
+    const uint32_t tag = __float_as_uint(cc.w);
+    Chain *ch = Q.chains + (tag & 0x0fffffffu);
+    const uint32_t dz = (tag >> 28) & 7u;
+    atomicAdd(&ch->sum[dz][0], cc.x); atomicAdd(&ch->sum[dz][1], cc.y); atomicAdd(&ch->sum[dz][2], cc.z);
+    if (tag & 0x80000000u) { atomicOr(&ch->ldmask, 1u << dz); }
+}
+
 __global__ void __launch_bounds__(kWfThreads) k_wf_shadow(SceneDev s, Queues Q, DeviceCounters *dc) {
     const uint32_t n = min(Q.counts[8], Q.cap_shadow);
+    const int lane = threadIdx.x & 31;
     int overflow = 0;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const float4 a = Q.s0[i], c = Q.s1[i];
-        int sk, si;
-        unpack_skip(__float_as_uint(c.w), sk, si);
-        if (trace_shadow(s, mk3(a.x, a.y, a.z), mk3(a.w, c.x, c.y), c.z, sk, si, &overflow)) { continue; }
-        const float4 cc = Q.s2[i];
-        const uint32_t tag = __float_as_uint(cc.w);
-        Chain *ch = Q.chains + (tag & 0x0fffffffu);
-        const uint32_t dz = (tag >> 28) & 7u;
-        atomicAdd(&ch->sum[dz][0], cc.x); atomicAdd(&ch->sum[dz][1], cc.y); atomicAdd(&ch->sum[dz][2], cc.z);
-        if (tag & 0x80000000u) { atomicOr(&ch->ldmask, 1u << dz); }
+    bool has = false, exhausted = false;
+    uint32_t cur = 0;
+    Trav8 t;
+    while (true) {
+        const uint32_t idle = __ballot_sync(0xffffffffu, !has);
+        if (!exhausted && __popc(idle) > 32 - kRefillLanes) {
+            uint32_t base = 0;
+            if (lane == 0) { base = atomicAdd(&Q.counts[kCounterShadow], static_cast<uint32_t>(__popc(idle))); }
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (base + __popc(idle) >= n) { exhausted = true; }
+            if (!has) {
+                cur = base + __popc(idle & ((1u << lane) - 1u));
+                if (cur < n) {
+                    const float4 a = Q.s0[cur], c = Q.s1[cur];
+                    const v3 o = mk3(a.x, a.y, a.z), d = mk3(a.w, c.x, c.y);
+                    int sk, si;
+                    unpack_skip(__float_as_uint(c.w), sk, si);
+                    HitRec h;
+                    h.t = c.z; h.kind = HIT_NONE; h.idx = -1; h.u = 0.0f; h.v = 0.0f;
+                    const bool occluded = trace_ref_bvh<0>(s, o, d, true, sk, si, h, &overflow) || trace_ref_bvh<1>(s, o, d, true, sk, si, h, &overflow);
+                    if (!occluded) {
+                        if (s.n_bvh_prims > 0 && triangles_root_hit(s, o, d)) {
+                            trav8_init(t, o, d, sk == HIT_TRIANGLE ? si : -1, h.t);
+                            has = true;
+                        } else {
+                            shadow_unoccluded(Q, cur);
+                        }
+                    }
+                }
+            }
+        }
+        if (__ballot_sync(0xffffffffu, has) == 0u) {
+            if (exhausted) { break; }
+            continue;
+        }
+        if (has) {
+            while (true) {
+                if (!trav8_step<true>(s, t, &overflow)) {
+                    if (t.bestPrim < 0) { shadow_unoccluded(Q, cur); }
+                    MRT_STAT(atomicAdd(&g_stat_nodes, t.n_nodes); atomicAdd(&g_stat_tris, t.n_tris); atomicAdd(&g_stat_rays, 1ull);)
+                    has = false;
+                    break;
+                }
+                if (!exhausted && __popc(__activemask()) < kRefillLanes) { break; }
+            }
+        }
     }
     if (overflow) { dc->overflow = 1; }
 }
@@ -256,6 +356,7 @@ __global__ void __launch_bounds__(kWfThreads) k_wf_shadow(SceneDev s, Queues Q, 
 __global__ void k_wf_end_level(Queues Q, int level, DeviceCounters *dc) {
     dc->extend_traced += min(Q.counts[level], Q.cap_rays);
     dc->shadow_traced += min(Q.counts[8], Q.cap_shadow);
+    Q.counts[kCounterExtend] = 0u; Q.counts[kCounterShadow] = 0u;   // work counters of the persistent traversal kernels
     Q.counts[8] = 0u;                         // shadow queue consumed
     Q.counts[10 + level] = min(Q.counts[9], Q.cap_chains);   // chain pool size after this level
 }
@@ -419,3 +520,13 @@ cudaError_t wavefront_render_sample(Wavefront *w, const SceneDev &s, const Camer
 }
 
 }  // namespace mrt
+
+#ifdef MRT_TRAVERSAL_STATS
+// diagnostic library only: node visits / triangle tests / rays of the wavefront kernels since the last reset
+extern "C" int mrt_debug_traversal_stats(unsigned long long out[3], int reset) {
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(&out[0], mrt::g_stat_nodes, 8); cudaMemcpyFromSymbol(&out[1], mrt::g_stat_tris, 8); cudaMemcpyFromSymbol(&out[2], mrt::g_stat_rays, 8);
+    if (reset) { const unsigned long long z = 0; cudaMemcpyToSymbol(mrt::g_stat_nodes, &z, 8); cudaMemcpyToSymbol(mrt::g_stat_tris, &z, 8); cudaMemcpyToSymbol(mrt::g_stat_rays, &z, 8); }
+    return 0;
+}
+#endif
