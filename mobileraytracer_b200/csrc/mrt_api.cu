@@ -216,7 +216,9 @@ int upload_scene(mrt_handle *h, const mrt_scene_desc &sc) {
     // acceleration structure over triangles + light triangles, on the GPU
     // binned-SAH hierarchy by default; MRT_B200_BVH=lbvh selects the Morton-order hierarchy (build-speed / quality experiments)
     const char *bvh_env = std::getenv("MRT_B200_BVH");
-    const uint32_t build_flags = (bvh_env && std::strcmp(bvh_env, "lbvh") == 0) ? 0u : 1u;
+    const char *leaf_env = std::getenv("MRT_B200_LEAF");   // triangles per leaf slot, 1..7 (tuning experiments)
+    const uint32_t leaf = leaf_env ? static_cast<uint32_t>(std::atoi(leaf_env)) & 7u : 3u;
+    const uint32_t build_flags = ((bvh_env && std::strcmp(bvh_env, "lbvh") == 0) ? 0u : 1u) | (leaf << 8);
     API_CUDA(h, build_bvh8(h->d_tris9.as<float>(), static_cast<int>(nprims), build_flags, st, &h->bvh));
     h->stats.build_ms = h->bvh.build_ms;
     h->stats.bvh_nodes = h->bvh.n_nodes;
@@ -225,6 +227,11 @@ int upload_scene(mrt_handle *h, const mrt_scene_desc &sc) {
     h->stats.n_primitives = nt + sc.n_spheres + sc.n_planes;
     h->d_tris9.release();   // geometry now lives in the BVH8 leaf array
     SceneDev &s = h->scene;
+    {
+        const char *tp = std::getenv("MRT_B200_POSTPONE"), *tr = std::getenv("MRT_B200_REFILL");   // tuning experiments only
+        s.tune_postpone = tp ? std::atoi(tp) : 12;
+        s.tune_refill = tr ? std::atoi(tr) : 22;
+    }
     s.nodes = h->bvh.nodes; s.tri_geom = h->bvh.tri_geom; s.tri_shade = h->d_tri_shade.as<TriShade>();
     s.n_triangles = static_cast<int32_t>(nt); s.n_bvh_prims = static_cast<int32_t>(nprims);
     s.sphere_nodes = h->d_sphere_nodes.as<RefNode>(); s.spheres = h->d_spheres.as<SphereRec>(); s.n_spheres = static_cast<int32_t>(sc.n_spheres);

@@ -459,6 +459,7 @@ struct CollapseArgs {
     uint32_t *node_counter, *tri_counter;
     const WorkItem *in; int n_in; WorkItem *out; uint32_t *n_out;
     uint32_t max_nodes;
+    int max_leaf;                 // primitives per leaf slot, 1..7
     int *error;
 };
 
@@ -473,8 +474,9 @@ __global__ void k_collapse8(CollapseArgs a) {
     const WorkItem item = a.in[w];
     const BinTree &t = a.t;
     int kids[8]; int nk = 0;
-    // a binary subtree with <= 3 primitives can live in one leaf slot (leaves have count 1 in both hierarchies)
-    if (t.count[item.bin] <= 3) { kids[nk++] = item.bin; }
+    // a binary subtree with <= max_leaf primitives can live in one leaf slot (leaves have count 1 in both hierarchies)
+    const int ML = a.max_leaf;
+    if (t.count[item.bin] <= ML) { kids[nk++] = item.bin; }
     else { kids[nk++] = t.left[item.bin]; kids[nk++] = t.right[item.bin]; }
     while (nk < 8) {
         int best = -1; float bestA = -1.0f;
@@ -483,7 +485,7 @@ __global__ void k_collapse8(CollapseArgs a) {
             if (t.count[b] <= 1) { continue; }   // a single primitive cannot be opened
             const float A = box_area(&t.lo[3ll * b], &t.hi[3ll * b]);
             // prefer opening subtrees that would need their own wide node; ties by area
-            const float key = (t.count[b] > 3 ? 1.0e30f : 0.0f) + A;
+            const float key = (t.count[b] > ML ? 1.0e30f : 0.0f) + A;
             if (key > bestA) { bestA = key; best = k; }
         }
         if (best < 0) { break; }
@@ -532,12 +534,23 @@ __global__ void k_collapse8(CollapseArgs a) {
         slot_of[bc] = bs; child_in_slot[bs] = bc;
     }
     // count inner children / leaf triangles
+    // the node's triangle mask has 24 bits: while the leaf slots hold more than that, the fullest one becomes an inner child
+    bool force_inner[8] = {false, false, false, false, false, false, false, false};
+    while (true) {
+        int total = 0, big = -1, bigc = 1;
+        for (int c = 0; c < nk; ++c) {
+            const int cc = t.count[kids[c]];
+            if (cc <= ML && !force_inner[c]) { total += cc; if (cc > bigc) { bigc = cc; big = c; } }
+        }
+        if (total <= 24 || big < 0) { break; }
+        force_inner[big] = true;
+    }
     uint32_t imask = 0; int ninner = 0, ntris = 0;
     for (int s = 0; s < 8; ++s) {
         const int c = child_in_slot[s];
         if (c < 0) { continue; }
         const int b = kids[c];
-        if (t.count[b] > 3) { imask |= 1u << s; ++ninner; } else { ntris += t.count[b]; }
+        if (t.count[b] > ML || force_inner[c]) { imask |= 1u << s; ++ninner; } else { ntris += t.count[b]; }
     }
     const uint32_t child_base = ninner ? atomicAdd(a.node_counter, static_cast<uint32_t>(ninner)) : 0u;
     const uint32_t tri_base = ntris ? atomicAdd(a.tri_counter, static_cast<uint32_t>(ntris)) : 0u;
@@ -572,7 +585,7 @@ __global__ void k_collapse8(CollapseArgs a) {
                 ++inner_rank;
             } else {
                 const int cnt = t.count[b];
-                node.meta[s] = static_cast<uint8_t>((((1u << cnt) - 1u) << 5) | static_cast<uint32_t>(tri_off));
+                node.meta[s] = static_cast<uint8_t>((static_cast<uint32_t>(cnt) << 5) | static_cast<uint32_t>(tri_off));   // binary count 1..7
                 const int first = t.first[b];
                 for (int j = 0; j < cnt; ++j) {
                     const uint32_t prim = a.sorted[first + j];
@@ -728,6 +741,7 @@ cudaError_t build_bvh8(const float *d_tris9, int n, uint32_t flags, cudaStream_t
     CollapseArgs a;
     a.t = t; a.n = n; a.sorted = va; a.tris9 = d_tris9; a.nodes = out->nodes; a.tri_geom = out->tri_geom;
     a.node_counter = d_node_counter; a.tri_counter = d_tri_counter; a.n_out = d_nout; a.max_nodes = max_nodes; a.error = d_error;
+    a.max_leaf = static_cast<int>((flags >> 8) & 7u) ? static_cast<int>((flags >> 8) & 7u) : 3;
     WorkItem *qi = q0.as<WorkItem>(), *qo = q1.as<WorkItem>();
     uint32_t n_in = 1, levels = 0;
     while (n_in > 0) {

@@ -12,6 +12,7 @@ namespace mrt {
 
 constexpr int kStack8 = 40;     // node-group stack entries per thread (local memory, L1 resident)
 constexpr int kStackRef = 64;
+constexpr int kPend = 6;        // parked triangle groups per thread
 
 struct HitRec {
     float t;
@@ -90,7 +91,8 @@ struct Trav8 {
     int skipPrim;
     float tbest; int bestPrim; float bu, bv;
     uint2 ngroup, tgroup;      // x = base index, y = pending bits (node group: inner hits in 31..24, imask in 7..0)
-    int sp;
+    int sp, np;
+    uint2 pend[kPend];         // parked leaf groups (x = triangle base, y = pending triangle bits)
 #ifdef MRT_TRAVERSAL_STATS
     uint32_t n_nodes, n_tris;  // diagnostic build only (libmobilert_b200_stats.so): node visits / triangle tests of this ray
 #endif
@@ -119,7 +121,7 @@ MRT_D void trav8_init(Trav8 &t, v3 o, v3 d, int skipPrim, float tbest) {
     t.tbest = tbest; t.bestPrim = -1; t.bu = 0.0f; t.bv = 0.0f;
     t.ngroup = make_uint2(0u, 0x80000000u);   // the root
     t.tgroup = make_uint2(0u, 0u);
-    t.sp = 0;
+    t.sp = 0; t.np = 0;
     MRT_STAT(t.n_nodes = 0u; t.n_tris = 0u;)
 }
 
@@ -136,8 +138,8 @@ MRT_D uint32_t child_hit(uint32_t nx, uint32_t ny, uint32_t nz, uint32_t fx, uin
     const float t1x = __fmaf_rn(u8_to_float<B>(fx), ax, ox1), t1y = __fmaf_rn(u8_to_float<B>(fy), ay, oy1), t1z = __fmaf_rn(u8_to_float<B>(fz), az, oz1);
     const float tmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, 0.0f));
     const float tmax = fminf(fminf(t1x, t1y), fminf(t1z, tbest));
-    const uint32_t bits = (bits4 >> (8 * B)) & 0xffu, index = (index4 >> (8 * B)) & 0x1fu;
-    return tmin <= tmax * 1.000001f ? bits << index : 0u;
+    const uint32_t count = (bits4 >> (8 * B)) & 0xffu, index = (index4 >> (8 * B)) & 0x1fu;   // count: 1 for an inner child, 1..7 triangles for a leaf
+    return tmin <= tmax * 1.000001f ? ((1u << count) - 1u) << index : 0u;
 }
 
 // Visits the next pending inner node of t.ngroup: afterwards t.ngroup holds that node's hit children and
@@ -178,7 +180,7 @@ MRT_D bool trav8_node_step(const SceneDev &s, Trav8 &t, uint2 &tnew, int *overfl
     for (int w = 0; w < 2; ++w) {
         const uint32_t meta4 = __float_as_uint(w == 0 ? n1.z : n1.w);
         // per byte: inner children carry (1 << 5) | (24 + slot); their bit index is XORed with the inverse octant so that the
-        // highest pending bit is always the nearest child along the ray. Leaves carry (unary count << 5) | triangle offset.
+        // highest pending bit is always the nearest child along the ray. Leaves carry (triangle count << 5) | triangle offset.
         const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
         const uint32_t inner_mask4 = (is_inner4 >> 4) * 0xffu;
         const uint32_t index4 = (meta4 ^ (t.octinv4 & inner_mask4)) & 0x1f1f1f1fu;
@@ -243,34 +245,37 @@ MRT_D bool trav8_triangle_step(const SceneDev &s, Trav8 &t) {
     return false;
 }
 
-// One scheduling step for this lane: a node visit when inner children are pending, else the pending triangles.
-// Triangle postponing (Ylitie et al. 2017): a triangle test costs about a third of a node test but, per step, only a few
-// lanes of a warp have hit a leaf; when fewer than kPostponeLanes lanes are inside the triangle loop the group is parked
-// on the stack (a group with an empty inner byte) and retried later together with other lanes' groups.
-// Returns false when the ray is finished (t.tbest / t.bestPrim hold the result; ANY: occluded iff bestPrim >= 0).
-constexpr int kPostponeLanes = 7;
+// One scheduling step for this lane: a node visit when inner children are pending, then - only when the warp agrees -
+// the triangle phase. A triangle test costs about a fifth of a node test, but after any single node step only a few
+// lanes have hit a leaf (ncu, profiles/: 2-4 of 32 threads active in the triangle code when it ran after every step).
+// So hit leaf groups are parked in t.pend and the warp enters the triangle phase together, when at least
+// s.tune_postpone lanes have parked work, when nobody has node work left, or when this lane's parking space is full.
+// Deferring a test only delays the shrinking of tbest; the result does not depend on the order (exact-t ties go to the
+// lower primitive id). Returns false when the ray is finished (ANY: occluded iff bestPrim >= 0).
+constexpr int kPostponeLanes = 12;
 template <bool ANY>
 MRT_D bool trav8_step(const SceneDev &s, Trav8 &t, int *overflow) {
-    if (t.ngroup.y & 0xff000000u) {
+    if (!(t.ngroup.y & 0xff000000u) && t.sp > 0) { t.ngroup = t.stack[--t.sp]; }
+    bool node_work = (t.ngroup.y & 0xff000000u) != 0u;
+    if (node_work) {
         uint2 tnew;
         if (!trav8_node_step(s, t, tnew, overflow)) { return false; }
-        t.tgroup = tnew;
-    } else {
-        t.tgroup = t.ngroup;
-        t.ngroup = make_uint2(0u, 0u);
+        if (tnew.y) { t.pend[t.np++] = tnew; }
+        node_work = (t.ngroup.y & 0xff000000u) != 0u || t.sp > 0;
     }
-    while (t.tgroup.y) {
-        if (__popc(__activemask()) < kPostponeLanes && (t.ngroup.y & 0xff000000u) && t.sp < kStack8) {
-            t.stack[t.sp++] = t.tgroup;      // there is node work left for this lane: park the triangles
-            break;
+    const uint32_t mask = __activemask();
+    const uint32_t ready = __ballot_sync(mask, t.np > 0);
+    const uint32_t busy = __ballot_sync(mask, node_work);
+    const uint32_t full = __ballot_sync(mask, t.np >= kPend);
+    if (__popc(ready) >= s.tune_postpone || busy == 0u || full != 0u) {
+        if (t.np > 0) {
+            t.tgroup = t.pend[--t.np];
+            while (t.tgroup.y) {
+                if (trav8_triangle_step<ANY>(s, t)) { return false; }
+            }
         }
-        if (trav8_triangle_step<ANY>(s, t)) { return false; }
     }
-    if (!(t.ngroup.y & 0xff000000u)) {
-        if (t.sp == 0) { return false; }
-        t.ngroup = t.stack[--t.sp];
-    }
-    return true;
+    return node_work || t.np > 0;
 }
 
 // ANY: stop at the first hit with t < tbest (shadow rays). skipPrim: primitive id the ray leaves (Triangle.cpp:64), or -1.

@@ -124,7 +124,7 @@ __global__ void __launch_bounds__(kWfThreads) k_wf_extend(SceneDev s, Queues Q, 
     while (true) {
         // refill the idle lanes
         const uint32_t idle = __ballot_sync(0xffffffffu, !has);
-        if (!exhausted && __popc(idle) > 32 - kRefillLanes) {
+        if (!exhausted && __popc(idle) > 32 - s.tune_refill) {
             uint32_t base = 0;
             if (lane == 0) { base = atomicAdd(&Q.counts[kCounterExtend], static_cast<uint32_t>(__popc(idle))); }
             base = __shfl_sync(0xffffffffu, base, 0);
@@ -166,7 +166,7 @@ __global__ void __launch_bounds__(kWfThreads) k_wf_extend(SceneDev s, Queues Q, 
                     has = false;
                     break;
                 }
-                if (!exhausted && __popc(__activemask()) < kRefillLanes) { break; }
+                if (!exhausted && __popc(__activemask()) < s.tune_refill) { break; }
             }
         }
     }
@@ -308,7 +308,7 @@ __global__ void __launch_bounds__(kWfThreads) k_wf_shadow(SceneDev s, Queues Q, 
     Trav8 t;
     while (true) {
         const uint32_t idle = __ballot_sync(0xffffffffu, !has);
-        if (!exhausted && __popc(idle) > 32 - kRefillLanes) {
+        if (!exhausted && __popc(idle) > 32 - s.tune_refill) {
             uint32_t base = 0;
             if (lane == 0) { base = atomicAdd(&Q.counts[kCounterShadow], static_cast<uint32_t>(__popc(idle))); }
             base = __shfl_sync(0xffffffffu, base, 0);
@@ -346,7 +346,7 @@ __global__ void __launch_bounds__(kWfThreads) k_wf_shadow(SceneDev s, Queues Q, 
                     has = false;
                     break;
                 }
-                if (!exhausted && __popc(__activemask()) < kRefillLanes) { break; }
+                if (!exhausted && __popc(__activemask()) < s.tune_refill) { break; }
             }
         }
     }
