@@ -41,7 +41,7 @@ def scene_files():
     """Writes the conference stand-in once per box (deterministic bytes) and returns its paths."""
     from tools import make_conference_standin as gen
     out = os.environ.get("MRT_SCENE_DIR", os.path.join(tempfile.gettempdir(), "mrt_b200_scenes"))
-    marker = os.path.join(out, "conference_standin.ok")
+    marker = os.path.join(out, "conference_standin.v2.ok")
     if not os.path.exists(marker):
         info = gen.write(out)
         with open(marker, "w") as fh:
@@ -88,7 +88,7 @@ class ClockSampler(threading.Thread):
 def base_line(args, height):
     return {"metric": "Mrays/s (primary+shadow+secondary rays, reference definition) on the conference path tracer", "unit": "Mrays/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic (procedural conference stand-in, seed 7, 328180 triangles; conference.obj is absent from the reference snapshot)",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic (procedural conference stand-in, seed 7, 328120 triangles; conference.obj is absent from the reference snapshot)",
             "config": {"workload": "BASELINE config 4: conference (stand-in), PathTracer, 1 spl, %dx%d, %d spp per GPU (sample-partitioned, NCCL reduce)" % (WIDTH, height, SPP),
                        "width": WIDTH, "height": height, "spp_per_gpu": SPP, "spp_total": SPP * args.gpus, "samples_light": SPL,
                        "shader": "PathTracer", "accelerator": "BVH", "parallelism": "sample-partition x%d" % args.gpus}}

@@ -3,7 +3,7 @@
 reference's own loader (tinyobjloader) and mobileraytracer_b200.loaders read:
 
   a closed room with panelled walls, a long table, rows of chairs, table-top objects and 4 emissive ceiling panels
-  (material `light`, Ke 0.9 like conference.mtl:360-361), 328 180 triangles at the default detail, 36 diffuse materials,
+  (material `light`, Ke 0.9 like conference.mtl:360-361), 328 120 triangles at the default detail, 36 diffuse materials,
   camera = WavefrontOBJs/conference/conference.cam (p -460 500 -1000, l 0 400 0, f 45 45).
 
 Everything is generated from a fixed seed; the same arguments always give the same bytes. Numbers measured on this scene
@@ -14,7 +14,7 @@ import os
 import numpy as np
 
 N_MATERIALS = 36
-DEFAULT_DETAIL = 1.085   # gives 328 180 faces (the original conference.obj has about 331 k)
+DEFAULT_DETAIL = 1.095   # gives 328 120 faces (the original conference.obj has about 331 k)
 
 
 class Mesh:
@@ -31,7 +31,11 @@ class Mesh:
         self.nv += len(verts)
 
     def arrays(self):
-        return np.concatenate(self.v), np.concatenate(self.f), np.concatenate(self.m)
+        v, f, m = np.concatenate(self.v), np.concatenate(self.f), np.concatenate(self.m)
+        # drop zero-area faces (poles of the lathes and of the polar table top): they can never be hit and have no normal
+        a, b, c = v[f[:, 0]], v[f[:, 1]], v[f[:, 2]]
+        keep = np.linalg.norm(np.cross(b - a, c - a), axis=1) > 1e-9
+        return v, f[keep], m[keep]
 
 
 def grid_faces(nu, nv, flip=False):
