@@ -108,7 +108,8 @@ MRT_D void resolve_surface(const SceneDev &s, v3 o, v3 d, const HitRec &h, Surfa
         sf.skipKind = HIT_PLANE; sf.skipIdx = h.idx;
     } else {  // HIT_LIGHT: material = the light's radiance_ (Le only)
         const LightRec &l = s.lights[h.idx];
-        sf.normal = mk3(0.0f, 1.0f, 0.0f);
+        // the light triangle's face normal (Triangle::Builder, Triangle.cpp:328-340); no shader reads it: Le > 0 ends the path
+        sf.normal = normalize(normalize(cross(mk3(l.AC[0], l.AC[1], l.AC[2]), mk3(l.AB[0], l.AB[1], l.AB[2]))));
         sf.Le = mk3(l.Le[0], l.Le[1], l.Le[2]);
         sf.Kd = sf.Ks = sf.Kt = mk3(0.0f, 0.0f, 0.0f);
         sf.ior = 1.0f;
