@@ -231,6 +231,9 @@ int upload_scene(mrt_handle *h, const mrt_scene_desc &sc) {
         const char *tp = std::getenv("MRT_B200_POSTPONE"), *tr = std::getenv("MRT_B200_REFILL");   // tuning experiments only
         s.tune_postpone = tp ? std::atoi(tp) : 12;
         s.tune_refill = tr ? std::atoi(tr) : 22;
+        s.prmt_one = 0x3F800000u;
+        const char *tw = std::getenv("MRT_B200_WAIT");
+        s.tune_wait = tw ? std::atoi(tw) : 8;
     }
     s.nodes = h->bvh.nodes; s.tri_geom = h->bvh.tri_geom; s.tri_shade = h->d_tri_shade.as<TriShade>();
     s.n_triangles = static_cast<int32_t>(nt); s.n_bvh_prims = static_cast<int32_t>(nprims);

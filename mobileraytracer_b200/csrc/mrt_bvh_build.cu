@@ -507,7 +507,8 @@ __global__ void k_collapse8(CollapseArgs a) {
             int ex; frexpf(ext / 255.0f, &ex);      // ext/255 = m * 2^ex, m in [0.5,1)  =>  2^ex >= ext/255
             e = ex + 127;
             if (e < 1) { e = 1; }
-            while (e < 254 && __int_as_float(e << 23) * 255.0f < ext) { ++e; }
+            while (e < 239 && __int_as_float(e << 23) * 255.0f < ext) { ++e; }
+            if (__int_as_float(e << 23) * 255.0f < ext) { *a.error = 1; }   // extent beyond 2^119: outside the node format
         }
         e8[k] = e; scale[k] = __int_as_float(e << 23);
     }
@@ -557,7 +558,8 @@ __global__ void k_collapse8(CollapseArgs a) {
     if (ninner && child_base + ninner > a.max_nodes) { *a.error = 1; return; }
     Node8 node;
     node.px = plo[0]; node.py = plo[1]; node.pz = plo[2];
-    node.ex = static_cast<uint8_t>(e8[0]); node.ey = static_cast<uint8_t>(e8[1]); node.ez = static_cast<uint8_t>(e8[2]);
+    // stored biased by 15: the traversal's slab scale is 2^15 * 2^e (mrt_traverse.cuh, trav8_node_step)
+    node.ex = static_cast<uint8_t>(e8[0] + 15); node.ey = static_cast<uint8_t>(e8[1] + 15); node.ez = static_cast<uint8_t>(e8[2] + 15);
     node.imask = static_cast<uint8_t>(imask);
     node.child_base = child_base; node.tri_base = tri_base;
     int inner_rank = 0, tri_off = 0;

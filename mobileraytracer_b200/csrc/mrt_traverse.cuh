@@ -92,11 +92,15 @@ struct Trav8 {
     float tbest; int bestPrim; float bu, bv;
     uint2 ngroup, tgroup;      // x = base index, y = pending bits (node group: inner hits in 31..24, imask in 7..0)
     int sp, np;
-    uint2 pend[kPend];         // parked leaf groups (x = triangle base, y = pending triangle bits)
 #ifdef MRT_TRAVERSAL_STATS
     uint32_t n_nodes, n_tris;  // diagnostic build only (libmobilert_b200_stats.so): node visits / triangle tests of this ray
 #endif
-    uint2 stack[kStack8];
+};
+// The indexed arrays live outside Trav8 so that its scalar fields stay in registers (with the arrays inside, the whole
+// struct sat in local memory: 9 LDL per node step in the first ncu SASS view).
+struct TravMem {
+    uint2 stack[kStack8];      // node groups still to visit
+    uint2 pend[kPend];         // parked leaf groups (x = triangle base, y = pending triangle bits); per-thread callers only
 };
 
 #ifdef MRT_TRAVERSAL_STATS
@@ -125,47 +129,59 @@ MRT_D void trav8_init(Trav8 &t, v3 o, v3 d, int skipPrim, float tbest) {
     MRT_STAT(t.n_nodes = 0u; t.n_tris = 0u;)
 }
 
-// byte b of w -> float, via 0x4B0000bb = 2^23 + bb
-template <int B> MRT_D float u8_to_float(uint32_t w) {
-    return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7440u | B)) - 8388608.0f;
+// byte B of w -> the float 1 + b * 2^-15 (0x3F80bb00): one PRMT, no integer-to-float conversion and no bias subtraction;
+// the "1 +" is folded into the slab offset once per node and axis (see trav8_node_step). `one` is 0x3F800000 held in a
+// register the compiler cannot see through (SceneDev::prmt_one, a kernel parameter set by the host): PRMT takes one immediate, and with a known constant there nvcc keeps the
+// 48 selectors of a node step in registers instead (40 extra MOV / IMAD per step in the first version, ncu SASS view).
+template <int B> MRT_D float u8_to_unit(uint32_t w, uint32_t one) {
+    return __uint_as_float(__byte_perm(w, one, 0x7604u | (B << 4)));
 }
-
-// Four children (bytes 0..3 of the quantised plane words) against the ray; returns their contribution to the hit mask.
+// One child (byte B of the quantised plane words) against the ray.
 template <int B>
-MRT_D uint32_t child_hit(uint32_t nx, uint32_t ny, uint32_t nz, uint32_t fx, uint32_t fy, uint32_t fz, float ax, float ay, float az,
-                         float ox0, float oy0, float oz0, float ox1, float oy1, float oz1, float tbest, uint32_t bits4, uint32_t index4) {
-    const float t0x = __fmaf_rn(u8_to_float<B>(nx), ax, ox0), t0y = __fmaf_rn(u8_to_float<B>(ny), ay, oy0), t0z = __fmaf_rn(u8_to_float<B>(nz), az, oz0);
-    const float t1x = __fmaf_rn(u8_to_float<B>(fx), ax, ox1), t1y = __fmaf_rn(u8_to_float<B>(fy), ay, oy1), t1z = __fmaf_rn(u8_to_float<B>(fz), az, oz1);
+MRT_D bool child_hit(uint32_t nx, uint32_t ny, uint32_t nz, uint32_t fx, uint32_t fy, uint32_t fz, float ax, float ay, float az,
+                     float ox0, float oy0, float oz0, float ox1, float oy1, float oz1, float tbest, uint32_t one) {
+    const float t0x = __fmaf_rn(u8_to_unit<B>(nx, one), ax, ox0), t0y = __fmaf_rn(u8_to_unit<B>(ny, one), ay, oy0), t0z = __fmaf_rn(u8_to_unit<B>(nz, one), az, oz0);
+    const float t1x = __fmaf_rn(u8_to_unit<B>(fx, one), ax, ox1), t1y = __fmaf_rn(u8_to_unit<B>(fy, one), ay, oy1), t1z = __fmaf_rn(u8_to_unit<B>(fz, one), az, oz1);
     const float tmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, 0.0f));
     const float tmax = fminf(fminf(t1x, t1y), fminf(t1z, tbest));
-    const uint32_t count = (bits4 >> (8 * B)) & 0xffu, index = (index4 >> (8 * B)) & 0x1fu;   // count: 1 for an inner child, 1..7 triangles for a leaf
-    return tmin <= tmax * 1.000001f ? ((1u << count) - 1u) << index : 0u;
+    return tmin <= tmax;
 }
 
 // Visits the next pending inner node of t.ngroup: afterwards t.ngroup holds that node's hit children and
 // `tnew` the hit leaf triangles (the previous group, if it still has pending nodes, goes to the stack).
-MRT_D bool trav8_node_step(const SceneDev &s, Trav8 &t, uint2 &tnew, int *overflow) {
+//
+// Slab arithmetic per axis (s = 2^e the node's quantisation step, q the 8-bit plane, r = 1/d):
+//   t = (p + q s - o) r = m A + O   with m = 1 + q 2^-15 (exact, from PRMT), A = 2^15 s r, O = (p - o) r - A.
+// The node stores e + 15, so A is one shift, one mask and one multiply. Rounding: r, (p - o) r and O are each off by at
+// most 2^-24 relative to |(p - o) r| + |A|, the fused multiply-add by 2^-24 |t|; the offsets are therefore widened by
+// 1e-6 (|(p - o) r| + |A|) (about 2^-20, four times the bound) on the near side downwards and on the far side upwards.
+// The test is conservative: it can only accept more children than exact arithmetic would, never fewer.
+// Core: leaves the hit leaf slots in `lh` (bit k = slot k) with the node's meta words m0 / m1 and triangle base.
+MRT_D bool trav8_node_core(const SceneDev &s, Trav8 &t, TravMem &tm_, uint32_t &tbase, uint32_t &lh, uint32_t &m0, uint32_t &m1, int *overflow) {
     MRT_STAT(++t.n_nodes;)
     const uint32_t bit = 31u - __clz(t.ngroup.y);
     t.ngroup.y &= ~(1u << bit);
-    if (t.ngroup.y & 0xff000000u) {
-        if (t.sp >= kStack8) { *overflow = 1; return false; }
-        t.stack[t.sp++] = t.ngroup;
+    {   // the rest of the group goes to the stack: an unconditional store plus a conditional bump of sp (no divergent branch)
+        const bool push = (t.ngroup.y & 0xff000000u) != 0u;
+        if (push && t.sp >= kStack8) { *overflow = 1; return false; }
+        tm_.stack[t.sp < kStack8 ? t.sp : kStack8 - 1] = t.ngroup;
+        t.sp += push ? 1 : 0;
     }
-    const uint32_t slot = (bit - 24u) ^ (t.octinv4 & 0xffu);
+    const uint32_t one = s.prmt_one;
+    const uint32_t octinv = t.octinv4 & 0xffu;
+    const uint32_t slot = (bit - 24u) ^ octinv;
     const uint32_t rel = __popc(t.ngroup.y & ((1u << slot) - 1u) & 0xffu);
     const float4 *np = reinterpret_cast<const float4 *>(s.nodes) + 5ull * (t.ngroup.x + rel);
     const float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
-    // n0 = px py pz (ex ey ez imask) | n1 = child_base tri_base meta[0..3] meta[4..7]
+    // n0 = px py pz (ex+15 ey+15 ez+15 imask) | n1 = child_base tri_base meta[0..3] meta[4..7]
     // n2 = qlox[0..7] qloy[0..7] | n3 = qloz[0..7] qhix[0..7] | n4 = qhiy[0..7] qhiz[0..7]
     const uint32_t e = __float_as_uint(n0.w);
-    const float ax = __uint_as_float((e & 0xffu) << 23) * t.idx, ay = __uint_as_float(((e >> 8) & 0xffu) << 23) * t.idy,
-                az = __uint_as_float(((e >> 16) & 0xffu) << 23) * t.idz;
-    const float ox = (n0.x - t.o.x) * t.idx, oy = (n0.y - t.o.y) * t.idy, oz = (n0.z - t.o.z) * t.idz;
-    // conservative slabs: the offsets are widened by their own rounding error (relative 1e-6), the final comparison
-    // by the rounding of the fused multiply-adds
-    const float sxo = 1.0e-6f * fabsf(ox), syo = 1.0e-6f * fabsf(oy), szo = 1.0e-6f * fabsf(oz);
-    const float ox0 = ox - sxo, ox1 = ox + sxo, oy0 = oy - syo, oy1 = oy + syo, oz0 = oz - szo, oz1 = oz + szo;
+    const float ax = __uint_as_float((e << 23) & 0x7f800000u) * t.idx, ay = __uint_as_float((e << 15) & 0x7f800000u) * t.idy,
+                az = __uint_as_float((e << 7) & 0x7f800000u) * t.idz;
+    const float px = (n0.x - t.o.x) * t.idx, py = (n0.y - t.o.y) * t.idy, pz = (n0.z - t.o.z) * t.idz;
+    const float ox = px - ax, oy = py - ay, oz = pz - az;
+    const float wx = 1.0e-6f * (fabsf(px) + fabsf(ax)), wy = 1.0e-6f * (fabsf(py) + fabsf(ay)), wz = 1.0e-6f * (fabsf(pz) + fabsf(az));
+    const float ox0 = ox - wx, ox1 = ox + wx, oy0 = oy - wy, oy1 = oy + wy, oz0 = oz - wz, oz1 = oz + wz;
     // near / far plane words per axis, chosen once per node by the ray octant
     const bool fx_ = t.oct & 1u, fy_ = t.oct & 2u, fz_ = t.oct & 4u;
     const uint32_t qlx0 = __float_as_uint(n2.x), qlx1 = __float_as_uint(n2.y), qly0 = __float_as_uint(n2.z), qly1 = __float_as_uint(n2.w);
@@ -175,33 +191,82 @@ MRT_D bool trav8_node_step(const SceneDev &s, Trav8 &t, uint2 &tnew, int *overfl
     const uint32_t ny0 = fy_ ? qhy0 : qly0, ny1 = fy_ ? qhy1 : qly1, fy0 = fy_ ? qly0 : qhy0, fy1 = fy_ ? qly1 : qhy1;
     const uint32_t nz0 = fz_ ? qhz0 : qlz0, nz1 = fz_ ? qhz1 : qlz1, fz0 = fz_ ? qlz0 : qhz0, fz1 = fz_ ? qlz1 : qhz1;
     const uint32_t imask = e >> 24;
-    uint32_t hitmask = 0u;
-#pragma unroll
-    for (int w = 0; w < 2; ++w) {
-        const uint32_t meta4 = __float_as_uint(w == 0 ? n1.z : n1.w);
-        // per byte: inner children carry (1 << 5) | (24 + slot); their bit index is XORed with the inverse octant so that the
-        // highest pending bit is always the nearest child along the ray. Leaves carry (triangle count << 5) | triangle offset.
-        const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
-        const uint32_t inner_mask4 = (is_inner4 >> 4) * 0xffu;
-        const uint32_t index4 = (meta4 ^ (t.octinv4 & inner_mask4)) & 0x1f1f1f1fu;
-        const uint32_t bits4 = (meta4 >> 5) & 0x07070707u;
-        const uint32_t nx = w == 0 ? nx0 : nx1, ny = w == 0 ? ny0 : ny1, nz = w == 0 ? nz0 : nz1;
-        const uint32_t fx = w == 0 ? fx0 : fx1, fy = w == 0 ? fy0 : fy1, fz = w == 0 ? fz0 : fz1;
-        hitmask |= child_hit<0>(nx, ny, nz, fx, fy, fz, ax, ay, az, ox0, oy0, oz0, ox1, oy1, oz1, t.tbest, bits4, index4);
-        hitmask |= child_hit<1>(nx, ny, nz, fx, fy, fz, ax, ay, az, ox0, oy0, oz0, ox1, oy1, oz1, t.tbest, bits4, index4);
-        hitmask |= child_hit<2>(nx, ny, nz, fx, fy, fz, ax, ay, az, ox0, oy0, oz0, ox1, oy1, oz1, t.tbest, bits4, index4);
-        hitmask |= child_hit<3>(nx, ny, nz, fx, fy, fz, ax, ay, az, ox0, oy0, oz0, ox1, oy1, oz1, t.tbest, bits4, index4);
-    }
+    uint32_t hits = 0u;   // bit k: child slot k is hit
+#define MRT_CHILD(B, NX, NY, NZ, FX, FY, FZ, K) \
+    if (child_hit<B>(NX, NY, NZ, FX, FY, FZ, ax, ay, az, ox0, oy0, oz0, ox1, oy1, oz1, t.tbest, one)) { hits |= 1u << (K); }
+    MRT_CHILD(0, nx0, ny0, nz0, fx0, fy0, fz0, 0) MRT_CHILD(1, nx0, ny0, nz0, fx0, fy0, fz0, 1)
+    MRT_CHILD(2, nx0, ny0, nz0, fx0, fy0, fz0, 2) MRT_CHILD(3, nx0, ny0, nz0, fx0, fy0, fz0, 3)
+    MRT_CHILD(0, nx1, ny1, nz1, fx1, fy1, fz1, 4) MRT_CHILD(1, nx1, ny1, nz1, fx1, fy1, fz1, 5)
+    MRT_CHILD(2, nx1, ny1, nz1, fx1, fy1, fz1, 6) MRT_CHILD(3, nx1, ny1, nz1, fx1, fy1, fz1, 7)
+#undef MRT_CHILD
+    // inner children: bit (slot ^ octinv), so that the highest pending bit is always the nearest child along the ray
+    // (slot s of a node holds the child lying towards +axis k for every set bit k of s, see k_collapse8)
+    uint32_t in = hits & imask;
+    if (octinv & 1u) { in = ((in & 0x55u) << 1) | ((in & 0xaau) >> 1); }
+    if (octinv & 2u) { in = ((in & 0x33u) << 2) | ((in & 0xccu) >> 2); }
+    if (octinv & 4u) { in = ((in & 0x0fu) << 4) | ((in & 0xf0u) >> 4); }
     t.ngroup.x = __float_as_uint(n1.x);
-    t.ngroup.y = (hitmask & 0xff000000u) | imask;
-    tnew.x = __float_as_uint(n1.y);
-    tnew.y = hitmask & 0x00ffffffu;
+    t.ngroup.y = (in << 24) | imask;
+    // leaf children: meta byte = (triangle count 1..7 << 5) | offset 0..23 into the node's triangle run (0 for an empty slot)
+    lh = hits & ~imask;
+    m0 = __float_as_uint(n1.z); m1 = __float_as_uint(n1.w);
+    tbase = __float_as_uint(n1.y);
     return true;
 }
 
+// meta byte of leaf slot k
+MRT_D uint32_t leaf_meta(uint32_t m0, uint32_t m1, uint32_t k) { return __byte_perm(m0, m1, k) & 0xffu; }
+
+// Per-thread form: `tnew` = (triangle base, bit mask of the hit leaf triangles within the node's run of <= 24).
+MRT_D bool trav8_node_step(const SceneDev &s, Trav8 &t, TravMem &tm_, uint2 &tnew, int *overflow) {
+    uint32_t tbase, lh, m0, m1;
+    if (!trav8_node_core(s, t, tm_, tbase, lh, m0, m1, overflow)) { return false; }
+    uint32_t tm = 0u;
+    while (lh) {
+        const uint32_t k = __ffs(lh) - 1u;
+        lh &= lh - 1u;
+        const uint32_t mb = leaf_meta(m0, m1, k);
+        tm |= ((1u << (mb >> 5)) - 1u) << (mb & 31u);
+    }
+    tnew.x = tbase;
+    tnew.y = tm;
+    return true;
+}
+
+// Triangle::intersect (Triangle.cpp:63-99) on a packed triangle, without the "t < current length" rule (the callers apply
+// it so that they can break exact-t ties). A sound prefilter comes first: the sign / magnitude tests only reject what the
+// reference's own comparisons reject for certain (tbest is only used there); survivors run the reference's exact
+// arithmetic (one IEEE division). True when 0 <= u, v, u + v <= 1 and Epsilon <= tt.
+MRT_D bool tri_hit(const float4 g0, const float4 g1, const float4 g2, v3 o, v3 d, float tbest, float &tt, float &u, float &v) {
+    const v3 A = mk3(g0.x, g0.y, g0.z), AB = mk3(g0.w, g1.x, g1.y), AC = mk3(g1.z, g1.w, g2.x);
+    const v3 perpendicularVector = cross(d, AC);
+    const float det = dot(AB, perpendicularVector);
+    const float adet = fabsf(det);
+    if (adet < kEpsilon) { return false; }
+    const uint32_t sgn = __float_as_uint(det) & 0x80000000u;
+    const float hi = adet * 1.00001f;
+    const v3 vectorToCamera = o - A;
+    const float du = dot(vectorToCamera, perpendicularVector);
+    const float su = __uint_as_float(__float_as_uint(du) ^ sgn);
+    if (su < -1.0e-25f || su > hi) { return false; }
+    const v3 upPerpendicularVector = cross(vectorToCamera, AB);
+    const float dv = dot(d, upPerpendicularVector);
+    const float sv = __uint_as_float(__float_as_uint(dv) ^ sgn);
+    if (sv < -1.0e-25f || su + sv > hi) { return false; }
+    const float dt = dot(AC, upPerpendicularVector);
+    const float st = __uint_as_float(__float_as_uint(dt) ^ sgn);
+    if (st < -1.0e-25f || st > hi * fminf(tbest, 1.0e25f)) { return false; }
+    // exact path
+    const float inv = 1.0f / det;
+    u = inv * du;
+    if (u < 0.0f || u > 1.0f) { return false; }
+    v = inv * dv;
+    if (v < 0.0f || (u + v) > 1.0f) { return false; }
+    tt = inv * dt;
+    return !(tt < kEpsilon);
+}
+
 // Tests the next pending triangle of t.tgroup. Returns true when an ANY-hit ray found its occluder.
-// Triangle::intersect (Triangle.cpp:63-99) with a sound prefilter: the sign / magnitude tests below only reject what the
-// reference's own comparisons reject for certain; survivors run the reference's exact arithmetic (one IEEE division).
 template <bool ANY>
 MRT_D bool trav8_triangle_step(const SceneDev &s, Trav8 &t) {
     const uint32_t i = __ffs(t.tgroup.y) - 1u;
@@ -212,32 +277,8 @@ MRT_D bool trav8_triangle_step(const SceneDev &s, Trav8 &t) {
     if (prim == t.skipPrim) { return false; }
     if (ANY && prim >= s.n_triangles) { return false; }      // area lights do not occlude (Shader.cpp:132-158)
     MRT_STAT(++t.n_tris;)
-    const v3 A = mk3(g0.x, g0.y, g0.z), AB = mk3(g0.w, g1.x, g1.y), AC = mk3(g1.z, g1.w, g2.x);
-    const v3 perpendicularVector = cross(t.d, AC);
-    const float det = dot(AB, perpendicularVector);
-    const float adet = fabsf(det);
-    if (adet < kEpsilon) { return false; }
-    const uint32_t sgn = __float_as_uint(det) & 0x80000000u;
-    const float hi = adet * 1.00001f;
-    const v3 vectorToCamera = t.o - A;
-    const float du = dot(vectorToCamera, perpendicularVector);
-    const float su = __uint_as_float(__float_as_uint(du) ^ sgn);
-    if (su < -1.0e-25f || su > hi) { return false; }
-    const v3 upPerpendicularVector = cross(vectorToCamera, AB);
-    const float dv = dot(t.d, upPerpendicularVector);
-    const float sv = __uint_as_float(__float_as_uint(dv) ^ sgn);
-    if (sv < -1.0e-25f || su + sv > hi) { return false; }
-    const float dt = dot(AC, upPerpendicularVector);
-    const float st = __uint_as_float(__float_as_uint(dt) ^ sgn);
-    if (st < -1.0e-25f || st > hi * fminf(t.tbest, 1.0e25f)) { return false; }
-    // exact path
-    const float inv = 1.0f / det;
-    const float u = inv * du;
-    if (u < 0.0f || u > 1.0f) { return false; }
-    const float v = inv * dv;
-    if (v < 0.0f || (u + v) > 1.0f) { return false; }
-    const float tt = inv * dt;
-    if (tt < kEpsilon) { return false; }
+    float tt, u, v;
+    if (!tri_hit(g0, g1, g2, t.o, t.d, t.tbest, tt, u, v)) { return false; }
     if (tt < t.tbest || (!ANY && tt == t.tbest && t.bestPrim >= 0 && prim < t.bestPrim)) {
         t.tbest = tt; t.bestPrim = prim; t.bu = u; t.bv = v;
         return ANY;
@@ -254,13 +295,13 @@ MRT_D bool trav8_triangle_step(const SceneDev &s, Trav8 &t) {
 // lower primitive id). Returns false when the ray is finished (ANY: occluded iff bestPrim >= 0).
 constexpr int kPostponeLanes = 12;
 template <bool ANY>
-MRT_D bool trav8_step(const SceneDev &s, Trav8 &t, int *overflow) {
-    if (!(t.ngroup.y & 0xff000000u) && t.sp > 0) { t.ngroup = t.stack[--t.sp]; }
+MRT_D bool trav8_step(const SceneDev &s, Trav8 &t, TravMem &tm_, int *overflow) {
+    if (!(t.ngroup.y & 0xff000000u) && t.sp > 0) { t.ngroup = tm_.stack[--t.sp]; }
     bool node_work = (t.ngroup.y & 0xff000000u) != 0u;
     if (node_work) {
         uint2 tnew;
-        if (!trav8_node_step(s, t, tnew, overflow)) { return false; }
-        if (tnew.y) { t.pend[t.np++] = tnew; }
+        if (!trav8_node_step(s, t, tm_, tnew, overflow)) { return false; }
+        if (tnew.y) { tm_.pend[t.np++] = tnew; }
         node_work = (t.ngroup.y & 0xff000000u) != 0u || t.sp > 0;
     }
     const uint32_t mask = __activemask();
@@ -269,7 +310,7 @@ MRT_D bool trav8_step(const SceneDev &s, Trav8 &t, int *overflow) {
     const uint32_t full = __ballot_sync(mask, t.np >= kPend);
     if (__popc(ready) >= s.tune_postpone || busy == 0u || full != 0u) {
         if (t.np > 0) {
-            t.tgroup = t.pend[--t.np];
+            t.tgroup = tm_.pend[--t.np];
             while (t.tgroup.y) {
                 if (trav8_triangle_step<ANY>(s, t)) { return false; }
             }
@@ -284,8 +325,9 @@ template <bool ANY>
 MRT_D bool trace_bvh8(const SceneDev &s, v3 o, v3 d, int skipPrim, float &tbest, int &bestPrim, float &bu, float &bv, int *overflow) {
     if (s.n_bvh_prims == 0) { return false; }
     Trav8 t;
+    TravMem tm_;
     trav8_init(t, o, d, skipPrim, tbest);
-    while (trav8_step<ANY>(s, t, overflow)) { }
+    while (trav8_step<ANY>(s, t, tm_, overflow)) { }
     MRT_STAT(atomicAdd(&g_stat_nodes, t.n_nodes); atomicAdd(&g_stat_tris, t.n_tris); atomicAdd(&g_stat_rays, 1ull);)
     if (t.bestPrim >= 0) { tbest = t.tbest; bestPrim = t.bestPrim; bu = t.bu; bv = t.bv; }
     return ANY && t.bestPrim >= 0;

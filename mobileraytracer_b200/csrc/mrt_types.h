@@ -5,7 +5,8 @@
 namespace mrt {
 
 // Compressed 8-wide BVH node, 80 bytes, 16-byte aligned (5 x float4 loads).
-// Child boxes are quantised to 8 bits per plane relative to (p, 2^e): lo = p + qlo * 2^e (rounded outward).
+// Child boxes are quantised to 8 bits per plane relative to (p, 2^e): lo = p + qlo * 2^e (rounded outward);
+// ex/ey/ez hold the IEEE exponent byte of 2^e plus 15.
 // meta[i]: empty 0 | inner: (1 << 5) | (24 + i) | leaf: (triangle count 1..7 << 5) | triangle offset 0..23.
 // Inner children are stored contiguously from child_base in slot order (imask bit i = slot i is inner);
 // the triangles of all leaf slots are stored contiguously from tri_base (<= 24 per node).
@@ -67,7 +68,8 @@ struct SceneDev {
     const float *tile_order;     // 256
     const float *shader_table;   // 1 << 20
     const float *static_halton;  // 1 << 20
-    int32_t tune_postpone, tune_refill;   // traversal scheduling thresholds in lanes (see mrt_traverse.cuh / mrt_wavefront.cu)
+    int32_t tune_postpone, tune_refill, tune_wait;   // traversal scheduling thresholds in lanes (see mrt_traverse.cuh / mrt_wavefront.cu)
+    uint32_t prmt_one;           // 0x3F800000, deliberately a run-time value (mrt_traverse.cuh, u8_to_unit)
     const float *pixel_table;    // table the pixel sampler reads (static_halton or static_mt), or null for Constant
 };
 

@@ -105,73 +105,265 @@ __global__ void k_wf_begin_levels(Queues Q) { Q.counts[9] = Q.counts[0]; }
 // ---- extend / shadow: persistent traversal kernels --------------------------------------------------------------
 // One CTA of 4 warps per scheduling slot, resident for the whole launch. A lane that has finished its ray fetches the
 // next one from the level's work counter (one warp-aggregated atomic per refill), so the lanes of a warp stay busy although
-// their rays need very different numbers of steps; refills happen when fewer than kRefillLanes lanes still hold a ray.
-constexpr int kRefillLanes = 22;
+// their rays need very different numbers of steps; refills happen when fewer than s.tune_refill lanes still hold a ray.
+//
+// Node tests and triangle tests are scheduled separately, because after any single node step only a few lanes have hit
+// a leaf (ncu, profiles/r1_s25_extend_*: 7 of 32 threads active in per-lane triangle code, which then cost a third of
+// the kernel for 3 % of its arithmetic):
+//   node phase     : every lane with pending inner nodes visits one BVH8 node; each leaf child it hits is appended as an
+//                    item (owner lane, first triangle slot, triangle count) to a per-warp list in shared memory;
+//   triangle phase : whenever 32 items are waiting, the warp tests them together, one leaf per lane. The ray of the
+//                    owner comes through warp shuffles; a hit is committed with one 64-bit atomicMin on the owner's
+//                    key (t bits << 32 | primitive id) in shared memory, which implements "nearest t, then lowest
+//                    primitive id" (the reference keeps the first hit of its left-first walk at equal t, mrt_traverse.cuh)
+//                    independently of the order the items are processed in.
+// A lane whose node work is finished may still own items in the list; it retires once the list has been emptied, which
+// is forced when s.tune_wait lanes are waiting or nobody has node work left.
 constexpr int kCounterExtend = 20, kCounterShadow = 21;   // Queues::counts slots used as work counters
+constexpr uint32_t kItemCap = 128;                        // leaf items per warp; one node step adds at most 8 per lane
+
+struct __align__(16) WarpShared {
+    unsigned long long key[32];   // per lane: best hit so far, (float bits of t) << 32 | primitive id
+    float2 uv[32];                // barycentrics of that hit
+    uint2 items[kItemCap];        // x = first triangle slot of the leaf, y = owner lane | triangle count << 8
+    uint32_t count;               // items in the list
+    uint32_t pad[3];
+};
 
 MRT_D uint32_t pack_hit(const HitRec &h) { return (static_cast<uint32_t>(h.kind) << 28) | (static_cast<uint32_t>(h.idx) & 0x0fffffffu); }
 
-// extend: closest hit for every ray of the level (Shader::rayTrace's geometric part, Shader.cpp:86-111)
-__global__ void __launch_bounds__(kWfThreads) k_wf_extend(SceneDev s, Queues Q, int level, DeviceCounters *dc) {
-    const int b = level & 1;
-    const uint32_t n = min(Q.counts[level], Q.cap_rays);
-    const int lane = threadIdx.x & 31;
-    int overflow = 0;
-    bool has = false, exhausted = false;
-    uint32_t cur = 0;
-    HitRec h;
-    Trav8 t;
-    while (true) {
-        // refill the idle lanes
-        const uint32_t idle = __ballot_sync(0xffffffffu, !has);
-        if (!exhausted && __popc(idle) > 32 - s.tune_refill) {
-            uint32_t base = 0;
-            if (lane == 0) { base = atomicAdd(&Q.counts[kCounterExtend], static_cast<uint32_t>(__popc(idle))); }
-            base = __shfl_sync(0xffffffffu, base, 0);
-            if (base + __popc(idle) >= n) { exhausted = true; }
-            if (!has) {
-                cur = base + __popc(idle & ((1u << lane) - 1u));
-                if (cur < n) {
-                    const float4 a = Q.r0[b][cur], c = Q.r1[b][cur];
-                    const v3 o = mk3(a.x, a.y, a.z), d = mk3(a.w, c.x, c.y);
-                    int sk, si;
-                    unpack_skip(__float_as_uint(c.z), sk, si);
-                    h.t = kRayLengthMax; h.kind = HIT_NONE; h.idx = -1; h.u = 0.0f; h.v = 0.0f;
-                    trace_ref_bvh<0>(s, o, d, false, sk, si, h, &overflow);
-                    trace_ref_bvh<1>(s, o, d, false, sk, si, h, &overflow);
-                    if (s.n_bvh_prims > 0 && triangles_root_hit(s, o, d)) {
-                        trav8_init(t, o, d, sk == HIT_TRIANGLE ? si : -1, h.t);
-                        has = true;
-                    } else {
-                        if (s.n_bvh_prims > s.n_triangles) { trace_lights_linear(s, o, d, h); }
-                        Q.hit[cur] = make_float4(h.t, h.u, h.v, __uint_as_float(pack_hit(h)));
-                    }
-                }
-            }
-        }
-        if (__ballot_sync(0xffffffffu, has) == 0u) {
-            if (exhausted) { break; }
-            continue;
-        }
-        if (has) {
-            while (true) {
-                if (!trav8_step<false>(s, t, &overflow)) {
-                    if (t.bestPrim >= 0) {
-                        h.t = t.tbest; h.u = t.bu; h.v = t.bv;
-                        if (t.bestPrim < s.n_triangles) { h.kind = HIT_TRIANGLE; h.idx = t.bestPrim; }
-                        else { h.kind = HIT_LIGHT; h.idx = t.bestPrim - s.n_triangles; }
-                    }
-                    Q.hit[cur] = make_float4(h.t, h.u, h.v, __uint_as_float(pack_hit(h)));
-                    MRT_STAT(atomicAdd(&g_stat_nodes, t.n_nodes); atomicAdd(&g_stat_tris, t.n_tris); atomicAdd(&g_stat_rays, 1ull);)
-                    has = false;
-                    break;
-                }
-                if (!exhausted && __popc(__activemask()) < s.tune_refill) { break; }
+// an unoccluded shadow sample adds its share of Ld to the chain (PathTracer.cpp:72-80)
+MRT_D void shadow_unoccluded(const Queues &Q, uint32_t i) {
+    const float4 cc = Q.s2[i];
+    const uint32_t tag = __float_as_uint(cc.w);
+    Chain *ch = Q.chains + (tag & 0x0fffffffu);
+    const uint32_t dz = (tag >> 28) & 7u;
+    atomicAdd(&ch->sum[dz][0], cc.x); atomicAdd(&ch->sum[dz][1], cc.y); atomicAdd(&ch->sum[dz][2], cc.z);
+    if (tag & 0x80000000u) { atomicOr(&ch->ldmask, 1u << dz); }
+}
+
+// The warp tests the leaves items[first, first + n), n <= 32, one per lane. Must be called by all 32 lanes.
+template <bool ANY>
+MRT_D void coop_triangle_pass(const SceneDev &s, WarpShared &w, const Trav8 &t, uint32_t first, uint32_t n, int lane) {
+    const uint32_t full = 0xffffffffu;
+    const bool valid = static_cast<uint32_t>(lane) < n;
+    const uint2 item = valid ? w.items[first + lane] : make_uint2(0u, static_cast<uint32_t>(lane));
+    const int owner = static_cast<int>(item.y & 31u);
+    const uint32_t cnt = item.y >> 8;        // 0 for a lane without an item
+    const v3 o = mk3(__shfl_sync(full, t.o.x, owner), __shfl_sync(full, t.o.y, owner), __shfl_sync(full, t.o.z, owner));
+    const v3 d = mk3(__shfl_sync(full, t.d.x, owner), __shfl_sync(full, t.d.y, owner), __shfl_sync(full, t.d.z, owner));
+    const int skip = __shfl_sync(full, t.skipPrim, owner);
+    unsigned long long mykey = ~0ull;
+    float bu = 0.0f, bv = 0.0f;
+    if (cnt != 0u) {
+        float tbest = __uint_as_float(reinterpret_cast<const uint2 *>(&w.key[owner])->y);
+        const float4 *tp = reinterpret_cast<const float4 *>(s.tri_geom) + 3ull * item.x;
+        for (uint32_t j = 0; j < cnt; ++j, tp += 3) {
+            const float4 g0 = __ldg(tp), g1 = __ldg(tp + 1), g2 = __ldg(tp + 2);
+            const uint32_t prim = __float_as_uint(g2.y);
+            // self-hit skip (Triangle.cpp:64); area lights do not occlude (Shader.cpp:132-158)
+            if (static_cast<int>(prim) == skip || (ANY && static_cast<int>(prim) >= s.n_triangles)) { continue; }
+            MRT_STAT(atomicAdd(&g_stat_tris, 1ull);)
+            float tt, u, v;
+            if (tri_hit(g0, g1, g2, o, d, tbest, tt, u, v)) {
+                const unsigned long long k = (static_cast<unsigned long long>(__float_as_uint(tt)) << 32) | prim;
+                if (k < mykey) { mykey = k; bu = u; bv = v; tbest = fminf(tbest, tt); }
             }
         }
     }
+    bool won = false;
+    if (mykey != ~0ull) { won = atomicMin(&w.key[owner], mykey) > mykey; }
+    if (!ANY) {
+        __syncwarp();
+        if (won && w.key[owner] == mykey) { w.uv[owner] = make_float2(bu, bv); }   // the one final winner of this pass
+    }
+    __syncwarp();
+}
+
+// ANY = false: closest hit for every ray of the level (Shader::rayTrace's geometric part, Shader.cpp:86-111) -> Q.hit
+// ANY = true : any hit within the light distance for every shadow ray (Shader::shadowTrace, Shader.cpp:132-158)
+template <bool ANY>
+MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCounters *dc) {
+    __shared__ WarpShared wsh[kWfThreads / 32];
+    WarpShared &w = wsh[threadIdx.x >> 5];
+    const uint32_t full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const uint32_t lane_bit = 1u << lane;
+    const int b = level & 1;
+    const uint32_t n = ANY ? min(Q.counts[8], Q.cap_shadow) : min(Q.counts[level], Q.cap_rays);
+    uint32_t *work = &Q.counts[ANY ? kCounterShadow : kCounterExtend];
+    int overflow = 0;
+    bool exhausted = false;
+    bool node_work = false;          // this lane has pending inner nodes
+    uint32_t hasmask = 0u;           // lanes holding a ray (warp-uniform)
+    uint32_t outmask = 0u;           // lanes that may own items in the list (warp-uniform)
+    uint32_t busy = 0u;              // ballot of node_work (warp-uniform)
+    uint32_t cur = 0, count = 0;     // count: items in the warp's list (warp-uniform copy of w.count)
+    unsigned long long key0 = 0ull;  // the key the ray started with: tbest of the plane / sphere pass (or the light distance), id 0
+    HitRec h;
+    h.t = kRayLengthMax; h.kind = HIT_NONE; h.idx = -1; h.u = 0.0f; h.v = 0.0f;
+    Trav8 t;
+    TravMem tmem;
+    t.o = mk3(0.0f, 0.0f, 0.0f); t.d = mk3(0.0f, 0.0f, 1.0f); t.skipPrim = -1;
+    t.ngroup = make_uint2(0u, 0u); t.sp = 0; t.tbest = 0.0f;
+    MRT_STAT(t.n_nodes = 0u; t.n_tris = 0u;)
+    if (lane == 0) { w.count = 0u; }
+    __syncwarp();
+
+    // empties the warp's item list (top chunk first); afterwards nobody owns pending items
+#define MRT_FLUSH_ITEMS()                                                                         \
+    do {                                                                                          \
+        while (count > 0u) {                                                                      \
+            const uint32_t m_ = count < 32u ? count : 32u;                                        \
+            coop_triangle_pass<ANY>(s, w, t, count - m_, m_, lane);                               \
+            count -= m_;                                                                          \
+        }                                                                                         \
+        if (lane == 0) { w.count = 0u; }                                                          \
+        __syncwarp();                                                                             \
+        outmask = 0u;                                                                             \
+    } while (0)
+    // after triangle passes: the lane's own best hit bounds its further node tests; an occluded shadow ray stops
+#define MRT_REFRESH_BEST()                                                                        \
+    do {                                                                                          \
+        if (hasmask & lane_bit) {                                                                 \
+            const unsigned long long k_ = w.key[lane];                                            \
+            if (ANY) { if (k_ != key0) { t.ngroup.y = 0u; t.sp = 0; node_work = false; } }        \
+            else { t.tbest = __uint_as_float(static_cast<uint32_t>(k_ >> 32)); }                  \
+        }                                                                                         \
+        busy = __ballot_sync(full, node_work);                                                    \
+    } while (0)
+
+    while (true) {
+        // retire: node work done and no item of the lane left in the list
+        const uint32_t done = hasmask & ~busy & ~outmask;
+        if (done) {
+            if (done & lane_bit) {
+                const unsigned long long k = w.key[lane];
+                if (ANY) {
+                    if (k == key0) { shadow_unoccluded(Q, cur); }
+                } else {
+                    if (k != key0) {
+                        const int prim = static_cast<int>(static_cast<uint32_t>(k));
+                        const float2 uv = w.uv[lane];
+                        h.t = __uint_as_float(static_cast<uint32_t>(k >> 32)); h.u = uv.x; h.v = uv.y;
+                        if (prim < s.n_triangles) { h.kind = HIT_TRIANGLE; h.idx = prim; }
+                        else { h.kind = HIT_LIGHT; h.idx = prim - s.n_triangles; }
+                    }
+                    Q.hit[cur] = make_float4(h.t, h.u, h.v, __uint_as_float(pack_hit(h)));
+                }
+                MRT_STAT(atomicAdd(&g_stat_nodes, t.n_nodes); atomicAdd(&g_stat_rays, 1ull); t.n_nodes = 0u;)
+            }
+            hasmask &= ~done;
+        }
+        // refill the idle lanes
+        if (!exhausted && __popc(~hasmask) > 32 - s.tune_refill) {
+            const uint32_t idle = ~hasmask;
+            uint32_t base = 0;
+            if (lane == 0) { base = atomicAdd(work, static_cast<uint32_t>(__popc(idle))); }
+            base = __shfl_sync(full, base, 0);
+            if (base + __popc(idle) >= n) { exhausted = true; }
+            bool got = false;
+            if (idle & lane_bit) {
+                cur = base + __popc(idle & (lane_bit - 1u));
+                if (cur < n) {
+                    const float4 a = ANY ? Q.s0[cur] : Q.r0[b][cur], c = ANY ? Q.s1[cur] : Q.r1[b][cur];
+                    const v3 o = mk3(a.x, a.y, a.z), d = mk3(a.w, c.x, c.y);
+                    int sk, si;
+                    unpack_skip(__float_as_uint(ANY ? c.w : c.z), sk, si);
+                    h.t = ANY ? c.z : kRayLengthMax; h.kind = HIT_NONE; h.idx = -1; h.u = 0.0f; h.v = 0.0f;
+                    bool occluded = false;
+                    if (ANY) {
+                        occluded = trace_ref_bvh<0>(s, o, d, true, sk, si, h, &overflow) || trace_ref_bvh<1>(s, o, d, true, sk, si, h, &overflow);
+                    } else {
+                        trace_ref_bvh<0>(s, o, d, false, sk, si, h, &overflow);
+                        trace_ref_bvh<1>(s, o, d, false, sk, si, h, &overflow);
+                    }
+                    if (!occluded) {
+                        if (s.n_bvh_prims > 0 && triangles_root_hit(s, o, d)) {
+                            trav8_init(t, o, d, sk == HIT_TRIANGLE ? si : -1, h.t);
+                            key0 = static_cast<unsigned long long>(__float_as_uint(h.t)) << 32;
+                            w.key[lane] = key0;
+                            got = true; node_work = true;
+                        } else if (ANY) {
+                            shadow_unoccluded(Q, cur);
+                        } else {
+                            if (s.n_bvh_prims > s.n_triangles) { trace_lights_linear(s, o, d, h); }
+                            Q.hit[cur] = make_float4(h.t, h.u, h.v, __uint_as_float(pack_hit(h)));
+                        }
+                    }
+                }
+            }
+            hasmask |= __ballot_sync(full, got);
+            busy = __ballot_sync(full, node_work);
+        }
+        if (busy == 0u) {
+            if (count > 0u) { MRT_FLUSH_ITEMS(); MRT_REFRESH_BEST(); continue; }
+            if (hasmask == 0u && exhausted) { break; }
+            continue;
+        }
+        // node phase
+        uint32_t tbase = 0u, lh = 0u, m0 = 0u, m1 = 0u;
+        {
+            // pop speculatively (the load does not wait inside a divergent branch)
+            const uint2 top = tmem.stack[t.sp > 0 ? t.sp - 1 : 0];
+            if (node_work) {
+                if (!(t.ngroup.y & 0xff000000u)) { t.ngroup = top; --t.sp; }
+                if (!trav8_node_core(s, t, tmem, tbase, lh, m0, m1, &overflow)) { t.ngroup.y = 0u; t.sp = 0; lh = 0u; }
+                node_work = (t.ngroup.y & 0xff000000u) != 0u || t.sp > 0;
+            }
+        }
+        // append the hit leaves to the warp's list: one shared-memory atomic per lane that hit a leaf
+        uint32_t emit = __ballot_sync(full, lh != 0u);
+        while (emit != 0u) {
+            uint32_t pos = 0xffffffffu;
+            if (lh != 0u) {
+                const uint32_t nl = __popc(lh);
+                pos = atomicAdd(&w.count, nl);
+                if (pos + nl <= kItemCap) {
+                    do {
+                        const uint32_t k = __ffs(lh) - 1u;
+                        lh &= lh - 1u;
+                        const uint32_t mb = leaf_meta(m0, m1, k);
+                        w.items[pos++] = make_uint2(tbase + (mb & 31u), static_cast<uint32_t>(lane) | ((mb >> 5) << 8));
+                    } while (lh != 0u);
+                    pos = 0xffffffffu;   // appended
+                }
+            }
+            outmask |= emit;
+            __syncwarp();
+            count = w.count;
+            emit = 0u;
+            if (count > kItemCap) {
+                // list full (rare): the appended items are exactly [0, lowest refused position); empty it and let the others retry
+                count = __reduce_min_sync(full, pos);
+                MRT_FLUSH_ITEMS();
+                MRT_REFRESH_BEST();
+                emit = __ballot_sync(full, lh != 0u);
+            }
+        }
+        // triangle phase: full chunks only
+        if (count >= 32u) {
+            do {
+                coop_triangle_pass<ANY>(s, w, t, count - 32u, 32u, lane);
+                count -= 32u;
+            } while (count >= 32u);
+            if (lane == 0) { w.count = count; }
+            __syncwarp();
+            if (count == 0u) { outmask = 0u; }
+            MRT_REFRESH_BEST();
+        } else {
+            busy = __ballot_sync(full, node_work);
+        }
+        // lanes that only wait for their items: force the triangle phase when enough of them pile up
+        if (__popc(hasmask & ~busy & outmask) >= s.tune_wait) { MRT_FLUSH_ITEMS(); MRT_REFRESH_BEST(); }
+    }
+#undef MRT_FLUSH_ITEMS
+#undef MRT_REFRESH_BEST
     if (overflow) { dc->overflow = 1; }
 }
+
+__global__ void __launch_bounds__(kWfThreads, 8) k_wf_extend(SceneDev s, Queues Q, int level, DeviceCounters *dc) { wf_traverse<false>(s, Q, level, dc); }
+__global__ void __launch_bounds__(kWfThreads, 8) k_wf_shadow(SceneDev s, Queues Q, DeviceCounters *dc) { wf_traverse<true>(s, Q, 0, dc); }
 
 // Shader::getCosineSampleHemisphere (Shader.cpp:188-216)
 MRT_D v3 cosine_sample_hemisphere(v3 normal, float uniformRandom1, float uniformRandom2) {
@@ -285,70 +477,6 @@ __global__ void __launch_bounds__(kWfThreads) k_wf_shade(SceneDev s, RenderParam
     if ((threadIdx.x & 31) == 0) {
         if (sh) { atomicAdd(&dc->rays_shadow, static_cast<unsigned long long>(sh)); }
         if (se) { atomicAdd(&dc->rays_secondary, static_cast<unsigned long long>(se)); }
-    }
-    if (overflow) { dc->overflow = 1; }
-}
-
-// ---- shadow: any-hit (Shader::shadowTrace, Shader.cpp:132-158); an unoccluded sample adds its share of Ld to the chain
-MRT_D void shadow_unoccluded(const Queues &Q, uint32_t i) {
-    const float4 cc = Q.s2[i];
-    const uint32_t tag = __float_as_uint(cc.w);
-    Chain *ch = Q.chains + (tag & 0x0fffffffu);
-    const uint32_t dz = (tag >> 28) & 7u;
-    atomicAdd(&ch->sum[dz][0], cc.x); atomicAdd(&ch->sum[dz][1], cc.y); atomicAdd(&ch->sum[dz][2], cc.z);
-    if (tag & 0x80000000u) { atomicOr(&ch->ldmask, 1u << dz); }
-}
-
-__global__ void __launch_bounds__(kWfThreads) k_wf_shadow(SceneDev s, Queues Q, DeviceCounters *dc) {
-    const uint32_t n = min(Q.counts[8], Q.cap_shadow);
-    const int lane = threadIdx.x & 31;
-    int overflow = 0;
-    bool has = false, exhausted = false;
-    uint32_t cur = 0;
-    Trav8 t;
-    while (true) {
-        const uint32_t idle = __ballot_sync(0xffffffffu, !has);
-        if (!exhausted && __popc(idle) > 32 - s.tune_refill) {
-            uint32_t base = 0;
-            if (lane == 0) { base = atomicAdd(&Q.counts[kCounterShadow], static_cast<uint32_t>(__popc(idle))); }
-            base = __shfl_sync(0xffffffffu, base, 0);
-            if (base + __popc(idle) >= n) { exhausted = true; }
-            if (!has) {
-                cur = base + __popc(idle & ((1u << lane) - 1u));
-                if (cur < n) {
-                    const float4 a = Q.s0[cur], c = Q.s1[cur];
-                    const v3 o = mk3(a.x, a.y, a.z), d = mk3(a.w, c.x, c.y);
-                    int sk, si;
-                    unpack_skip(__float_as_uint(c.w), sk, si);
-                    HitRec h;
-                    h.t = c.z; h.kind = HIT_NONE; h.idx = -1; h.u = 0.0f; h.v = 0.0f;
-                    const bool occluded = trace_ref_bvh<0>(s, o, d, true, sk, si, h, &overflow) || trace_ref_bvh<1>(s, o, d, true, sk, si, h, &overflow);
-                    if (!occluded) {
-                        if (s.n_bvh_prims > 0 && triangles_root_hit(s, o, d)) {
-                            trav8_init(t, o, d, sk == HIT_TRIANGLE ? si : -1, h.t);
-                            has = true;
-                        } else {
-                            shadow_unoccluded(Q, cur);
-                        }
-                    }
-                }
-            }
-        }
-        if (__ballot_sync(0xffffffffu, has) == 0u) {
-            if (exhausted) { break; }
-            continue;
-        }
-        if (has) {
-            while (true) {
-                if (!trav8_step<true>(s, t, &overflow)) {
-                    if (t.bestPrim < 0) { shadow_unoccluded(Q, cur); }
-                    MRT_STAT(atomicAdd(&g_stat_nodes, t.n_nodes); atomicAdd(&g_stat_tris, t.n_tris); atomicAdd(&g_stat_rays, 1ull);)
-                    has = false;
-                    break;
-                }
-                if (!exhausted && __popc(__activemask()) < s.tune_refill) { break; }
-            }
-        }
     }
     if (overflow) { dc->overflow = 1; }
 }

@@ -179,8 +179,10 @@ def test_stop_and_progress_polling(mrt):
     bm = np.zeros(1024 * 1024, np.int32)
     th = threading.Thread(target=lambda: r.renderFrame(bm))
     th.start()
-    time.sleep(0.3)
-    mid = r.getSample()
+    mid, deadline = 0, time.time() + 20.0
+    while mid == 0 and time.time() < deadline and th.is_alive():   # the first sample may wait for lazy CUDA module loading
+        time.sleep(0.05)
+        mid = r.getSample()
     r.stopRender()
     th.join(timeout=60)
     assert not th.is_alive()

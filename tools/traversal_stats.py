@@ -15,7 +15,8 @@ h = bench.round_down16(bench.HEIGHT_ASKED)
 obj, mtl, cam = bench.scene_files()
 scene = loaders.load_obj(obj, mtl).arrays()
 camera = loaders.load_camera(cam, np.float32(bench.WIDTH) / np.float32(h))
-r = mrt.Renderer(scene, camera, bench.WIDTH, h, 1, 1, capi.SHADER_PATHTRACER)
+shader = int(sys.argv[1]) if len(sys.argv) > 1 else capi.SHADER_PATHTRACER
+r = mrt.Renderer(scene, camera, bench.WIDTH, h, 1, 1, shader)
 L = capi.lib()
 out = (C.c_ulonglong * 3)()
 L.mrt_debug_traversal_stats(out, 1)
