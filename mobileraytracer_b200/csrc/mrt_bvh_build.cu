@@ -479,14 +479,16 @@ __global__ void k_collapse8(CollapseArgs a) {
     if (t.count[item.bin] <= ML) { kids[nk++] = item.bin; }
     else { kids[nk++] = t.left[item.bin]; kids[nk++] = t.right[item.bin]; }
     while (nk < 8) {
-        int best = -1; float bestA = -1.0f;
+        // open the child with the largest surface area; subtrees that would need their own wide node go first
+        // (lexicographic: adding a large constant to the area instead would swallow the area in fp32 rounding and
+        // always open the first child, i.e. walk down the left spine)
+        int best = -1; float bestA = -1.0f; bool bestBig = false;
         for (int k = 0; k < nk; ++k) {
             const int b = kids[k];
             if (t.count[b] <= 1) { continue; }   // a single primitive cannot be opened
             const float A = box_area(&t.lo[3ll * b], &t.hi[3ll * b]);
-            // prefer opening subtrees that would need their own wide node; ties by area
-            const float key = (t.count[b] > ML ? 1.0e30f : 0.0f) + A;
-            if (key > bestA) { bestA = key; best = k; }
+            const bool big = t.count[b] > ML;
+            if (best < 0 || (big && !bestBig) || (big == bestBig && A > bestA)) { bestA = A; best = k; bestBig = big; }
         }
         if (best < 0) { break; }
         const int b = kids[best];
