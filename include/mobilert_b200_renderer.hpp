@@ -1,0 +1,133 @@
+/*
+ * mobilert_b200_renderer.hpp — C++ adapter with MobileRT::Renderer's public surface (MobileRT/Renderer.hpp:41-63) on
+ * top of the C-ABI in mobilert_b200.h. Header-only; compiles inside the reference tree (it includes the reference's own
+ * headers) and is what System_dependent/Native/C_wrapper.cpp:207-232 and Android_JNI/JNI_layer.cpp:691-694 would
+ * construct instead of MobileRT::Renderer when Config::accelerator == ACC_B200.
+ *
+ * The reference keeps Sphere's fields, AreaLight::triangle_ and PointLight::position_ private without getters; the
+ * adapter reads them directly, so this translation unit is compiled with -fno-access-control (as oracle/ref_shim is),
+ * or the maintainer adds the four one-line getters named in INTEGRATION.md.
+ */
+#ifndef MOBILERT_B200_RENDERER_HPP
+#define MOBILERT_B200_RENDERER_HPP
+
+#include "mobilert_b200.h"
+
+#include "Components/Cameras/Orthographic.hpp"
+#include "Components/Cameras/Perspective.hpp"
+#include "Components/Lights/AreaLight.hpp"
+#include "Components/Lights/PointLight.hpp"
+#include "MobileRT/Camera.hpp"
+#include "MobileRT/Scene.hpp"
+
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+namespace MobileRT {
+
+class B200Renderer final {
+    mrt_handle *handle_ {nullptr};
+
+    static void put3(float *dst, const ::glm::vec3 &v) { dst[0] = v.x; dst[1] = v.y; dst[2] = v.z; }
+
+    static mrt_triangle flatten(const Triangle &t) {
+        mrt_triangle r;
+        put3(r.AC, t.getAC()); put3(r.AB, t.getAB()); put3(r.A, t.getA());
+        put3(r.nA, t.getNormalA()); put3(r.nB, t.getNormalB()); put3(r.nC, t.getNormalC());
+        const ::glm::vec2 a {t.getTexCoordA()}, b {t.getTexCoordB()}, c {t.getTexCoordC()};
+        r.tA[0] = a.x; r.tA[1] = a.y; r.tB[0] = b.x; r.tB[1] = b.y; r.tC[0] = c.x; r.tC[1] = c.y;
+        r.material = t.getMaterialIndex();
+        return r;
+    }
+
+    static mrt_camera_desc flatten(const Camera &camera, const ::glm::vec3 &lookAt, const ::glm::vec3 &up) {
+        mrt_camera_desc c;
+        ::std::memset(&c, 0, sizeof(c));
+        put3(c.position, camera.position_); put3(c.look_at, lookAt); put3(c.up, up);
+        if (const auto *p = dynamic_cast<const ::Components::Perspective *>(&camera)) {
+            c.kind = MRT_CAMERA_PERSPECTIVE;
+            // Perspective stores radians (Perspective.cpp:8-14); the C-ABI takes the constructor's degrees
+            c.a = p->getHFov() * 180.0F / 3.14159265358979323846F; c.b = p->getVFov() * 180.0F / 3.14159265358979323846F;
+        } else if (const auto *o = dynamic_cast<const ::Components::Orthographic *>(&camera)) {
+            c.kind = MRT_CAMERA_ORTHOGRAPHIC; c.a = o->getSizeH() * 2.0F; c.b = o->getSizeV() * 2.0F;
+        } else {
+            throw ::std::runtime_error("B200Renderer: unknown camera type");
+        }
+        return c;
+    }
+
+public:
+    /* Same inputs the front-ends hold right before they build Shader + Renderer (C_wrapper.cpp:76-203): the Scene
+     * (before it is moved into the Shader), the camera with its lookAt / up, the Config fields. */
+    B200Renderer(const Scene &scene, const Camera &camera, const ::glm::vec3 &lookAt, const ::glm::vec3 &up,
+                 ::std::int32_t width, ::std::int32_t height, ::std::int32_t samplesPixel, ::std::int32_t samplesLight,
+                 ::std::int32_t shader) {
+        ::std::vector<mrt_triangle> tris; tris.reserve(scene.triangles_.size());
+        for (const Triangle &t : scene.triangles_) { tris.push_back(flatten(t)); }
+        ::std::vector<mrt_sphere> spheres;
+        for (const Sphere &s : scene.spheres_) {
+            mrt_sphere r; put3(r.center, s.center_); r.sq_radius = s.sqRadius_; r.material = s.materialIndex_; spheres.push_back(r);
+        }
+        ::std::vector<mrt_plane> planes;
+        for (const Plane &p : scene.planes_) {
+            mrt_plane r; put3(r.normal, p.getNormal()); put3(r.point, p.getPoint()); r.material = p.getMaterialIndex(); planes.push_back(r);
+        }
+        ::std::vector<mrt_material> mats;
+        for (const Material &m : scene.materials_) {
+            mrt_material r; put3(r.Le, m.Le_); put3(r.Kd, m.Kd_); put3(r.Ks, m.Ks_); put3(r.Kt, m.Kt_); r.ior = m.refractiveIndice_; mats.push_back(r);
+        }
+        ::std::vector<mrt_light> lights;
+        for (const auto &l : scene.lights_) {
+            mrt_light r;
+            ::std::memset(&r, 0, sizeof(r));
+            put3(r.Le, l->radiance_.Le_);
+            if (const auto *a = dynamic_cast<const ::Components::AreaLight *>(l.get())) {
+                r.kind = MRT_LIGHT_AREA; r.triangle = flatten(a->triangle_);
+            } else if (const auto *p = dynamic_cast<const ::Components::PointLight *>(l.get())) {
+                r.kind = MRT_LIGHT_POINT; put3(r.position, p->position_);
+            } else {
+                throw ::std::runtime_error("B200Renderer: unknown light type");
+            }
+            lights.push_back(r);
+        }
+        mrt_scene_desc sd;
+        sd.triangles = tris.data(); sd.n_triangles = static_cast<int64_t>(tris.size());
+        sd.spheres = spheres.data(); sd.n_spheres = static_cast<int64_t>(spheres.size());
+        sd.planes = planes.data(); sd.n_planes = static_cast<int64_t>(planes.size());
+        sd.materials = mats.data(); sd.n_materials = static_cast<int64_t>(mats.size());
+        sd.lights = lights.data(); sd.n_lights = static_cast<int64_t>(lights.size());
+        const mrt_camera_desc cd = flatten(camera, lookAt, up);
+        mrt_render_desc rd;
+        ::std::memset(&rd, 0, sizeof(rd));
+        rd.width = width; rd.height = height; rd.samples_pixel = samplesPixel; rd.samples_light = samplesLight;
+        rd.shader = shader; rd.accelerator = MRT_ACC_B200; rd.pixel_sampler = MRT_SAMPLER_AUTO; rd.seed = 1u;
+        rd.depth_max_point[0] = rd.depth_max_point[1] = rd.depth_max_point[2] = 1.0F;   // C_wrapper.cpp:138
+        rd.device = -1;
+        if (mrt_create(&sd, &cd, &rd, nullptr, &handle_) != MRT_OK) {
+            // the front-ends catch ::std::exception around construction (C_wrapper.cpp:257-263, JNI_layer.cpp:706-715)
+            throw ::std::runtime_error(::std::string("B200Renderer: ") + mrt_last_error(nullptr));
+        }
+    }
+
+    B200Renderer(const B200Renderer &) = delete;
+    B200Renderer &operator=(const B200Renderer &) = delete;
+    ~B200Renderer() { mrt_destroy(handle_); }
+
+    /* Renderer::renderFrame (Renderer.cpp:53-88). numThreads has no meaning on the GPU. */
+    void renderFrame(::std::int32_t *bitmap, ::std::int32_t /*numThreads*/) {
+        const int rc = mrt_render_frame(handle_, bitmap);
+        if (rc != MRT_OK && rc != MRT_ERR_STOPPED) { throw ::std::runtime_error(::std::string("B200Renderer: ") + mrt_last_error(handle_)); }
+    }
+    /* Renderer::stopRender (Renderer.cpp:93-99) */
+    void stopRender() { mrt_stop(handle_); }
+    /* Renderer::getSample (Renderer.cpp:176-178) */
+    ::std::int32_t getSample() const { ::std::int32_t s = 0; mrt_get_sample(handle_, &s); return s; }
+    /* Renderer::getTotalCastedRays (Renderer.cpp:204-207) */
+    ::std::uint64_t getTotalCastedRays() const { ::std::uint64_t r = 0; mrt_get_total_rays(handle_, &r); return r; }
+};
+
+}  // namespace MobileRT
+
+#endif  // MOBILERT_B200_RENDERER_HPP

@@ -153,3 +153,23 @@ def test_partition_reduce_resolve_over_gloo_world2(tmp_path):
     out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
                           "--master-port", "29611", str(script)], env=env, capture_output=True, text=True, timeout=300)
     assert out.returncode == 0 and "GLOO_OK" in out.stdout, out.stdout[-2000:] + out.stderr[-2000:]
+
+
+def test_cpp_adapter_compiles_against_reference(tmp_path):
+    """include/mobilert_b200_renderer.hpp (the B200Renderer adapter of INTEGRATION.md) against the reference's own headers.
+    Needs /root/reference (this container only); the GPU box has no reference tree."""
+    import glob
+    import subprocess
+    ref = "/root/reference/app"
+    if not os.path.isdir(ref):
+        pytest.skip("reference tree not present")
+    tp = ref + "/third_party"
+    src = tmp_path / "adapter_check.cpp"
+    src.write_text('#include "mobilert_b200_renderer.hpp"\nint main() { return 0; }\n')
+    cmd = ["/usr/bin/g++", "-std=c++17", "-fsyntax-only", "-fno-access-control", "-w", "-I", os.path.join(ROOT, "include"), "-I", ref,
+           "-I", ref + "/System_dependent/Native", "-isystem", tp, "-isystem", tp + "/glm", "-isystem", tp + "/stb",
+           "-isystem", tp + "/pcg-cpp/include"]
+    for d in sorted(glob.glob(tp + "/boost/libs/*/include")):
+        cmd += ["-isystem", d]
+    r = subprocess.run(cmd + [str(src)], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-2000:]
