@@ -124,7 +124,14 @@ constexpr uint32_t kItemCap = 128;                        // leaf items per warp
 
 struct __align__(16) WarpShared {
     unsigned long long key[32];   // per lane: best hit so far, (float bits of t) << 32 | primitive id
+    unsigned long long key0[32];  // the key the ray started with: tbest of the plane / sphere pass (or the light distance), id 0
     float2 uv[32];                // barycentrics of that hit
+    // ray state that only the triangle phase and the retire step need lives here instead of in registers (the node step
+    // is register bound: at 64 registers it spilled its own operands, ncu SASS view of the first cooperative version)
+    float ox[32], oy[32], oz[32], dx[32], dy[32], dz[32];
+    int32_t skip[32];             // primitive id the ray leaves (Triangle.cpp:64), or -1
+    uint32_t cur[32];             // queue index of the lane's ray
+    uint32_t pre[32];             // packed plane / sphere hit found before the triangles (kind << 28 | idx)
     uint2 items[kItemCap];        // x = first triangle slot of the leaf, y = owner lane | triangle count << 8
     uint32_t count;               // items in the list
     uint32_t pad[3];
@@ -144,15 +151,14 @@ MRT_D void shadow_unoccluded(const Queues &Q, uint32_t i) {
 
 // The warp tests the leaves items[first, first + n), n <= 32, one per lane. Must be called by all 32 lanes.
 template <bool ANY>
-MRT_D void coop_triangle_pass(const SceneDev &s, WarpShared &w, const Trav8 &t, uint32_t first, uint32_t n, int lane) {
-    const uint32_t full = 0xffffffffu;
+MRT_D void coop_triangle_pass(const SceneDev &s, WarpShared &w, uint32_t first, uint32_t n, int lane) {
     const bool valid = static_cast<uint32_t>(lane) < n;
     const uint2 item = valid ? w.items[first + lane] : make_uint2(0u, static_cast<uint32_t>(lane));
     const int owner = static_cast<int>(item.y & 31u);
     const uint32_t cnt = item.y >> 8;        // 0 for a lane without an item
-    const v3 o = mk3(__shfl_sync(full, t.o.x, owner), __shfl_sync(full, t.o.y, owner), __shfl_sync(full, t.o.z, owner));
-    const v3 d = mk3(__shfl_sync(full, t.d.x, owner), __shfl_sync(full, t.d.y, owner), __shfl_sync(full, t.d.z, owner));
-    const int skip = __shfl_sync(full, t.skipPrim, owner);
+    const v3 o = mk3(w.ox[owner], w.oy[owner], w.oz[owner]);
+    const v3 d = mk3(w.dx[owner], w.dy[owner], w.dz[owner]);
+    const int skip = w.skip[owner];
     unsigned long long mykey = ~0ull;
     float bu = 0.0f, bv = 0.0f;
     if (cnt != 0u) {
@@ -198,13 +204,10 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
     uint32_t hasmask = 0u;           // lanes holding a ray (warp-uniform)
     uint32_t outmask = 0u;           // lanes that may own items in the list (warp-uniform)
     uint32_t busy = 0u;              // ballot of node_work (warp-uniform)
-    uint32_t cur = 0, count = 0;     // count: items in the warp's list (warp-uniform copy of w.count)
-    unsigned long long key0 = 0ull;  // the key the ray started with: tbest of the plane / sphere pass (or the light distance), id 0
-    HitRec h;
-    h.t = kRayLengthMax; h.kind = HIT_NONE; h.idx = -1; h.u = 0.0f; h.v = 0.0f;
+    uint32_t count = 0;              // items in the warp's list (warp-uniform copy of w.count)
     Trav8 t;
     TravMem tmem;
-    t.o = mk3(0.0f, 0.0f, 0.0f); t.d = mk3(0.0f, 0.0f, 1.0f); t.skipPrim = -1;
+    t.o = mk3(0.0f, 0.0f, 0.0f);
     t.ngroup = make_uint2(0u, 0u); t.sp = 0; t.tbest = 0.0f;
     MRT_STAT(t.n_nodes = 0u; t.n_tris = 0u;)
     if (lane == 0) { w.count = 0u; }
@@ -215,7 +218,7 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
     do {                                                                                          \
         while (count > 0u) {                                                                      \
             const uint32_t m_ = count < 32u ? count : 32u;                                        \
-            coop_triangle_pass<ANY>(s, w, t, count - m_, m_, lane);                               \
+            coop_triangle_pass<ANY>(s, w, count - m_, m_, lane);                               \
             count -= m_;                                                                          \
         }                                                                                         \
         if (lane == 0) { w.count = 0u; }                                                          \
@@ -227,7 +230,7 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
     do {                                                                                          \
         if (hasmask & lane_bit) {                                                                 \
             const unsigned long long k_ = w.key[lane];                                            \
-            if (ANY) { if (k_ != key0) { t.ngroup.y = 0u; t.sp = 0; node_work = false; } }        \
+            if (ANY) { if (k_ != w.key0[lane]) { t.ngroup.y = 0u; t.sp = 0; node_work = false; } }        \
             else { t.tbest = __uint_as_float(static_cast<uint32_t>(k_ >> 32)); }                  \
         }                                                                                         \
         busy = __ballot_sync(full, node_work);                                                    \
@@ -238,10 +241,15 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
         const uint32_t done = hasmask & ~busy & ~outmask;
         if (done) {
             if (done & lane_bit) {
-                const unsigned long long k = w.key[lane];
+                const unsigned long long k = w.key[lane], key0 = w.key0[lane];
+                const uint32_t cur = w.cur[lane];
                 if (ANY) {
                     if (k == key0) { shadow_unoccluded(Q, cur); }
                 } else {
+                    HitRec h;
+                    const uint32_t pre = w.pre[lane];
+                    h.t = __uint_as_float(static_cast<uint32_t>(key0 >> 32)); h.kind = static_cast<int>(pre >> 28);
+                    h.idx = h.kind == HIT_NONE ? -1 : static_cast<int>(pre & 0x0fffffffu); h.u = 0.0f; h.v = 0.0f;
                     if (k != key0) {
                         const int prim = static_cast<int>(static_cast<uint32_t>(k));
                         const float2 uv = w.uv[lane];
@@ -264,8 +272,9 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
             if (base + __popc(idle) >= n) { exhausted = true; }
             bool got = false;
             if (idle & lane_bit) {
-                cur = base + __popc(idle & (lane_bit - 1u));
+                const uint32_t cur = base + __popc(idle & (lane_bit - 1u));
                 if (cur < n) {
+                    HitRec h;
                     const float4 a = ANY ? Q.s0[cur] : Q.r0[b][cur], c = ANY ? Q.s1[cur] : Q.r1[b][cur];
                     const v3 o = mk3(a.x, a.y, a.z), d = mk3(a.w, c.x, c.y);
                     int sk, si;
@@ -281,8 +290,11 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
                     if (!occluded) {
                         if (s.n_bvh_prims > 0 && triangles_root_hit(s, o, d)) {
                             trav8_init(t, o, d, sk == HIT_TRIANGLE ? si : -1, h.t);
-                            key0 = static_cast<unsigned long long>(__float_as_uint(h.t)) << 32;
-                            w.key[lane] = key0;
+                            const unsigned long long key0 = static_cast<unsigned long long>(__float_as_uint(h.t)) << 32;
+                            w.key[lane] = key0; w.key0[lane] = key0;
+                            w.ox[lane] = o.x; w.oy[lane] = o.y; w.oz[lane] = o.z; w.dx[lane] = d.x; w.dy[lane] = d.y; w.dz[lane] = d.z;
+                            w.skip[lane] = sk == HIT_TRIANGLE ? si : -1;
+                            w.cur[lane] = cur; w.pre[lane] = pack_hit(h);
                             got = true; node_work = true;
                         } else if (ANY) {
                             shadow_unoccluded(Q, cur);
@@ -344,7 +356,7 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
         // triangle phase: full chunks only
         if (count >= 32u) {
             do {
-                coop_triangle_pass<ANY>(s, w, t, count - 32u, 32u, lane);
+                coop_triangle_pass<ANY>(s, w, count - 32u, 32u, lane);
                 count -= 32u;
             } while (count >= 32u);
             if (lane == 0) { w.count = count; }
