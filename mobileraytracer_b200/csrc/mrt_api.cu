@@ -218,7 +218,8 @@ int upload_scene(mrt_handle *h, const mrt_scene_desc &sc) {
     const char *bvh_env = std::getenv("MRT_B200_BVH");
     const char *leaf_env = std::getenv("MRT_B200_LEAF");   // triangles per leaf slot, 1..7 (tuning experiments)
     const uint32_t leaf = leaf_env ? static_cast<uint32_t>(std::atoi(leaf_env)) & 7u : 3u;
-    const uint32_t build_flags = ((bvh_env && std::strcmp(bvh_env, "lbvh") == 0) ? 0u : 1u) | (leaf << 8);
+    const char *fat_env = std::getenv("MRT_B200_FATLEAF");   // 1: never split a subtree that fits one leaf slot (tuning experiments)
+    const uint32_t build_flags = ((bvh_env && std::strcmp(bvh_env, "lbvh") == 0) ? 0u : 1u) | (leaf << 8) | ((fat_env && std::atoi(fat_env)) ? 2u : 0u);
     API_CUDA(h, build_bvh8(h->d_tris9.as<float>(), static_cast<int>(nprims), build_flags, st, &h->bvh));
     h->stats.build_ms = h->bvh.build_ms;
     h->stats.bvh_nodes = h->bvh.n_nodes;
@@ -352,7 +353,9 @@ int mrt_create(const mrt_scene_desc *scene, const mrt_camera_desc *camera, const
         if ((e = cudaMallocHost(reinterpret_cast<void **>(&h->h_pinned_bitmap), npix * sizeof(int32_t))) != cudaSuccess) { rc = cuda_fail(h, e, "pinned bitmap"); break; }
         h->pinned_bytes = npix * sizeof(int32_t);
         if (render->shader == MRT_SHADER_PATHTRACER) {
-            if ((e = wavefront_create(render->width, render->height, &h->wavefront)) != cudaSuccess) { rc = cuda_fail(h, e, "wavefront queues"); break; }
+            const char *be = std::getenv("MRT_B200_BATCH");   // samples traced together per wavefront pass
+            const int batch = std::max(1, std::min(be ? std::atoi(be) : 8, render->samples_pixel));
+            if ((e = wavefront_create(render->width, render->height, batch, &h->wavefront)) != cudaSuccess) { rc = cuda_fail(h, e, "wavefront queues"); break; }
         }
         if ((e = cudaStreamSynchronize(h->stream)) != cudaSuccess) { rc = cuda_fail(h, e, "create sync"); break; }
     } while (false);
@@ -410,11 +413,14 @@ int render_samples(mrt_handle *h, int32_t *d_bitmap, float4 *d_accum, int sample
     const int spp = h->rp.spp;
     bool stopped = false;
     if (h->rp.shader == MRT_SHADER_PATHTRACER) {
-        for (int s = sample_begin, k = 0; s < spp; s += sample_stride, ++k) {
+        const int batch = wavefront_batch(h->wavefront);
+        for (int s = sample_begin, k = 0; s < spp;) {
             if (h->stop.load()) { stopped = true; break; }
-            API_CUDA(h, wavefront_render_sample(h->wavefront, h->scene, h->camera, h->rp, h->d_inv_tile.as<int2>(), s, d_bitmap ? s + 1 : k + 1,
-                                                tg, h->d_counters.as<DeviceCounters>(), (h->flags & MRT_FLAG_SORT_BY_MATERIAL) != 0, &wt, &launches, st));
-            h->sample.store(s + 1);
+            int samples[kWfMaxBatch], avg_n[kWfMaxBatch], nb = 0;
+            for (; nb < batch && s < spp; s += sample_stride, ++k, ++nb) { samples[nb] = s; avg_n[nb] = d_bitmap ? s + 1 : k + 1; }
+            API_CUDA(h, wavefront_render_batch(h->wavefront, h->scene, h->camera, h->rp, h->d_inv_tile.as<int2>(), nb, samples, avg_n,
+                                               tg, h->d_counters.as<DeviceCounters>(), &wt, &launches, st));
+            h->sample.store(samples[nb - 1] + 1);
         }
     } else {
         const size_t depth = 4;   // samples in flight, so that mrt_stop() takes effect within a few samples
@@ -446,7 +452,7 @@ int render_samples(mrt_handle *h, int32_t *d_bitmap, float4 *d_accum, int sample
         h->stats.rays_primary = hc.rays_primary; h->stats.rays_shadow = hc.rays_shadow; h->stats.rays_secondary = hc.rays_secondary;
         h->stats.launches = launches;
         h->stats.rays_extend_traced = hc.extend_traced; h->stats.rays_shadow_traced = hc.shadow_traced;
-        const uint64_t per_class = h->rp.shader == MRT_SHADER_PATHTRACER ? launches / 33u * 6u : 0u;   // 33 launches per sample, of which 6 levels x (extend, shade, shadow)
+        const uint64_t per_class = h->rp.shader == MRT_SHADER_PATHTRACER ? wt.extend_launches : 0u;   // 6 levels x (extend, shade, shadow) per pass
         h->stats.extend_launches = per_class; h->stats.shade_launches = per_class; h->stats.shadow_launches = per_class;
     }
     h->total_rays.store(hc.rays_primary + hc.rays_shadow + hc.rays_secondary);

@@ -460,6 +460,7 @@ struct CollapseArgs {
     const WorkItem *in; int n_in; WorkItem *out; uint32_t *n_out;
     uint32_t max_nodes;
     int max_leaf;                 // primitives per leaf slot, 1..7
+    int fat_leaves;               // 1: a subtree that fits one leaf slot is never opened further
     int *error;
 };
 
@@ -488,6 +489,7 @@ __global__ void k_collapse8(CollapseArgs a) {
             if (t.count[b] <= 1) { continue; }   // a single primitive cannot be opened
             const float A = box_area(&t.lo[3ll * b], &t.hi[3ll * b]);
             const bool big = t.count[b] > ML;
+            if (!big && a.fat_leaves) { continue; }
             if (best < 0 || (big && !bestBig) || (big == bestBig && A > bestA)) { bestA = A; best = k; bestBig = big; }
         }
         if (best < 0) { break; }
@@ -745,6 +747,7 @@ cudaError_t build_bvh8(const float *d_tris9, int n, uint32_t flags, cudaStream_t
     CollapseArgs a;
     a.t = t; a.n = n; a.sorted = va; a.tris9 = d_tris9; a.nodes = out->nodes; a.tri_geom = out->tri_geom;
     a.node_counter = d_node_counter; a.tri_counter = d_tri_counter; a.n_out = d_nout; a.max_nodes = max_nodes; a.error = d_error;
+    a.fat_leaves = (flags & 2u) ? 1 : 0;
     a.max_leaf = static_cast<int>((flags >> 8) & 7u) ? static_cast<int>((flags >> 8) & 7u) : 3;
     WorkItem *qi = q0.as<WorkItem>(), *qo = q1.as<WorkItem>();
     uint32_t n_in = 1, levels = 0;

@@ -36,7 +36,8 @@ struct Queues {
     float4 *hit;                 // t u v (kind << 28 | idx)
     float4 *s0, *s1, *s2;        // shadow queue: o.xyz d.x | d.y d.z dist skip | c.xyz (chain | depth << 28)
     Chain *chains;
-    uint32_t *counts;            // [0..7] ray count per level, [8] shadow count, [9] chain pool size, [10..17] chain pool size after each level
+    uint32_t *counts;            // [0..7] ray count per level, [8] shadow count, [9] chain pool size, [10..17] chain pool size after each level,
+                                 // [20],[21] work counters, [24..32] root-chain range boundaries of the samples of a batch
     uint32_t cap_rays, cap_shadow, cap_chains;
 };
 
@@ -46,6 +47,7 @@ struct Wavefront {
     Queues q {};
     int width = 0, height = 0;
     int sm_count = 148;
+    int batch = 1;
     std::vector<void *> allocs;
     std::vector<WfMark> marks;        // one event after every launch; the class says what ran before it
     std::vector<cudaEvent_t> pool;
@@ -101,6 +103,8 @@ __global__ void __launch_bounds__(kWfThreads) k_wf_generate(Queues Q, CameraRec 
 
 // the chain pool starts right after the root chains
 __global__ void k_wf_begin_levels(Queues Q) { Q.counts[9] = Q.counts[0]; }
+// camera paths of batch sample i occupy root chains [counts[24 + i], counts[24 + i + 1])
+__global__ void k_wf_mark_roots(Queues Q, int i) { Q.counts[24 + i + 1] = Q.counts[0]; }
 
 // ---- extend / shadow: persistent traversal kernels --------------------------------------------------------------
 // One CTA of 4 warps per scheduling slot, resident for the whole launch. A lane that has finished its ray fetches the
@@ -529,9 +533,9 @@ __global__ void k_wf_finalize_level(Queues Q, int level) {
 }
 
 // camera paths -> pixels (Renderer.cpp:149-157)
-__global__ void k_wf_resolve_roots(Queues Q, int avg_n, FrameTargets tg) {
-    const uint32_t n = min(Q.counts[0], Q.cap_rays);
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+__global__ void k_wf_resolve_roots(Queues Q, int batch_index, int avg_n, FrameTargets tg) {
+    const uint32_t begin = min(Q.counts[24 + batch_index], Q.cap_rays), end = min(Q.counts[24 + batch_index + 1], Q.cap_rays);
+    for (uint32_t i = begin + blockIdx.x * blockDim.x + threadIdx.x; i < end; i += gridDim.x * blockDim.x) {
         const Chain *ch = Q.chains + i;
         const v3 rgb = chain_total(ch);
         const int pix = ch->parent_depth;
@@ -561,15 +565,18 @@ static WavefrontHost *host_of(Wavefront *w) { return w; }
 
 #define WF_TRY(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { return e_; } } while (0)
 
-cudaError_t wavefront_create(int width, int height, Wavefront **out) {
+int wavefront_batch(const Wavefront *w) { return w->batch; }
+
+cudaError_t wavefront_create(int width, int height, int batch, Wavefront **out) {
     Wavefront *w = new Wavefront;
     *out = w;
     w->width = width; w->height = height;
+    w->batch = batch < 1 ? 1 : (batch > kWfMaxBatch ? kWfMaxBatch : batch);
     WavefrontHost *hst = w;
     int dev = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&hst->sm_count, cudaDevAttrMultiProcessorCount, dev);
-    const size_t P = static_cast<size_t>(width) * height;
+    const size_t P = static_cast<size_t>(width) * height * static_cast<size_t>(w->batch);
     Queues &q = w->q;
     q.cap_rays = static_cast<uint32_t>(std::min<size_t>(2 * P + 1024, 0x0ffffff0u));
     q.cap_shadow = q.cap_rays;
@@ -581,7 +588,7 @@ cudaError_t wavefront_create(int width, int height, Wavefront **out) {
     WF_TRY(wf_alloc(w, &q.hit, q.cap_rays));
     WF_TRY(wf_alloc(w, &q.s0, q.cap_shadow)); WF_TRY(wf_alloc(w, &q.s1, q.cap_shadow)); WF_TRY(wf_alloc(w, &q.s2, q.cap_shadow));
     WF_TRY(wf_alloc(w, &q.chains, q.cap_chains));
-    WF_TRY(wf_alloc(w, &q.counts, 32));
+    WF_TRY(wf_alloc(w, &q.counts, 40));
     return cudaSuccess;
 }
 
@@ -613,7 +620,7 @@ cudaError_t wavefront_collect_times(Wavefront *w, WavefrontTimes *t) {
         float ms = 0.0f;
         WF_TRY(cudaEventElapsedTime(&ms, hst->marks[i - 1].ev, hst->marks[i].ev));
         switch (hst->marks[i].cls) {
-            case WF_EXTEND: t->extend_ms += ms; break;
+            case WF_EXTEND: t->extend_ms += ms; t->extend_launches += 1; break;
             case WF_SHADE: t->shade_ms += ms; break;
             case WF_SHADOW: t->shadow_ms += ms; break;
             default: t->other_ms += ms; break;
@@ -624,21 +631,26 @@ cudaError_t wavefront_collect_times(Wavefront *w, WavefrontTimes *t) {
     return cudaSuccess;
 }
 
-cudaError_t wavefront_render_sample(Wavefront *w, const SceneDev &s, const CameraRec &cam, const RenderParams &rp, const int2 *d_tile_origin,
-                                    int sample, int avg_n, FrameTargets tg, DeviceCounters *dc, bool sort_by_material,
-                                    WavefrontTimes *times, uint64_t *launches, cudaStream_t st) {
-    (void)sort_by_material; (void)times;
+cudaError_t wavefront_render_batch(Wavefront *w, const SceneDev &s, const CameraRec &cam, const RenderParams &rp, const int2 *d_tile_origin,
+                                   int n_samples, const int *samples, const int *avg_n, FrameTargets tg, DeviceCounters *dc,
+                                   WavefrontTimes *times, uint64_t *launches, cudaStream_t st) {
+    (void)times;
     WavefrontHost *hst = host_of(w);
     Queues &Q = w->q;
+    if (n_samples < 1 || n_samples > hst->batch) { return cudaErrorInvalidValue; }
     const int grid = hst->sm_count * 8;
     WF_TRY(wf_mark(hst, -1, st));
-    WF_TRY(cudaMemsetAsync(Q.counts, 0, 32 * sizeof(uint32_t), st));
+    WF_TRY(cudaMemsetAsync(Q.counts, 0, 40 * sizeof(uint32_t), st));
     const int patches = kNumberOfTiles * ((rp.bsx + 7) / 8) * ((rp.bsy + 3) / 4);
     if (patches == 0) { return cudaSuccess; }
-    k_wf_generate<<<(patches + kWfThreads / 32 - 1) / (kWfThreads / 32), kWfThreads, 0, st>>>(Q, cam, rp, s.pixel_table, d_tile_origin, sample, dc);
+    for (int i = 0; i < n_samples; ++i) {
+        k_wf_generate<<<(patches + kWfThreads / 32 - 1) / (kWfThreads / 32), kWfThreads, 0, st>>>(Q, cam, rp, s.pixel_table, d_tile_origin, samples[i], dc);
+        k_wf_mark_roots<<<1, 1, 0, st>>>(Q, i);
+        *launches += 2;
+    }
     k_wf_begin_levels<<<1, 1, 0, st>>>(Q);
     WF_TRY(wf_mark(hst, WF_OTHER, st));
-    *launches += 2;
+    *launches += 1;
     for (int level = 0; level < kLevels; ++level) {
         k_wf_extend<<<grid, kWfThreads, 0, st>>>(s, Q, level, dc);
         WF_TRY(wf_mark(hst, WF_EXTEND, st));
@@ -653,8 +665,10 @@ cudaError_t wavefront_render_sample(Wavefront *w, const SceneDev &s, const Camer
         k_wf_finalize_level<<<grid, kWfThreads, 0, st>>>(Q, level);
         *launches += 1;
     }
-    k_wf_resolve_roots<<<grid, kWfThreads, 0, st>>>(Q, avg_n, tg);
-    *launches += 1;
+    for (int i = 0; i < n_samples; ++i) {
+        k_wf_resolve_roots<<<grid, kWfThreads, 0, st>>>(Q, i, avg_n[i], tg);
+        *launches += 1;
+    }
     WF_TRY(wf_mark(hst, WF_OTHER, st));
     return cudaGetLastError();
 }

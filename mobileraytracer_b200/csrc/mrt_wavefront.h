@@ -7,14 +7,19 @@ namespace mrt {
 
 struct Wavefront;   // opaque: queues, chain records, counters
 
-struct WavefrontTimes { double extend_ms = 0, shadow_ms = 0, shade_ms = 0, other_ms = 0; };
+struct WavefrontTimes { double extend_ms = 0, shadow_ms = 0, shade_ms = 0, other_ms = 0; uint64_t extend_launches = 0; };
 
-cudaError_t wavefront_create(int width, int height, Wavefront **out);
+constexpr int kWfMaxBatch = 8;
+// batch: samples of every pixel traced together in one pass (1..kWfMaxBatch); the queues are sized for it
+cudaError_t wavefront_create(int width, int height, int batch, Wavefront **out);
+int wavefront_batch(const Wavefront *w);
 void wavefront_destroy(Wavefront *w);
-// One sample of every pixel. avg_n = the sample number used by the integer running average (bitmap target).
-cudaError_t wavefront_render_sample(Wavefront *w, const SceneDev &s, const CameraRec &cam, const RenderParams &rp, const int2 *d_tile_origin,
-                                    int sample, int avg_n, FrameTargets tg, DeviceCounters *d_counters, bool sort_by_material,
-                                    WavefrontTimes *times, uint64_t *launches, cudaStream_t st);
+// n_samples (<= batch) samples of every pixel in one pass over the queues. samples[i] = sample index (selects the jitter
+// draws), avg_n[i] = the sample number used by the integer running average (bitmap target); the samples are resolved
+// into the targets in the order given, one after the other, so the 8-bit running average stays exact.
+cudaError_t wavefront_render_batch(Wavefront *w, const SceneDev &s, const CameraRec &cam, const RenderParams &rp, const int2 *d_tile_origin,
+                                   int n_samples, const int *samples, const int *avg_n, FrameTargets tg, DeviceCounters *d_counters,
+                                   WavefrontTimes *times, uint64_t *launches, cudaStream_t st);
 
 // After the stream has been synchronised: adds the device time of every launch since the last call, per kernel class.
 cudaError_t wavefront_collect_times(Wavefront *w, WavefrontTimes *times);
