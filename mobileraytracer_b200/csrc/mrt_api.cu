@@ -38,6 +38,7 @@ struct DevMem {
 }  // namespace
 
 struct mrt_handle {
+    uint32_t roots_per_sample = 0;   // valid pixels of one sample (wavefront path slots)
     int device = 0;
     cudaStream_t stream = nullptr;       // stream in use (own_stream unless mrt_set_stream installed the caller's)
     cudaStream_t own_stream = nullptr;
@@ -49,7 +50,7 @@ struct mrt_handle {
     uint32_t flags = 0;
     Bvh8 bvh {};
     DevMem d_tris9, d_tri_shade, d_sphere_nodes, d_spheres, d_plane_nodes, d_planes, d_materials, d_lights;
-    DevMem d_tile, d_shader_table, d_static_halton, d_static_mt, d_inv_tile, d_bitmap, d_accum, d_counters, d_scratch;
+    DevMem d_tile, d_shader_table, d_static_halton, d_static_mt, d_inv_tile, d_tile_base, d_bitmap, d_accum, d_counters, d_scratch;
     std::vector<int> plane_slot_of_id, sphere_slot_of_id;
     int32_t *h_pinned_bitmap = nullptr;
     size_t pinned_bytes = 0;
@@ -257,6 +258,7 @@ int upload_tables(mrt_handle *h, const mrt_render_desc &rd, const mrt_sampler_ta
     if (need_mt && !p_smt) { make_mt_table(smt, kArraySize, rd.seed * 4u + 3u); p_smt = smt.data(); }
     // Renderer::renderScene's tile -> first pixel mapping (Renderer.cpp:125-133), integer for integer
     std::vector<int2> origin(kNumberOfTiles, make_int2(0, 0));
+    std::vector<uint32_t> tile_base(kNumberOfTiles + 1, 0u);   // valid pixels before each tile (the wavefront's deterministic path slots)
     {
         const int w = rd.width, hgt = rd.height, bsx = h->rp.bsx, bsy = h->rp.bsy;
         if (bsx > 0 && bsy > 0) {
@@ -268,6 +270,16 @@ int upload_tables(mrt_handle *h, const mrt_render_desc &rd, const mrt_sampler_ta
                 const int startY = ((pixel / w) * bsy) % hgt;
                 origin[static_cast<size_t>(k)] = make_int2(pixel % w, startY);   // startX = (pixel + y * w) % w
             }
+            for (int k = 0; k < kNumberOfTiles; ++k) {
+                // a pixel index past the end of the image is dropped (tile_pixel, mrt_shade.cuh); those are the last ones of the tile
+                uint32_t valid = 0;
+                for (int ly = 0; ly < bsy; ++ly) {
+                    const long long first = static_cast<long long>(origin[static_cast<size_t>(k)].y + ly) * w + origin[static_cast<size_t>(k)].x;
+                    const long long room = static_cast<long long>(resolution) - first;
+                    valid += static_cast<uint32_t>(room <= 0 ? 0 : (room < bsx ? room : bsx));
+                }
+                tile_base[static_cast<size_t>(k) + 1] = tile_base[static_cast<size_t>(k)] + valid;
+            }
         }
     }
     API_CUDA(h, h->d_tile.upload(p_tile, kNumberOfTiles * sizeof(float), st));
@@ -275,6 +287,8 @@ int upload_tables(mrt_handle *h, const mrt_render_desc &rd, const mrt_sampler_ta
     API_CUDA(h, h->d_static_halton.upload(p_sh, kArraySize * sizeof(float), st));
     if (need_mt) { API_CUDA(h, h->d_static_mt.upload(p_smt, kArraySize * sizeof(float), st)); }
     API_CUDA(h, h->d_inv_tile.upload(origin.data(), origin.size() * sizeof(int2), st));
+    API_CUDA(h, h->d_tile_base.upload(tile_base.data(), tile_base.size() * sizeof(uint32_t), st));
+    h->roots_per_sample = tile_base[kNumberOfTiles];
     API_CUDA(h, cudaStreamSynchronize(st));
     SceneDev &s = h->scene;
     s.tile_order = h->d_tile.as<float>(); s.shader_table = h->d_shader_table.as<float>(); s.static_halton = h->d_static_halton.as<float>();
@@ -418,7 +432,7 @@ int render_samples(mrt_handle *h, int32_t *d_bitmap, float4 *d_accum, int sample
             if (h->stop.load()) { stopped = true; break; }
             int samples[kWfMaxBatch], avg_n[kWfMaxBatch], nb = 0;
             for (; nb < batch && s < spp; s += sample_stride, ++k, ++nb) { samples[nb] = s; avg_n[nb] = d_bitmap ? s + 1 : k + 1; }
-            API_CUDA(h, wavefront_render_batch(h->wavefront, h->scene, h->camera, h->rp, h->d_inv_tile.as<int2>(), nb, samples, avg_n,
+            API_CUDA(h, wavefront_render_batch(h->wavefront, h->scene, h->camera, h->rp, h->d_inv_tile.as<int2>(), h->d_tile_base.as<uint32_t>(), h->roots_per_sample, nb, samples, avg_n,
                                                tg, h->d_counters.as<DeviceCounters>(), &wt, &launches, st));
             h->sample.store(samples[nb - 1] + 1);
         }

@@ -34,7 +34,7 @@ MRT_D void generate_ray(const CameraRec &c, float u, float v, float du, float dv
 MRT_D int tile_patches_x(const RenderParams &rp) { return (rp.bsx + 7) >> 3; }
 MRT_D int tile_patches_y(const RenderParams &rp) { return (rp.bsy + 3) >> 2; }
 MRT_D bool tile_pixel(const RenderParams &rp, const int2 *__restrict__ tile_origin, int patch, int lane, int sample,
-                      int &x, int &y, int &pix, uint32_t &q) {
+                      int &x, int &y, int &pix, uint32_t &q, int *tile_out = nullptr, int *rank_out = nullptr) {
     const int ptx = tile_patches_x(rp), per_tile = ptx * tile_patches_y(rp);
     const int k = patch / per_tile;
     if (k >= kNumberOfTiles) { return false; }
@@ -47,6 +47,8 @@ MRT_D bool tile_pixel(const RenderParams &rp, const int2 *__restrict__ tile_orig
     if (pix >= rp.width * rp.height) { return false; }        // the reference writes out of bounds here; this library does not
     q = (static_cast<uint32_t>(sample) * kNumberOfTiles + static_cast<uint32_t>(k)) * static_cast<uint32_t>(rp.bsx * rp.bsy) +
         static_cast<uint32_t>(ly * rp.bsx + lx);
+    if (tile_out) { *tile_out = k; }
+    if (rank_out) { *rank_out = ly * rp.bsx + lx; }   // valid pixels of a tile are a prefix of its row-major order (pix is monotone in it)
     return true;
 }
 

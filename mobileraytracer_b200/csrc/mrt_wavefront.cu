@@ -70,13 +70,15 @@ MRT_D uint32_t queue_push(uint32_t *counter) {
 
 // ---- generate: Renderer::renderScene's jitter + Camera::generateRay (Renderer.cpp:130-141) ---------------------------
 __global__ void __launch_bounds__(kWfThreads) k_wf_generate(Queues Q, CameraRec cam, RenderParams rp, const float *__restrict__ pixel_table,
-                                                            const int2 *__restrict__ tile_origin, int sample, DeviceCounters *dc) {
+                                                            const int2 *__restrict__ tile_origin, const uint32_t *__restrict__ tile_base,
+                                                            uint32_t slot_base, int sample, DeviceCounters *dc) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int patch = blockIdx.x * (kWfThreads / 32) + warp;
     uint32_t q = 0;
     int x, y, pix;
     RayCounters rc = {0u, 0u, 0u};
-    if (tile_pixel(rp, tile_origin, patch, lane, sample, x, y, pix, q)) {
+    int tile, rank;
+    if (tile_pixel(rp, tile_origin, patch, lane, sample, x, y, pix, q, &tile, &rank)) {
         const float invImgWidth = 1.0f / static_cast<float>(rp.width), invImgHeight = 1.0f / static_cast<float>(rp.height);
         const float pixelWidth = 0.5f / static_cast<float>(rp.width), pixelHeight = 0.5f / static_cast<float>(rp.height);
         const float u = static_cast<float>(x) * invImgWidth, v = static_cast<float>(y) * invImgHeight;
@@ -84,7 +86,8 @@ __global__ void __launch_bounds__(kWfThreads) k_wf_generate(Queues Q, CameraRec 
         if (pixel_table != nullptr) { r1 = __ldg(pixel_table + ((2u * q) & kArrayMask)); r2 = __ldg(pixel_table + ((2u * q + 1u) & kArrayMask)); }
         v3 o, d;
         generate_ray(cam, u, v, (r1 - 0.5f) * 2.0f * pixelWidth, (r2 - 0.5f) * 2.0f * pixelHeight, o, d);
-        const uint32_t slot = queue_push(&Q.counts[0]);
+        // deterministic slot: no atomics (64 k same-address atomics per sample made this kernel latency bound, profiles/)
+        const uint32_t slot = slot_base + __ldg(tile_base + tile) + static_cast<uint32_t>(rank);
         // the root chain of camera path `slot` is chain `slot`
         Chain *c = Q.chains + slot;
         float4 *cz = reinterpret_cast<float4 *>(c);
@@ -102,9 +105,11 @@ __global__ void __launch_bounds__(kWfThreads) k_wf_generate(Queues Q, CameraRec 
 }
 
 // the chain pool starts right after the root chains
-__global__ void k_wf_begin_levels(Queues Q) { Q.counts[9] = Q.counts[0]; }
-// camera paths of batch sample i occupy root chains [counts[24 + i], counts[24 + i + 1])
-__global__ void k_wf_mark_roots(Queues Q, int i) { Q.counts[24 + i + 1] = Q.counts[0]; }
+// camera paths of batch sample i occupy root chains [counts[24 + i], counts[24 + i + 1]) = i * roots_per_sample ...
+__global__ void k_wf_begin_levels(Queues Q, uint32_t n_samples, uint32_t roots_per_sample) {
+    Q.counts[0] = n_samples * roots_per_sample; Q.counts[9] = n_samples * roots_per_sample;
+    for (uint32_t i = 0; i <= n_samples; ++i) { Q.counts[24 + i] = i * roots_per_sample; }
+}
 
 // ---- extend / shadow: persistent traversal kernels --------------------------------------------------------------
 // One CTA of 4 warps per scheduling slot, resident for the whole launch. A lane that has finished its ray fetches the
@@ -505,16 +510,32 @@ __global__ void k_wf_end_level(Queues Q, int level, DeviceCounters *dc) {
     Q.counts[10 + level] = min(Q.counts[9], Q.cap_chains);   // chain pool size after this level
 }
 
-MRT_D v3 chain_total(const Chain *ch) {
+// The whole 128-byte record comes in as eight independent 16-byte loads (one dependent scalar load after the other made
+// the resolve / finalize kernels latency bound, profiles/r1_resolve_s28_*), then the reference's rule is applied.
+struct ChainRegs { float4 v[8]; };
+MRT_D ChainRegs chain_load(const Chain *ch) {
+    ChainRegs r;
+    const float4 *p = reinterpret_cast<const float4 *>(ch);
+#pragma unroll
+    for (int k = 0; k < 8; ++k) { r.v[k] = p[k]; }
+    return r;
+}
+MRT_D v3 chain_total(const ChainRegs &r, int32_t &parent, int32_t &parent_depth) {
+    // layout of Chain: floats 0..17 sum[6][3], 18..20 emit, 21 ldmask, 22 ended_on_light, 23 parent, 24 parent_depth
+    const float f[28] = {r.v[0].x, r.v[0].y, r.v[0].z, r.v[0].w, r.v[1].x, r.v[1].y, r.v[1].z, r.v[1].w, r.v[2].x, r.v[2].y, r.v[2].z, r.v[2].w,
+                         r.v[3].x, r.v[3].y, r.v[3].z, r.v[3].w, r.v[4].x, r.v[4].y, r.v[4].z, r.v[4].w, r.v[5].x, r.v[5].y, r.v[5].z, r.v[5].w,
+                         r.v[6].x, r.v[6].y, r.v[6].z, r.v[6].w};
+    const uint32_t ldmask = __float_as_uint(f[21]), ended = __float_as_uint(f[22]);
+    parent = __float_as_int(f[23]); parent_depth = __float_as_int(f[24]);
     int last = kLevels - 1;
     bool with_emit = true;
-    if (ch->ended_on_light) {
-        const uint32_t m = ch->ldmask;
-        if (m) { last = __ffs(m) - 1; with_emit = false; }
-    }
+    if (ended && ldmask) { last = __ffs(ldmask) - 1; with_emit = false; }
     v3 t = mk3(0.0f, 0.0f, 0.0f);
-    for (int k = 0; k <= last; ++k) { t = t + mk3(ch->sum[k][0], ch->sum[k][1], ch->sum[k][2]); }
-    if (with_emit) { t = t + mk3(ch->emit[0], ch->emit[1], ch->emit[2]); }
+#pragma unroll
+    for (int k = 0; k < kLevels; ++k) {
+        if (k <= last) { t = t + mk3(f[3 * k], f[3 * k + 1], f[3 * k + 2]); }
+    }
+    if (with_emit) { t = t + mk3(f[18], f[19], f[20]); }
     return t;
 }
 
@@ -522,10 +543,10 @@ MRT_D v3 chain_total(const Chain *ch) {
 __global__ void k_wf_finalize_level(Queues Q, int level) {
     const uint32_t begin = level == 0 ? Q.counts[0] : Q.counts[10 + level - 1], end = Q.counts[10 + level];
     for (uint32_t i = begin + blockIdx.x * blockDim.x + threadIdx.x; i < end; i += gridDim.x * blockDim.x) {
-        const Chain *ch = Q.chains + i;
-        const v3 t = chain_total(ch);
-        Chain *p = Q.chains + ch->parent;
-        const int dz = ch->parent_depth - 1;
+        int32_t parent, parent_depth;
+        const v3 t = chain_total(chain_load(Q.chains + i), parent, parent_depth);
+        Chain *p = Q.chains + parent;
+        const int dz = parent_depth - 1;
         if (t.x != 0.0f) { atomicAdd(&p->sum[dz][0], t.x); }
         if (t.y != 0.0f) { atomicAdd(&p->sum[dz][1], t.y); }
         if (t.z != 0.0f) { atomicAdd(&p->sum[dz][2], t.z); }
@@ -536,9 +557,8 @@ __global__ void k_wf_finalize_level(Queues Q, int level) {
 __global__ void k_wf_resolve_roots(Queues Q, int batch_index, int avg_n, FrameTargets tg) {
     const uint32_t begin = min(Q.counts[24 + batch_index], Q.cap_rays), end = min(Q.counts[24 + batch_index + 1], Q.cap_rays);
     for (uint32_t i = begin + blockIdx.x * blockDim.x + threadIdx.x; i < end; i += gridDim.x * blockDim.x) {
-        const Chain *ch = Q.chains + i;
-        const v3 rgb = chain_total(ch);
-        const int pix = ch->parent_depth;
+        int32_t parent, pix;
+        const v3 rgb = chain_total(chain_load(Q.chains + i), parent, pix);
         if (tg.bitmap != nullptr) { tg.bitmap[pix] = incremental_avg(rgb, tg.bitmap[pix], avg_n); }
         if (tg.accum != nullptr) {
             float4 a = tg.accum[pix];
@@ -632,7 +652,7 @@ cudaError_t wavefront_collect_times(Wavefront *w, WavefrontTimes *t) {
 }
 
 cudaError_t wavefront_render_batch(Wavefront *w, const SceneDev &s, const CameraRec &cam, const RenderParams &rp, const int2 *d_tile_origin,
-                                   int n_samples, const int *samples, const int *avg_n, FrameTargets tg, DeviceCounters *dc,
+                                   const uint32_t *d_tile_base, uint32_t roots_per_sample, int n_samples, const int *samples, const int *avg_n, FrameTargets tg, DeviceCounters *dc,
                                    WavefrontTimes *times, uint64_t *launches, cudaStream_t st) {
     (void)times;
     WavefrontHost *hst = host_of(w);
@@ -643,12 +663,13 @@ cudaError_t wavefront_render_batch(Wavefront *w, const SceneDev &s, const Camera
     WF_TRY(cudaMemsetAsync(Q.counts, 0, 40 * sizeof(uint32_t), st));
     const int patches = kNumberOfTiles * ((rp.bsx + 7) / 8) * ((rp.bsy + 3) / 4);
     if (patches == 0) { return cudaSuccess; }
+    if (static_cast<unsigned long long>(roots_per_sample) * static_cast<unsigned long long>(n_samples) > Q.cap_rays) { return cudaErrorInvalidValue; }
     for (int i = 0; i < n_samples; ++i) {
-        k_wf_generate<<<(patches + kWfThreads / 32 - 1) / (kWfThreads / 32), kWfThreads, 0, st>>>(Q, cam, rp, s.pixel_table, d_tile_origin, samples[i], dc);
-        k_wf_mark_roots<<<1, 1, 0, st>>>(Q, i);
-        *launches += 2;
+        k_wf_generate<<<(patches + kWfThreads / 32 - 1) / (kWfThreads / 32), kWfThreads, 0, st>>>(Q, cam, rp, s.pixel_table, d_tile_origin, d_tile_base,
+                                                                                              static_cast<uint32_t>(i) * roots_per_sample, samples[i], dc);
+        *launches += 1;
     }
-    k_wf_begin_levels<<<1, 1, 0, st>>>(Q);
+    k_wf_begin_levels<<<1, 1, 0, st>>>(Q, static_cast<uint32_t>(n_samples), roots_per_sample);
     WF_TRY(wf_mark(hst, WF_OTHER, st));
     *launches += 1;
     for (int level = 0; level < kLevels; ++level) {

@@ -17,8 +17,9 @@ void wavefront_destroy(Wavefront *w);
 // n_samples (<= batch) samples of every pixel in one pass over the queues. samples[i] = sample index (selects the jitter
 // draws), avg_n[i] = the sample number used by the integer running average (bitmap target); the samples are resolved
 // into the targets in the order given, one after the other, so the 8-bit running average stays exact.
+// d_tile_base[k] = valid pixels in tiles 0..k-1 (device, 257 entries), roots_per_sample = d_tile_base[256]: camera path slots are deterministic.
 cudaError_t wavefront_render_batch(Wavefront *w, const SceneDev &s, const CameraRec &cam, const RenderParams &rp, const int2 *d_tile_origin,
-                                   int n_samples, const int *samples, const int *avg_n, FrameTargets tg, DeviceCounters *d_counters,
+                                   const uint32_t *d_tile_base, uint32_t roots_per_sample, int n_samples, const int *samples, const int *avg_n, FrameTargets tg, DeviceCounters *d_counters,
                                    WavefrontTimes *times, uint64_t *launches, cudaStream_t st);
 
 // After the stream has been synchronised: adds the device time of every launch since the last call, per kernel class.
