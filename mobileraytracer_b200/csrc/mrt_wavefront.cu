@@ -18,6 +18,9 @@ namespace mrt {
 
 constexpr int kLevels = kRayDepthMax;          // depths 1..6 are traced; a depth-7 ray contributes nothing (PathTracer.cpp:24-26)
 constexpr int kWfThreads = 128;
+#ifndef MRT_SHADE_MIN_BLOCKS
+#define MRT_SHADE_MIN_BLOCKS 8
+#endif
 
 struct __align__(16) Chain {
     float sum[kLevels][3];   // [depth-1]: throughput-weighted Ld and folded child chains of that vertex
@@ -399,18 +402,19 @@ MRT_D v3 cosine_sample_hemisphere(v3 normal, float uniformRandom1, float uniform
 }
 
 // ---- shade: PathTracer::shade for every hit of the level; emits shadow rays and the next level's rays --------------
-__global__ void __launch_bounds__(kWfThreads) k_wf_shade(SceneDev s, RenderParams rp, Queues Q, int level, DeviceCounters *dc) {
+__global__ void __launch_bounds__(kWfThreads, MRT_SHADE_MIN_BLOCKS) k_wf_shade(SceneDev s, RenderParams rp, Queues Q, int level, DeviceCounters *dc) {
     const int b = level & 1, nb = b ^ 1;
     const uint32_t n = min(Q.counts[level], Q.cap_rays);
     RayCounters rc = {0u, 0u, 0u};
     int overflow = 0;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        // hit and ray records are independent loads: issue all five before the first use (most rays hit something)
         const float4 hq = Q.hit[i];
+        const float4 a = Q.r0[b][i], c1 = Q.r1[b][i], c2 = Q.r2[b][i], c3 = Q.r3[b][i];
         const uint32_t packed = __float_as_uint(hq.w);
         HitRec h;
         h.t = hq.x; h.u = hq.y; h.v = hq.z; h.kind = static_cast<int>(packed >> 28); h.idx = static_cast<int>(packed & 0x0fffffffu);
         if (h.kind == HIT_NONE) { continue; }                      // Shader.cpp:122: no intersection, rgb stays 0
-        const float4 a = Q.r0[b][i], c1 = Q.r1[b][i], c2 = Q.r2[b][i], c3 = Q.r3[b][i];
         const v3 o = mk3(a.x, a.y, a.z), d = mk3(a.w, c1.x, c1.y), T = mk3(c2.x, c2.y, c2.z);
         const int depth = __float_as_int(c1.w);
         const uint32_t chain = __float_as_uint(c2.w);
@@ -675,7 +679,7 @@ cudaError_t wavefront_render_batch(Wavefront *w, const SceneDev &s, const Camera
     for (int level = 0; level < kLevels; ++level) {
         k_wf_extend<<<grid, kWfThreads, 0, st>>>(s, Q, level, dc);
         WF_TRY(wf_mark(hst, WF_EXTEND, st));
-        k_wf_shade<<<grid, kWfThreads, 0, st>>>(s, rp, Q, level, dc);
+        k_wf_shade<<<hst->sm_count * MRT_SHADE_MIN_BLOCKS, kWfThreads, 0, st>>>(s, rp, Q, level, dc);
         WF_TRY(wf_mark(hst, WF_SHADE, st));
         k_wf_shadow<<<grid, kWfThreads, 0, st>>>(s, Q, dc);
         WF_TRY(wf_mark(hst, WF_SHADOW, st));
