@@ -285,6 +285,9 @@ def run_b200(args, height):
             "kernel_ms_per_frame": {"extend": ext_ms / args.steps, "shadow": sh_ms / args.steps, "shade": shade_ms / args.steps, "other": other_ms / args.steps},
             "rays_per_frame": {"total_all_gpus": rays_frame, "primary": st["rays_primary"], "shadow": st["rays_shadow"], "secondary": st["rays_secondary"],
                                "extend_traced": st["rays_extend_traced"], "shadow_traced": st["rays_shadow_traced"]},
+            "kernel_grays_per_s": {"extend_closest_hit": ext_rays / (ext_ms * 1e-3) / 1e9 if ext_ms > 0 else None,
+                                   "shadow_any_hit": sh_rays / (sh_ms * 1e-3) / 1e9 if sh_ms > 0 else None,
+                                   "note": "rays traversed by the kernel / summed CUDA-event time of its launches, all ranks' average"},
             "grays_per_s_primary_plus_shadow": (st["rays_primary"] + st["rays_shadow"]) * world * args.steps / (total_ms * 1e-3) / 1e9,
             "scene": {"triangles": n_tri, "area_lights": n_lights, "bvh_nodes": stats0["bvh_nodes"], "bvh_bytes": stats0["bvh_bytes"],
                       "build_ms": stats0["build_ms"], "upload_ms": stats0["upload_ms"]},

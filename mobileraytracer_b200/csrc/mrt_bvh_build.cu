@@ -246,7 +246,10 @@ __global__ void k_refit(const uint32_t *__restrict__ sorted, const float *__rest
 //     (left before right), which is all the 8-wide collapse needs. Replaces the reference's single-threaded
 //     10-bucket + full-sweep SAH build (BVH.hpp:160-283, 396-439); the topology differs, the hit results do not.
 // ---------------------------------------------------------------------------------------------------------
-constexpr int SAH_BINS = 16;
+#ifndef MRT_SAH_BINS
+#define MRT_SAH_BINS 16
+#endif
+constexpr int SAH_BINS = MRT_SAH_BINS;
 constexpr int SAH_BIN_WORDS = 7;                      // ordered min xyz, ordered max xyz, count
 constexpr int SAH_NODE_WORDS = 3 * SAH_BINS * SAH_BIN_WORDS;
 constexpr int SAH_RANK_SPLIT_DEPTH = 36;              // from this depth on, halve by arrival order so that depth stays < 64
