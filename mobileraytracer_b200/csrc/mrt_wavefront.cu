@@ -343,6 +343,17 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
                 if (!(t.ngroup.y & 0xff000000u)) { t.ngroup = top; --t.sp; }
                 if (!trav8_node_core(s, t, tmem, tbase, lh, m0, m1, &overflow)) { t.ngroup.y = 0u; t.sp = 0; lh = 0u; }
                 node_work = (t.ngroup.y & 0xff000000u) != 0u || t.sp > 0;
+#ifndef MRT_NO_NODE_PREFETCH
+                if (t.ngroup.y & 0xff000000u) {
+                    // the node this lane visits next is known now: pull it into L1 while the warp does the list / triangle work
+                    const uint32_t nbit = 31u - __clz(t.ngroup.y);
+                    const uint32_t nslot = (nbit - 24u) ^ (t.octinv4 & 0xffu);
+                    const uint32_t nrel = __popc(t.ngroup.y & ((1u << nslot) - 1u) & 0xffu);
+                    const char *np = reinterpret_cast<const char *>(s.nodes) + 80ull * (t.ngroup.x + nrel);
+                    asm volatile("prefetch.global.L1 [%0];" :: "l"(np));
+                    asm volatile("prefetch.global.L1 [%0];" :: "l"(np + 64));
+                }
+#endif
             }
         }
         // append the hit leaves to the warp's list: one shared-memory atomic per lane that hit a leaf
