@@ -165,7 +165,9 @@ const char *mrt_last_error(mrt_handle *h);
 /* Per-ray ground-truth access for parity tests (what Shader::rayTrace's geometric part, Shader.cpp:86-111, and
  * Shader::shadowTrace, :132-158, compute). HOST arrays. origin_kind/origin_idx give the primitive a ray leaves
  * (self-hit skip, Triangle.cpp:64, Plane.cpp:39); shadow_dist[i] >= 0 selects any-hit semantics.
- * out_kind: 0 miss, 1 plane, 2 sphere, 3 triangle, 4 light; out_idx indexes the arrays given to mrt_create. */
+ * out_kind: 0 miss, 1 plane, 2 sphere, 3 triangle, 4 light; out_idx indexes the arrays given to mrt_create.
+ * For shadow rays out_kind is 1 when occluded, 0 when not. A PathTracer handle answers through the same persistent
+ * extend / shadow kernels its frames use (n up to the queue capacity), any other handle through the per-thread traversal. */
 int mrt_trace_rays(mrt_handle *h, int64_t n, const float *origins, const float *directions,
                    const int32_t *origin_kind, const int32_t *origin_idx, const float *shadow_dist,
                    float *out_t, int32_t *out_kind, int32_t *out_idx, int32_t *out_material, float *out_normal);

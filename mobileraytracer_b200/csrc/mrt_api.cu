@@ -593,7 +593,12 @@ int mrt_trace_rays(mrt_handle *h, int64_t n, const float *origins, const float *
     API_CUDA(h, tmp.get(&d_t, N)); API_CUDA(h, tmp.get(&d_kind, N)); API_CUDA(h, tmp.get(&d_idx, N)); API_CUDA(h, tmp.get(&d_mat, N));
     if (out_normal) { API_CUDA(h, tmp.get(&d_n, 3 * N)); API_CUDA(h, cudaMemsetAsync(d_n, 0, 3 * N * sizeof(float), st)); }
     API_CUDA(h, cudaMemsetAsync(h->d_counters.p, 0, sizeof(DeviceCounters), st));
-    API_CUDA(h, launch_trace_rays(h->scene, n, d_o, d_d, d_ok, d_oi, d_sd, d_t, d_kind, d_idx, d_mat, d_n, h->d_counters.as<DeviceCounters>(), st));
+    // a PathTracer handle answers through its own persistent extend / shadow kernels, any other through the per-thread traversal
+    if (h->wavefront && wavefront_capacity(h->wavefront) >= static_cast<uint64_t>(n)) {
+        API_CUDA(h, wavefront_trace_rays(h->wavefront, h->scene, n, d_o, d_d, d_ok, d_oi, d_sd, d_t, d_kind, d_idx, d_mat, d_n, h->d_counters.as<DeviceCounters>(), st));
+    } else {
+        API_CUDA(h, launch_trace_rays(h->scene, n, d_o, d_d, d_ok, d_oi, d_sd, d_t, d_kind, d_idx, d_mat, d_n, h->d_counters.as<DeviceCounters>(), st));
+    }
     DeviceCounters hc {};
     API_CUDA(h, cudaMemcpyAsync(out_t, d_t, N * 4, cudaMemcpyDeviceToHost, st));
     API_CUDA(h, cudaMemcpyAsync(out_kind, d_kind, N * 4, cudaMemcpyDeviceToHost, st));

@@ -606,6 +606,7 @@ static WavefrontHost *host_of(Wavefront *w) { return w; }
 #define WF_TRY(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { return e_; } } while (0)
 
 int wavefront_batch(const Wavefront *w) { return w->batch; }
+uint64_t wavefront_capacity(const Wavefront *w) { return w->q.cap_rays < w->q.cap_shadow ? w->q.cap_rays : w->q.cap_shadow; }
 
 cudaError_t wavefront_create(int width, int height, int batch, Wavefront **out) {
     Wavefront *w = new Wavefront;
@@ -725,3 +726,78 @@ extern "C" int mrt_debug_traversal_stats(unsigned long long out[3], int reset) {
     return 0;
 }
 #endif
+
+// ---- per-ray ground truth through the wavefront kernels (mrt_trace_rays on a PathTracer handle) ------------------------
+// The parity tests compare these results with the reference ray by ray, so that the persistent extend / shadow kernels
+// themselves (not only the per-thread traversal of the megakernel) are pinned bit for bit.
+namespace mrt {
+
+__global__ void k_wf_test_fill(Queues Q, int64_t n, const float *__restrict__ o, const float *__restrict__ d, const int32_t *__restrict__ okind,
+                               const int32_t *__restrict__ oidx, const float *__restrict__ sdist) {
+    const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+    if (i >= n) { return; }
+    const int sk = okind ? okind[i] : HIT_NONE, si = oidx ? oidx[i] : -1;
+    const uint32_t skip = pack_skip(sk, si);
+    if (sdist != nullptr && sdist[i] >= 0.0f) {
+        const uint32_t slot = atomicAdd(&Q.counts[8], 1u);
+        chain_init(Q.chains + slot, -1, static_cast<int32_t>(i));
+        Q.s0[slot] = make_float4(o[3 * i], o[3 * i + 1], o[3 * i + 2], d[3 * i]);
+        Q.s1[slot] = make_float4(d[3 * i + 1], d[3 * i + 2], sdist[i], __uint_as_float(skip));
+        Q.s2[slot] = make_float4(1.0f, 0.0f, 0.0f, __uint_as_float(slot));     // an unoccluded ray leaves 1 in sum[0][0] of its chain
+    } else {
+        const uint32_t slot = atomicAdd(&Q.counts[0], 1u);
+        Q.r0[0][slot] = make_float4(o[3 * i], o[3 * i + 1], o[3 * i + 2], d[3 * i]);
+        Q.r1[0][slot] = make_float4(d[3 * i + 1], d[3 * i + 2], __uint_as_float(skip), __int_as_float(1));
+        Q.r3[0][slot] = make_float4(__uint_as_float(static_cast<uint32_t>(i)), 0.0f, 0.0f, 0.0f);
+    }
+}
+
+__global__ void k_wf_test_gather(SceneDev s, Queues Q, float *out_t, int32_t *out_kind, int32_t *out_idx, int32_t *out_mat, float *out_normal) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < Q.counts[0]) {
+        const float4 a = Q.r0[0][i], c1 = Q.r1[0][i], hq = Q.hit[i];
+        const uint32_t dst = __float_as_uint(Q.r3[0][i].x), packed = __float_as_uint(hq.w);
+        const v3 ro = mk3(a.x, a.y, a.z), rd = mk3(a.w, c1.x, c1.y);
+        HitRec h;
+        h.t = hq.x; h.u = hq.y; h.v = hq.z; h.kind = static_cast<int>(packed >> 28); h.idx = h.kind == HIT_NONE ? -1 : static_cast<int>(packed & 0x0fffffffu);
+        int idx = h.idx, mat = -1;
+        v3 nrm = mk3(0.0f, 1.0f, 0.0f);
+        if (h.kind != HIT_NONE) {
+            Surface sf;
+            resolve_surface(s, ro, rd, h, sf);
+            nrm = sf.normal;
+            if (h.kind == HIT_PLANE) { idx = s.planes[h.idx].id; mat = s.planes[h.idx].material; }
+            else if (h.kind == HIT_SPHERE) { idx = s.spheres[h.idx].id; mat = s.spheres[h.idx].material; }
+            else if (h.kind == HIT_TRIANGLE) { mat = __float_as_int(reinterpret_cast<const float4 *>(s.tri_shade + h.idx)[3].w); }
+        }
+        out_t[dst] = h.t; out_kind[dst] = h.kind; out_idx[dst] = idx; out_mat[dst] = mat;
+        if (out_normal) { out_normal[3 * dst] = nrm.x; out_normal[3 * dst + 1] = nrm.y; out_normal[3 * dst + 2] = nrm.z; }
+    }
+    if (i < Q.counts[9]) {   // counts[9]: shadow rays of this test (saved before the shadow queue counter is consumed)
+        const Chain *ch = Q.chains + i;
+        const uint32_t dst = static_cast<uint32_t>(ch->parent_depth);
+        const bool occluded = !(ch->sum[0][0] > 0.0f);
+        out_t[dst] = occluded ? 0.0f : Q.s1[i].z;
+        out_kind[dst] = occluded ? 1 : 0; out_idx[dst] = -1; out_mat[dst] = -1;
+    }
+}
+
+__global__ void k_wf_test_save_counts(Queues Q) { Q.counts[9] = Q.counts[8]; }
+
+cudaError_t wavefront_trace_rays(Wavefront *w, const SceneDev &s, int64_t n, const float *d_o, const float *d_d, const int32_t *d_okind,
+                                 const int32_t *d_oidx, const float *d_sdist, float *d_t, int32_t *d_kind, int32_t *d_idx, int32_t *d_mat,
+                                 float *d_normal, DeviceCounters *dc, cudaStream_t st) {
+    Queues &Q = w->q;
+    if (n < 0 || static_cast<uint64_t>(n) > Q.cap_rays || static_cast<uint64_t>(n) > Q.cap_shadow) { return cudaErrorInvalidValue; }
+    if (n == 0) { return cudaSuccess; }
+    WF_TRY(cudaMemsetAsync(Q.counts, 0, 40 * sizeof(uint32_t), st));
+    const int blocks = static_cast<int>((n + 255) / 256), grid = w->sm_count * 8;
+    k_wf_test_fill<<<blocks, 256, 0, st>>>(Q, n, d_o, d_d, d_okind, d_oidx, d_sdist);
+    k_wf_test_save_counts<<<1, 1, 0, st>>>(Q);
+    k_wf_extend<<<grid, kWfThreads, 0, st>>>(s, Q, 0, dc);
+    k_wf_shadow<<<grid, kWfThreads, 0, st>>>(s, Q, dc);
+    k_wf_test_gather<<<blocks, 256, 0, st>>>(s, Q, d_t, d_kind, d_idx, d_mat, d_normal);
+    return cudaGetLastError();
+}
+
+}  // namespace mrt

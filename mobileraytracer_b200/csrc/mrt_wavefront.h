@@ -13,6 +13,7 @@ constexpr int kWfMaxBatch = 8;
 // batch: samples of every pixel traced together in one pass (1..kWfMaxBatch); the queues are sized for it
 cudaError_t wavefront_create(int width, int height, int batch, Wavefront **out);
 int wavefront_batch(const Wavefront *w);
+uint64_t wavefront_capacity(const Wavefront *w);   // rays one pass can hold
 void wavefront_destroy(Wavefront *w);
 // n_samples (<= batch) samples of every pixel in one pass over the queues. samples[i] = sample index (selects the jitter
 // draws), avg_n[i] = the sample number used by the integer running average (bitmap target); the samples are resolved
@@ -21,6 +22,11 @@ void wavefront_destroy(Wavefront *w);
 cudaError_t wavefront_render_batch(Wavefront *w, const SceneDev &s, const CameraRec &cam, const RenderParams &rp, const int2 *d_tile_origin,
                                    const uint32_t *d_tile_base, uint32_t roots_per_sample, int n_samples, const int *samples, const int *avg_n, FrameTargets tg, DeviceCounters *d_counters,
                                    WavefrontTimes *times, uint64_t *launches, cudaStream_t st);
+
+// Per-ray results through the extend / shadow kernels themselves (test entry; same outputs as launch_trace_rays). n <= queue capacity.
+cudaError_t wavefront_trace_rays(Wavefront *w, const SceneDev &s, int64_t n, const float *d_o, const float *d_d, const int32_t *d_okind,
+                                 const int32_t *d_oidx, const float *d_sdist, float *d_t, int32_t *d_kind, int32_t *d_idx, int32_t *d_mat,
+                                 float *d_normal, DeviceCounters *dc, cudaStream_t st);
 
 // After the stream has been synchronised: adds the device time of every launch since the last call, per kernel class.
 cudaError_t wavefront_collect_times(Wavefront *w, WavefrontTimes *times);

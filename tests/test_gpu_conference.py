@@ -189,3 +189,39 @@ def test_stop_and_progress_polling(mrt):
     assert 0 < mid < 4000 and r.getSample() < 4000
     assert (bm != 0).any()
     r.close()
+
+
+@pytest.mark.parametrize("shader", [2, 0])
+def test_conference_incoherent_rays_match_reference(mrt, ref, conf, shader):
+    """Secondary-ray shaped work: 200 k rays from random points inside the room in random directions (closest hit, some
+    leaving a triangle they must skip) and 200 k shadow rays with random lengths (any hit), ray by ray against the
+    reference's BVH walk. shader=2: the handle is a PathTracer, so mrt_trace_rays answers through the persistent
+    cooperative extend / shadow kernels of the wavefront (the bench's hot kernels); shader=0: per-thread traversal."""
+    obj, mtl, cam = conf
+    w, h = 64, 64
+    r = ref.RefRenderer(w, h, 3, -1, obj=obj, mtl=mtl, cam=cam)
+    g = H.gpu_from_ref(ref, r, -1, shader, w, h, cam_file=cam)
+    rng = np.random.default_rng(11)
+    n = 200_000
+    o = (rng.uniform(-1, 1, (n, 3)) * np.array([850.0, 380.0, 1350.0]) + np.array([0.0, 400.0, 0.0])).astype(np.float32)
+    d = rng.normal(size=(n, 3))
+    d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(np.float32)
+    kind = np.where(rng.uniform(size=n) < 0.1, 3, 0).astype(np.int32)
+    idx = np.where(kind == 3, rng.integers(0, r.n_tri, n), -1).astype(np.int32)
+    a, b = r.trace(o, d, kind, idx), g.traceRays(o, d, kind, idx)
+    same = (a["kind"] == b["kind"]) & (a["idx"] == b["idx"])
+    ties = ~same & (a["t"] == b["t"])
+    assert same.mean() >= 0.9999, (same.mean(), int(ties.sum()), int((~same).sum()))
+    assert ((~same) & ~ties).sum() == 0, "a different primitive is only acceptable at exactly the same distance"
+    assert np.array_equal(a["t"][same], b["t"][same]), "t must be bit identical"
+    surf = same & (a["kind"] == 3)
+    assert np.array_equal(a["normal"][surf], b["normal"][surf]) and np.array_equal(a["mat"][surf], b["mat"][surf])
+    assert (a["kind"] != 0).mean() > 0.9          # the room is closed: nearly every ray hits something
+    # any hit: occlusion flags must agree exactly (which occluder is found first is free)
+    dist = rng.uniform(50.0, 2500.0, n).astype(np.float32)
+    sa, sb = r.trace(o, d, kind, idx, dist), g.traceRays(o, d, kind, idx, dist)
+    occ_ref, occ_gpu = sa["kind"] != 0, sb["kind"] != 0
+    assert 0.2 < occ_ref.mean() < 0.98
+    assert np.array_equal(occ_ref, occ_gpu), int((occ_ref != occ_gpu).sum())
+    g.close()
+    r.close()
