@@ -50,6 +50,10 @@ typedef struct mrt_light {
     float Le[3];
 } mrt_light;
 
+/* MobileRT/Texture.hpp: a decoded image exactly as stb_image returned it to Texture::createTexture (Texture.cpp:58-118):
+ * `channels` (1..4) bytes per texel, rows top to bottom. Texture::loadColor (Texture.cpp:37-48) reads bytes index..index+2. */
+typedef struct mrt_texture { const uint8_t *pixels; int32_t width, height, channels; } mrt_texture;
+
 /* MobileRT/Scene.hpp:20-27 flattened. The library copies everything at mrt_create; the caller may free at once. */
 typedef struct mrt_scene_desc {
     const mrt_triangle *triangles; int64_t n_triangles;
@@ -57,6 +61,11 @@ typedef struct mrt_scene_desc {
     const mrt_plane *planes;       int64_t n_planes;
     const mrt_material *materials; int64_t n_materials;
     const mrt_light *lights;       int64_t n_lights;
+    /* optional (may be NULL / 0): Material::texture_ (Material.hpp:43). material_texture[m] = index into textures or -1.
+     * A triangle hit whose interpolated texture coordinates are both >= 0 takes Kd from its material's texture
+     * (Shader::rayTrace, Shader.cpp:113-121). */
+    const mrt_texture *textures;   int64_t n_textures;
+    const int32_t *material_texture;
 } mrt_scene_desc;
 
 enum { MRT_CAMERA_PERSPECTIVE = 0, MRT_CAMERA_ORTHOGRAPHIC = 1 };

@@ -75,8 +75,20 @@ public:
             mrt_plane r; put3(r.normal, p.getNormal()); put3(r.point, p.getPoint()); r.material = p.getMaterialIndex(); planes.push_back(r);
         }
         ::std::vector<mrt_material> mats;
+        ::std::vector<mrt_texture> textures;          // Material::texture_ (Material.hpp:43), shared images listed once
+        ::std::vector<int32_t> materialTexture;
         for (const Material &m : scene.materials_) {
             mrt_material r; put3(r.Le, m.Le_); put3(r.Kd, m.Kd_); put3(r.Ks, m.Ks_); put3(r.Kt, m.Kt_); r.ior = m.refractiveIndice_; mats.push_back(r);
+            int32_t tex {-1};
+            if (m.texture_.isValid()) {
+                const uint8_t *pixels {m.texture_.image_};
+                for (size_t k {0}; k < textures.size(); ++k) { if (textures[k].pixels == pixels) { tex = static_cast<int32_t>(k); } }
+                if (tex < 0) {
+                    tex = static_cast<int32_t>(textures.size());
+                    textures.push_back(mrt_texture {pixels, m.texture_.width_, m.texture_.height_, m.texture_.channels_});
+                }
+            }
+            materialTexture.push_back(tex);
         }
         ::std::vector<mrt_light> lights;
         for (const auto &l : scene.lights_) {
@@ -93,6 +105,8 @@ public:
             lights.push_back(r);
         }
         mrt_scene_desc sd;
+        ::std::memset(&sd, 0, sizeof(sd));
+        sd.textures = textures.data(); sd.n_textures = static_cast<int64_t>(textures.size()); sd.material_texture = materialTexture.data();
         sd.triangles = tris.data(); sd.n_triangles = static_cast<int64_t>(tris.size());
         sd.spheres = spheres.data(); sd.n_spheres = static_cast<int64_t>(spheres.size());
         sd.planes = planes.data(); sd.n_planes = static_cast<int64_t>(planes.size());

@@ -29,7 +29,13 @@ assert LIGHT.itemsize == 128
 class SceneDesc(C.Structure):
     _fields_ = [("triangles", C.c_void_p), ("n_triangles", C.c_int64), ("spheres", C.c_void_p), ("n_spheres", C.c_int64),
                 ("planes", C.c_void_p), ("n_planes", C.c_int64), ("materials", C.c_void_p), ("n_materials", C.c_int64),
-                ("lights", C.c_void_p), ("n_lights", C.c_int64)]
+                ("lights", C.c_void_p), ("n_lights", C.c_int64),
+                ("textures", C.c_void_p), ("n_textures", C.c_int64), ("material_texture", C.c_void_p)]
+
+
+class Texture(C.Structure):
+    """mrt_texture: decoded image as stb_image returns it (rows top to bottom, `channels` bytes per texel)."""
+    _fields_ = [("pixels", C.c_void_p), ("width", C.c_int32), ("height", C.c_int32), ("channels", C.c_int32)]
 
 
 class CameraDesc(C.Structure):

@@ -50,7 +50,7 @@ struct mrt_handle {
     uint32_t flags = 0;
     Bvh8 bvh {};
     DevMem d_tris9, d_tri_shade, d_sphere_nodes, d_spheres, d_plane_nodes, d_planes, d_materials, d_lights;
-    DevMem d_tile, d_shader_table, d_static_halton, d_static_mt, d_inv_tile, d_tile_base, d_bitmap, d_accum, d_counters, d_scratch;
+    DevMem d_tile, d_shader_table, d_static_halton, d_static_mt, d_inv_tile, d_tile_base, d_textures, d_texels, d_bitmap, d_accum, d_counters, d_scratch;
     std::vector<int> plane_slot_of_id, sphere_slot_of_id;
     int32_t *h_pinned_bitmap = nullptr;
     size_t pinned_bytes = 0;
@@ -171,7 +171,25 @@ int upload_scene(mrt_handle *h, const mrt_scene_desc &sc) {
         std::memset(&m, 0, sizeof(m));
         for (int k = 0; k < 3; ++k) { m.Le[k] = sc.materials[i].Le[k]; m.Kd[k] = sc.materials[i].Kd[k]; m.Ks[k] = sc.materials[i].Ks[k]; m.Kt[k] = sc.materials[i].Kt[k]; }
         m.ior = sc.materials[i].ior;
+        m.texture = -1;
+        if (sc.material_texture != nullptr && sc.n_textures > 0) {
+            const int32_t tx = sc.material_texture[i];
+            if (tx >= sc.n_textures) { return fail(h, MRT_ERR_INVALID, "material texture index out of range"); }
+            m.texture = tx < 0 ? -1 : tx;
+        }
     }
+    // textures: one byte buffer + a record per texture
+    std::vector<TextureRec> texrecs(static_cast<size_t>(sc.n_textures > 0 ? sc.n_textures : 1));
+    std::vector<uint8_t> texels;
+    for (int64_t i = 0; i < sc.n_textures; ++i) {
+        const mrt_texture &tx = sc.textures[i];
+        if (!tx.pixels || tx.width <= 0 || tx.height <= 0 || tx.channels < 1 || tx.channels > 4) { return fail(h, MRT_ERR_INVALID, "bad texture"); }
+        const size_t bytes = static_cast<size_t>(tx.width) * tx.height * tx.channels;
+        if (texels.size() + bytes > 0xfffffff0ull) { return fail(h, MRT_ERR_INVALID, "textures too large"); }
+        texrecs[static_cast<size_t>(i)] = TextureRec{static_cast<uint32_t>(texels.size()), tx.width, tx.height, tx.channels, static_cast<uint32_t>(bytes)};
+        texels.insert(texels.end(), tx.pixels, tx.pixels + bytes);
+    }
+    texels.resize(texels.size() + 16, 0);   // loadColor reads index + 2 without a bound (Texture.cpp:42-46): keep that read inside the buffer
     // planes and spheres: reference-layout BVHs built on the host
     std::vector<HostBox> boxes;
     std::vector<RefNode> pnodes, snodes;
@@ -204,6 +222,8 @@ int upload_scene(mrt_handle *h, const mrt_scene_desc &sc) {
     API_CUDA(h, h->d_tri_shade.upload(shade.data(), shade.size() * sizeof(TriShade), st));
     API_CUDA(h, h->d_lights.upload(lights.data(), lights.size() * sizeof(LightRec), st));
     API_CUDA(h, h->d_materials.upload(mats.data(), mats.size() * sizeof(MaterialRec), st));
+    API_CUDA(h, h->d_textures.upload(texrecs.data(), texrecs.size() * sizeof(TextureRec), st));
+    API_CUDA(h, h->d_texels.upload(texels.data(), texels.size(), st));
     API_CUDA(h, h->d_plane_nodes.upload(pnodes.data(), pnodes.size() * sizeof(RefNode), st));
     API_CUDA(h, h->d_planes.upload(planes.data(), planes.size() * sizeof(PlaneRec), st));
     API_CUDA(h, h->d_sphere_nodes.upload(snodes.data(), snodes.size() * sizeof(RefNode), st));
@@ -242,6 +262,7 @@ int upload_scene(mrt_handle *h, const mrt_scene_desc &sc) {
     s.sphere_nodes = h->d_sphere_nodes.as<RefNode>(); s.spheres = h->d_spheres.as<SphereRec>(); s.n_spheres = static_cast<int32_t>(sc.n_spheres);
     s.plane_nodes = h->d_plane_nodes.as<RefNode>(); s.planes = h->d_planes.as<PlaneRec>(); s.n_planes = static_cast<int32_t>(sc.n_planes);
     s.materials = h->d_materials.as<MaterialRec>(); s.n_materials = static_cast<int32_t>(sc.n_materials);
+    s.textures = h->d_textures.as<TextureRec>(); s.texels = h->d_texels.as<uint8_t>(); s.n_textures = static_cast<int32_t>(sc.n_textures);
     s.lights = h->d_lights.as<LightRec>(); s.n_lights = static_cast<int32_t>(nl);
     return MRT_OK;
 }

@@ -77,6 +77,7 @@ struct Surface {
     v3 point, normal;
     v3 Le, Kd, Ks, Kt;
     float ior;
+    int32_t texture;             // the material's texture or -1
     int32_t skipKind, skipIdx;   // the primitive a ray leaving this surface must skip (Ray::primitive_)
 };
 
@@ -84,6 +85,20 @@ MRT_D void load_material(const SceneDev &s, int m, Surface &sf) {
     const float4 *mp = reinterpret_cast<const float4 *>(s.materials + m);
     const float4 a = __ldg(mp), b = __ldg(mp + 1), c = __ldg(mp + 2), d = __ldg(mp + 3);
     sf.Le = mk3(a.x, a.y, a.z); sf.Kd = mk3(a.w, b.x, b.y); sf.Ks = mk3(b.z, b.w, c.x); sf.Kt = mk3(c.y, c.z, c.w); sf.ior = d.x;
+    sf.texture = __float_as_int(d.y);
+}
+
+// Texture::loadColor (Texture.cpp:37-48): nearest texel, no wrap (the loader already took fract() of the coordinates,
+// OBJLoader.cpp:193-212, Utils.cpp:177-180), bytes index..index+2 whatever the channel count. The reference reads past
+// the image when a coordinate reaches 1.0; here the index is clamped to the texture's own bytes.
+MRT_D v3 texture_load_color(const SceneDev &s, int tex, float tu, float tv) {
+    const TextureRec tr = s.textures[tex];
+    const int32_t u = static_cast<int32_t>(tu * static_cast<float>(tr.width));
+    const int32_t v = static_cast<int32_t>(tv * static_cast<float>(tr.height));
+    uint32_t index = static_cast<uint32_t>(v * tr.width * tr.channels + u * tr.channels);
+    if (index + 3u > tr.bytes) { index = tr.bytes >= 3u ? tr.bytes - 3u : 0u; }
+    const uint8_t *p = s.texels + tr.offset + index;
+    return mk3(static_cast<float>(p[0]) / 255.0f, static_cast<float>(p[1]) / 255.0f, static_cast<float>(p[2]) / 255.0f);
 }
 
 // What the primitive's intersect() stores in the Intersection (Triangle.cpp:100-108, Sphere.cpp:69-78, Plane.cpp:64-70)
@@ -98,6 +113,11 @@ MRT_D void resolve_surface(const SceneDev &s, v3 o, v3 d, const HitRec &h, Surfa
         const v3 nA = mk3(s0.x, s0.y, s0.z), nB = mk3(s0.w, s1.x, s1.y), nC = mk3(s1.z, s1.w, s2.x);
         sf.normal = normalize((nA * w + nB * h.u) + nC * h.v);
         load_material(s, __float_as_int(s3.w), sf);
+        if (sf.texture >= 0) {
+            // Triangle.cpp:98 texCoords = tA * w + tB * u + tC * v; Shader.cpp:116-120: both >= 0 -> Kd comes from the texture
+            const float tu = (s2.y * w + s2.w * h.u) + s3.y * h.v, tv = (s2.z * w + s3.x * h.u) + s3.z * h.v;
+            if (tu >= 0.0f && tv >= 0.0f) { sf.Kd = texture_load_color(s, sf.texture, tu, tv); }
+        }
         sf.skipKind = HIT_TRIANGLE; sf.skipIdx = h.idx;
     } else if (h.kind == HIT_SPHERE) {
         const SphereRec sp = s.spheres[h.idx];

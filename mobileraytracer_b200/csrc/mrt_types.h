@@ -39,7 +39,9 @@ static_assert(sizeof(RefNode) == 32, "RefNode must be 32 bytes");
 struct SphereRec { float cx, cy, cz, sqRadius; int32_t material; int32_t id; int32_t pad0, pad1; };
 struct PlaneRec { float nx, ny, nz, px, py, pz; int32_t material; int32_t id; };
 
-struct __align__(16) MaterialRec { float Le[3], Kd[3], Ks[3], Kt[3]; float ior; float pad[3]; };
+struct __align__(16) MaterialRec { float Le[3], Kd[3], Ks[3], Kt[3]; float ior; int32_t texture; float pad[2]; };   // texture: index into SceneDev::textures or -1
+// Texture (MobileRT/Texture.hpp): texels of all textures live in one byte buffer
+struct TextureRec { uint32_t offset; int32_t width, height, channels; uint32_t bytes; };
 static_assert(sizeof(MaterialRec) == 64, "MaterialRec must be 64 bytes");
 
 struct __align__(16) LightRec { int32_t kind; float A[3], AB[3], AC[3], Le[3]; float pad[3]; };
@@ -64,6 +66,7 @@ struct SceneDev {
     const RefNode *sphere_nodes; const SphereRec *spheres; int32_t n_spheres;
     const RefNode *plane_nodes;  const PlaneRec *planes;   int32_t n_planes;
     const MaterialRec *materials; int32_t n_materials;
+    const TextureRec *textures; const uint8_t *texels; int32_t n_textures;
     const LightRec *lights; int32_t n_lights;
     const float *tile_order;     // 256
     const float *shader_table;   // 1 << 20

@@ -10,7 +10,11 @@ Mirrors what the reference does around tinyobjloader v1.0.7 (app/Components/Load
   * faces without a material take the first vertex's colour as Kd (OBJLoader.cpp:423-455)
 and Components::PerspectiveLoader / OrthographicLoader / CameraFactory for `.cam` (PerspectiveLoader.cpp:18-64).
 Triangle order is file order here (the reference's order depends on its loader threads, OBJLoader.cpp:83-97).
-Textures (map_Kd) are not sampled on the device yet: such faces keep their Kd and get texture coordinates -1."""
+Textures: a material with map_Kd in a file that has `vt` lines gets the decoded image (PIL here, stb_image in the reference:
+both return the PNG's own 8-bit channels) and its faces the fract() of their texture coordinates (OBJLoader.cpp:328-364,
+193-212, Utils.cpp:177-180); the texture is part of the material's identity for de-duplication (Material.cpp:36-45)."""
+import os
+
 import numpy as np
 
 from . import capi
@@ -68,7 +72,7 @@ def _color_normalize(c):
 def load_obj(obj_path, mtl_path=None):
     """OBJLoader(obj, mtl) + fillScene -> Scene (triangles as one structured numpy array)."""
     mats, mat_names = _parse_mtl(mtl_path) if mtl_path else ([], {})
-    v_txt, vn_txt, f_lines = [], [], []
+    v_txt, vn_txt, vt_txt, f_lines = [], [], [], []
     cur_mat = -1
     with open(obj_path, "r", errors="replace") as fh:
         for line in fh:
@@ -80,6 +84,8 @@ def load_obj(obj_path, mtl_path=None):
                     v_txt.append(line[2:])
                 elif c1 == "n":
                     vn_txt.append(line[3:])
+                elif c1 == "t":
+                    vt_txt.append(line[3:])
             elif c0 == "f" and (c1 == " " or c1 == "\t"):
                 f_lines.append((cur_mat, line[2:]))
             elif c0 == "u" and line.startswith("usemtl"):
@@ -96,17 +102,24 @@ def load_obj(obj_path, mtl_path=None):
         VN[:, 0] = -VN[:, 0]
 
     # faces -> fan-triangulated index triples (tinyobj triangulates polygons on load)
-    vi, ni, fm = [], [], []
+    vi, ni, ti, fm = [], [], [], []
     n_vn = len(VN)
+    VT = np.array([x.split()[:2] for x in vt_txt], dtype=np.float64).astype(f32).reshape(-1, 2) if vt_txt else np.zeros((0, 2), f32)
+    n_vt = len(VT)
     for m, txt in f_lines:
         toks = txt.split()
         if len(toks) < 3:
             continue
-        pv, pn = [], []
+        pv, pn, pt = [], [], []
         for t in toks:
             a = t.split("/")
             i = int(a[0])
             pv.append(i - 1 if i > 0 else nv + i)
+            if len(a) > 1 and a[1]:
+                j = int(a[1])
+                pt.append(j - 1 if j > 0 else n_vt + j)
+            else:
+                pt.append(-1)
             if len(a) > 2 and a[2]:
                 j = int(a[2])
                 pn.append(j - 1 if j > 0 else n_vn + j)
@@ -115,9 +128,11 @@ def load_obj(obj_path, mtl_path=None):
         for k in range(1, len(pv) - 1):
             vi.append((pv[0], pv[k], pv[k + 1]))
             ni.append((pn[0], pn[k], pn[k + 1]))
+            ti.append((pt[0], pt[k], pt[k + 1]))
             fm.append(m)
     vi = np.asarray(vi, np.int64).reshape(-1, 3)
     ni = np.asarray(ni, np.int64).reshape(-1, 3)
+    ti = np.asarray(ti, np.int64).reshape(-1, 3)
     fm = np.asarray(fm, np.int64)
     n = len(vi)
     A, B, Cc = V[vi[:, 0]], V[vi[:, 1]], V[vi[:, 2]]
@@ -147,14 +162,31 @@ def load_obj(obj_path, mtl_path=None):
         Le = _color_normalize(m["Ke"])
         recs.append((Kd, Ks, Kt, f32(m["ior"]), Le))
     dedup, out_mats = {}, []
+    tex_cache = {}      # texture file name -> index into scene.textures_ or -1 when it cannot be decoded (OBJLoader.cpp:253-270)
 
-    def mat_index(Kd, Ks, Kt, ior, Le):
-        key = (Kd.tobytes(), Ks.tobytes(), Kt.tobytes(), np.float32(ior).tobytes(), Le.tobytes())
+    def texture_index(name):
+        if name not in tex_cache:
+            tex_cache[name] = -1
+            try:
+                from PIL import Image
+                img = Image.open(os.path.join(os.path.dirname(obj_path), name))
+                if img.mode in ("P", "1") or img.mode.startswith("I") or img.mode == "F":
+                    img = img.convert("RGBA" if "transparency" in img.info else "RGB")   # stb_image expands palettes / 16 bit to 8-bit channels
+                px = np.asarray(img, np.uint8)
+                scene.textures_.append(px if px.ndim == 3 else px[:, :, None])
+                tex_cache[name] = len(scene.textures_) - 1
+            except Exception:
+                pass
+        return tex_cache[name]
+
+    def mat_index(Kd, Ks, Kt, ior, Le, tex=-1):
+        key = (Kd.tobytes(), Ks.tobytes(), Kt.tobytes(), np.float32(ior).tobytes(), Le.tobytes(), tex)
         if key not in dedup:
             dedup[key] = len(out_mats)
             r = np.zeros((), capi.MATERIAL)
             r["Kd"], r["Ks"], r["Kt"], r["ior"], r["Le"] = Kd, Ks, Kt, ior, Le
             out_mats.append(r)
+            scene.material_texture_.append(tex)
         return dedup[key]
 
     is_light = np.zeros(n, bool)
@@ -174,7 +206,14 @@ def load_obj(obj_path, mtl_path=None):
                 is_light |= sel
                 mat_of_file[m] = None
             else:
-                tri_mat[sel] = mat_index(Kd, Ks, Kt, ior, Le)
+                tex = -1
+                if mats[m]["map_Kd"] and n_vt:            # hasTexture && hasCoordTex (OBJLoader.cpp:332-336)
+                    tex = texture_index(mats[m]["map_Kd"])
+                    if tex >= 0:
+                        for name, col in (("tA", 0), ("tB", 1), ("tC", 2)):
+                            tc = VT[ti[sel, col]]
+                            tri[name][sel] = (tc - np.floor(tc)).astype(f32)     # glm::fract
+                tri_mat[sel] = mat_index(Kd, Ks, Kt, ior, Le, tex)
         else:
             cols = colors[vi[sel, 0]]
             idxs = np.nonzero(sel)[0]

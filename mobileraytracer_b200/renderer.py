@@ -53,6 +53,16 @@ class Renderer:
             a = arr[name]
             setattr(sd, name, a.ctypes.data if len(a) else None)
             setattr(sd, "n_" + name, len(a))
+        texs = arr.get("textures") or []
+        if texs:
+            self._tex_pixels = [np.ascontiguousarray(t, np.uint8) for t in texs]
+            self._tex_recs = (capi.Texture * len(texs))()
+            for rec, px in zip(self._tex_recs, self._tex_pixels):
+                hh, ww = px.shape[0], px.shape[1]
+                rec.pixels, rec.width, rec.height, rec.channels = px.ctypes.data, ww, hh, (px.shape[2] if px.ndim == 3 else 1)
+            self._mat_tex = np.ascontiguousarray(arr["material_texture"], np.int32)
+            assert len(self._mat_tex) == len(arr["materials"])
+            sd.textures, sd.n_textures, sd.material_texture = C.addressof(self._tex_recs), len(texs), self._mat_tex.ctypes.data
         rd = capi.RenderDesc()
         rd.width, rd.height, rd.samples_pixel, rd.samples_light = width, height, samplesPixel, samplesLight
         rd.shader, rd.accelerator, rd.pixel_sampler, rd.seed, rd.flags, rd.device = shader, accelerator, pixel_sampler, seed, flags, device

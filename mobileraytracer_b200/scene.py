@@ -69,6 +69,8 @@ class Scene:
         self.planes_ = []
         self.lights_ = []
         self.materials_ = []
+        self.textures_ = []            # decoded images, uint8 (h, w, channels) as stb_image returns them (Texture.cpp:58-118)
+        self.material_texture_ = []    # per material: index into textures_ or -1 (Material::texture_)
 
     # -- builders used by the built-in scenes and the loaders
     def add_material(self, m):
@@ -110,9 +112,13 @@ class Scene:
                 a[i] = x
             return a
         tri = self.triangles_ if isinstance(self.triangles_, np.ndarray) else pack(self.triangles_, capi.TRIANGLE)
-        return {"triangles": np.ascontiguousarray(tri), "spheres": pack(self.spheres_, capi.SPHERE),
-                "planes": pack(self.planes_, capi.PLANE), "lights": pack(self.lights_, capi.LIGHT),
-                "materials": pack(self.materials_, capi.MATERIAL) if not isinstance(self.materials_, np.ndarray) else self.materials_}
+        out = {"triangles": np.ascontiguousarray(tri), "spheres": pack(self.spheres_, capi.SPHERE),
+               "planes": pack(self.planes_, capi.PLANE), "lights": pack(self.lights_, capi.LIGHT),
+               "materials": pack(self.materials_, capi.MATERIAL) if not isinstance(self.materials_, np.ndarray) else self.materials_}
+        if self.textures_:
+            mt = list(self.material_texture_) + [-1] * (len(out["materials"]) - len(self.material_texture_))
+            out["textures"], out["material_texture"] = list(self.textures_), np.asarray(mt, np.int32)
+        return out
 
 
 class Camera:
