@@ -97,7 +97,9 @@ typedef struct mrt_render_desc {
     int32_t samples_pixel;          /* Config::samplesPixel */
     int32_t samples_light;          /* Config::samplesLight */
     int32_t shader;                 /* MRT_SHADER_* */
-    int32_t accelerator;            /* must be MRT_ACC_B200 or MRT_ACC_BVH (both select the BVH8 path) */
+    int32_t accelerator;            /* MRT_ACC_B200 or MRT_ACC_BVH: the reference's BVH visibility rules (finite plane boxes,
+                                       root-box NaN rule); MRT_ACC_NAIVE: Naive<T>'s rules (every plane / sphere tested, caller
+                                       order). Triangles go through the BVH8 either way. MRT_ACC_REGULAR_GRID is rejected. */
     int32_t pixel_sampler;          /* MRT_SAMPLER_* */
     uint32_t seed;                  /* seeds the library's own table shuffles when mrt_sampler_tables is NULL */
     uint32_t flags;                 /* MRT_FLAG_* */

@@ -38,6 +38,7 @@ struct DevMem {
 }  // namespace
 
 struct mrt_handle {
+    bool naive = false;              // MRT_ACC_NAIVE semantics for planes / spheres / the triangle root box
     uint32_t roots_per_sample = 0;   // valid pixels of one sample (wavefront path slots)
     int device = 0;
     cudaStream_t stream = nullptr;       // stream in use (own_stream unless mrt_set_stream installed the caller's)
@@ -195,10 +196,18 @@ int upload_scene(mrt_handle *h, const mrt_scene_desc &sc) {
     std::vector<RefNode> pnodes, snodes;
     std::vector<int> porder, sorder;
     for (int64_t i = 0; i < sc.n_planes; ++i) { boxes.push_back(hb_plane(sc.planes[i].normal, sc.planes[i].point)); }
-    build_ref_bvh(boxes, pnodes, porder);
+    // MRT_ACC_NAIVE (Naive<T>::intersect, Accelerators/Naive.hpp:80-91): every plane and sphere is tested in the caller's order
+    // and no box decides what a ray can see; expressed as one leaf holding all primitives behind an unbounded box
+    auto naive_leaf = [](size_t count, std::vector<RefNode> &nodes, std::vector<int> &order) {
+        nodes.clear(); order.clear();
+        if (count == 0) { return; }
+        nodes.push_back(RefNode{-3.0e38f, -3.0e38f, -3.0e38f, 3.0e38f, 3.0e38f, 3.0e38f, 0, static_cast<int32_t>(count)});
+        for (size_t i = 0; i < count; ++i) { order.push_back(static_cast<int>(i)); }
+    };
+    if (h->naive) { naive_leaf(static_cast<size_t>(sc.n_planes), pnodes, porder); } else { build_ref_bvh(boxes, pnodes, porder); }
     boxes.clear();
     for (int64_t i = 0; i < sc.n_spheres; ++i) { boxes.push_back(hb_sphere(sc.spheres[i].center, sc.spheres[i].sq_radius)); }
-    build_ref_bvh(boxes, snodes, sorder);
+    if (h->naive) { naive_leaf(static_cast<size_t>(sc.n_spheres), snodes, sorder); } else { build_ref_bvh(boxes, snodes, sorder); }
     std::vector<PlaneRec> planes(porder.size() ? porder.size() : 1);
     h->plane_slot_of_id.assign(porder.size(), 0);
     for (size_t sidx = 0; sidx < porder.size(); ++sidx) {
@@ -254,6 +263,7 @@ int upload_scene(mrt_handle *h, const mrt_scene_desc &sc) {
         s.tune_postpone = tp ? std::atoi(tp) : 12;
         s.tune_refill = tr ? std::atoi(tr) : 22;
         s.prmt_one = 0x3F800000u;
+        s.naive = h->naive ? 1 : 0;
         const char *tw = std::getenv("MRT_B200_WAIT");
         s.tune_wait = tw ? std::atoi(tw) : 8;
     }
@@ -356,7 +366,9 @@ int mrt_create(const mrt_scene_desc *scene, const mrt_camera_desc *camera, const
     *out = nullptr;
     if (render->width <= 0 || render->height <= 0 || render->samples_pixel < 0 || render->samples_light < 0) { return fail(nullptr, MRT_ERR_INVALID, "bad render size / sample counts"); }
     if (render->shader < 0 || render->shader > 4) { return fail(nullptr, MRT_ERR_INVALID, "unknown shader"); }
-    if (render->accelerator != MRT_ACC_B200 && render->accelerator != MRT_ACC_BVH) { return fail(nullptr, MRT_ERR_INVALID, "this library only provides the BVH accelerator (MRT_ACC_B200 / MRT_ACC_BVH)"); }
+    if (render->accelerator != MRT_ACC_B200 && render->accelerator != MRT_ACC_BVH && render->accelerator != MRT_ACC_NAIVE) {
+        return fail(nullptr, MRT_ERR_INVALID, "accelerator must be MRT_ACC_B200 / MRT_ACC_BVH (BVH semantics) or MRT_ACC_NAIVE (the reference's Naive visibility rules); RegularGrid is not provided");
+    }
     if (scene->n_triangles < 0 || scene->n_spheres < 0 || scene->n_planes < 0 || scene->n_materials < 0 || scene->n_lights < 0) { return fail(nullptr, MRT_ERR_INVALID, "negative count"); }
     if ((scene->n_triangles && !scene->triangles) || (scene->n_spheres && !scene->spheres) || (scene->n_planes && !scene->planes) ||
         (scene->n_materials && !scene->materials) || (scene->n_lights && !scene->lights)) { return fail(nullptr, MRT_ERR_INVALID, "null array with non-zero count"); }
@@ -373,6 +385,7 @@ int mrt_create(const mrt_scene_desc *scene, const mrt_camera_desc *camera, const
         if (e == cudaSuccess) { e = cudaEventCreate(&h->ev1); }
         if (e != cudaSuccess) { rc = cuda_fail(h, e, "device setup"); break; }
         h->flags = render->flags;
+        h->naive = render->accelerator == MRT_ACC_NAIVE;
         h->rp.width = render->width; h->rp.height = render->height; h->rp.spp = render->samples_pixel; h->rp.spl = render->samples_light;
         h->rp.shader = render->shader; h->rp.seed = render->seed;
         h->rp.bsx = render->width / 16; h->rp.bsy = render->height / 16;   // Renderer.cpp:33-34

@@ -338,6 +338,7 @@ MRT_D bool trace_bvh8(const SceneDev &s, v3 o, v3 d, int skipPrim, float &tbest,
 // misses, AABB.cpp:34-54) is visible in images of the orthographic scenes, so it is reproduced exactly here.
 MRT_D bool triangles_root_hit(const SceneDev &s, v3 o, v3 d) {
     if (s.n_triangles <= 0) { return false; }
+    if (s.naive) { return true; }                            // Naive<Triangle> has no box at all (Naive.hpp:80-91)
     // without a zero direction component the test has no NaN case and only rejects rays that cannot hit anything inside
     if (d.x != 0.0f && d.y != 0.0f && d.z != 0.0f) { return true; }
     return aabb_intersect_exact(s.tri_bmin, s.tri_bmax, o, d);

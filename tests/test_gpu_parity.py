@@ -233,3 +233,21 @@ def test_textured_obj_scene_matches_reference(mrt, ref, tmp_path):
     assert colours > 200, "the textures must be visible (%d distinct colours)" % colours
     assert c["exact"] >= 0.999 and c["max"] <= 1, c
     r.close()
+
+
+@pytest.mark.parametrize("scene,shader", [(0, 1), (1, 1), (3, 1), (2, 3)])
+def test_naive_accelerator_semantics_match_reference(mrt, ref, scene, shader):
+    """Config::accelerator = ACC_NAIVE (Naive.hpp:80-91): planes are unbounded and every primitive is tested in scene order.
+    The frame must equal the reference's Naive frame (which differs from its BVH frame where plane boxes cut planes off)."""
+    w = h = 256
+    r = ref.RefRenderer(w, h, shader, scene, accelerator=1)
+    bm_ref, _ = r.render(threads=1)
+    arrays = H.scene_arrays_from_ref(r)
+    cam = H.camera_from_config(scene, np.float32(w) / np.float32(h), None)
+    from mobileraytracer_b200 import scene as S
+    g = mrt.Renderer(arrays, cam, w, h, 1, 1, shader, accelerator=mrt.capi.ACC_NAIVE, depth_max_point=S.BUILTIN[scene][2],
+                     tables={"tile_order": ref.table("tile"), "shader_table": ref.table("shader"), "static_halton": ref.table("static_halton")})
+    c = H.compare_bitmaps(g.renderFrame(), bm_ref)
+    assert c["exact"] >= 0.999 and c["max"] <= 1, c
+    g.close()
+    r.close()
