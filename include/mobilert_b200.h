@@ -87,9 +87,11 @@ enum { MRT_SAMPLER_AUTO = 0, MRT_SAMPLER_CONSTANT = 1, MRT_SAMPLER_STATIC_HALTON
 enum {
     MRT_FLAG_FP32_ACCUMULATE = 1,  /* accumulate radiance in fp32 and quantise once (needed for multi-GPU partitions);
                                       default is the reference's 8-bit running average (MobileRT/Utils/Utils.cpp:66-90) */
-    MRT_FLAG_SORT_BY_MATERIAL = 2, /* wavefront path tracer: counting-sort the hit queue by material before shading */
-    MRT_FLAG_REPLAY_SAMPLERS = 4   /* deterministic shaders: replay the reference's single-thread draw order of
-                                      getLightIndex / AreaLight::getPosition exactly (count + scan + render) */
+    MRT_FLAG_SORT_BY_MATERIAL = 2, /* accepted and ignored: every material runs the same shading routine (materials are data,
+                                      Material.hpp), so the shade kernel has no per-material divergence to sort away; it is
+                                      bound by gather latency (profiles/), which a sort of the 16-byte hit records would not help */
+    MRT_FLAG_REPLAY_SAMPLERS = 4   /* reserved, not implemented: exact replay of the reference's single-thread draw order of
+                                      getLightIndex / AreaLight::getPosition for deterministic shaders with several lights */
 };
 
 typedef struct mrt_render_desc {

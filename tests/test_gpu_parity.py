@@ -251,3 +251,19 @@ def test_naive_accelerator_semantics_match_reference(mrt, ref, scene, shader):
     assert c["exact"] >= 0.999 and c["max"] <= 1, c
     g.close()
     r.close()
+
+
+@pytest.mark.parametrize("shader", [0, 1, 2, 3, 4])
+def test_empty_scene_renders_black(mrt, shader):
+    """No primitives, no lights, no materials: every ray misses, rgb stays 0 (Shader.cpp:122) and the pixel is 0xFF000000;
+    one primary ray per pixel is counted and nothing else."""
+    from mobileraytracer_b200 import scene as S
+    w, h = 64, 48
+    cam = S.Camera(mrt.capi.CAMERA_PERSPECTIVE, (0, 0, -3), (0, 0, 0), (0, 1, 0), 45.0, 45.0)
+    g = mrt.Renderer(S.Scene(), cam, w, h, 2, 1, shader)
+    bm = g.renderFrame()
+    assert (np.asarray(bm).reshape(-1).view(np.uint32) == 0xFF000000).all()
+    assert g.getTotalCastedRays() == 2 * w * h
+    t = g.traceRays(np.zeros((5, 3), np.float32), np.tile(np.array([[0, 0, 1]], np.float32), (5, 1)))
+    assert (t["kind"] == 0).all() and (t["t"] == np.float32(1e30)).all()
+    g.close()
