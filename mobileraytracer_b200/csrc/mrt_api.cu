@@ -402,7 +402,10 @@ int mrt_create(const mrt_scene_desc *scene, const mrt_camera_desc *camera, const
         h->pinned_bytes = npix * sizeof(int32_t);
         if (render->shader == MRT_SHADER_PATHTRACER) {
             const char *be = std::getenv("MRT_B200_BATCH");   // samples traced together per wavefront pass
-            const int batch = std::max(1, std::min(be ? std::atoi(be) : 8, render->samples_pixel));
+            // default: up to 16 samples per pass, as long as the queues (about 768 bytes per pixel and sample) stay below 32 GB
+            const double per_sample = 768.0 * static_cast<double>(render->width) * static_cast<double>(render->height);
+            const int by_memory = static_cast<int>(std::max(1.0, std::min(16.0, 32.0e9 / std::max(per_sample, 1.0))));
+            const int batch = std::max(1, std::min(be ? std::atoi(be) : by_memory, render->samples_pixel));
             if ((e = wavefront_create(render->width, render->height, batch, &h->wavefront)) != cudaSuccess) { rc = cuda_fail(h, e, "wavefront queues"); break; }
         }
         if ((e = cudaStreamSynchronize(h->stream)) != cudaSuccess) { rc = cuda_fail(h, e, "create sync"); break; }

@@ -629,7 +629,7 @@ cudaError_t wavefront_create(int width, int height, int batch, Wavefront **out) 
     WF_TRY(wf_alloc(w, &q.hit, q.cap_rays));
     WF_TRY(wf_alloc(w, &q.s0, q.cap_shadow)); WF_TRY(wf_alloc(w, &q.s1, q.cap_shadow)); WF_TRY(wf_alloc(w, &q.s2, q.cap_shadow));
     WF_TRY(wf_alloc(w, &q.chains, q.cap_chains));
-    WF_TRY(wf_alloc(w, &q.counts, 40));
+    WF_TRY(wf_alloc(w, &q.counts, kWfCounts));
     return cudaSuccess;
 }
 
@@ -681,7 +681,7 @@ cudaError_t wavefront_render_batch(Wavefront *w, const SceneDev &s, const Camera
     if (n_samples < 1 || n_samples > hst->batch) { return cudaErrorInvalidValue; }
     const int grid = hst->sm_count * 8;
     WF_TRY(wf_mark(hst, -1, st));
-    WF_TRY(cudaMemsetAsync(Q.counts, 0, 40 * sizeof(uint32_t), st));
+    WF_TRY(cudaMemsetAsync(Q.counts, 0, kWfCounts * sizeof(uint32_t), st));
     const int patches = kNumberOfTiles * ((rp.bsx + 7) / 8) * ((rp.bsy + 3) / 4);
     if (patches == 0) { return cudaSuccess; }
     if (static_cast<unsigned long long>(roots_per_sample) * static_cast<unsigned long long>(n_samples) > Q.cap_rays) { return cudaErrorInvalidValue; }
@@ -790,7 +790,7 @@ cudaError_t wavefront_trace_rays(Wavefront *w, const SceneDev &s, int64_t n, con
     Queues &Q = w->q;
     if (n < 0 || static_cast<uint64_t>(n) > Q.cap_rays || static_cast<uint64_t>(n) > Q.cap_shadow) { return cudaErrorInvalidValue; }
     if (n == 0) { return cudaSuccess; }
-    WF_TRY(cudaMemsetAsync(Q.counts, 0, 40 * sizeof(uint32_t), st));
+    WF_TRY(cudaMemsetAsync(Q.counts, 0, kWfCounts * sizeof(uint32_t), st));
     const int blocks = static_cast<int>((n + 255) / 256), grid = w->sm_count * 8;
     k_wf_test_fill<<<blocks, 256, 0, st>>>(Q, n, d_o, d_d, d_okind, d_oidx, d_sdist);
     k_wf_test_save_counts<<<1, 1, 0, st>>>(Q);

@@ -9,7 +9,8 @@ struct Wavefront;   // opaque: queues, chain records, counters
 
 struct WavefrontTimes { double extend_ms = 0, shadow_ms = 0, shade_ms = 0, other_ms = 0; uint64_t extend_launches = 0; };
 
-constexpr int kWfMaxBatch = 8;
+constexpr int kWfMaxBatch = 16;
+constexpr int kWfCounts = 24 + kWfMaxBatch + 8;   // Queues::counts entries (see mrt_wavefront.cu)
 // batch: samples of every pixel traced together in one pass (1..kWfMaxBatch); the queues are sized for it
 cudaError_t wavefront_create(int width, int height, int batch, Wavefront **out);
 int wavefront_batch(const Wavefront *w);
