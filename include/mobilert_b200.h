@@ -90,8 +90,11 @@ enum {
     MRT_FLAG_SORT_BY_MATERIAL = 2, /* accepted and ignored: every material runs the same shading routine (materials are data,
                                       Material.hpp), so the shade kernel has no per-material divergence to sort away; it is
                                       bound by gather latency (profiles/), which a sort of the 16-byte hit records would not help */
-    MRT_FLAG_REPLAY_SAMPLERS = 4   /* reserved, not implemented: exact replay of the reference's single-thread draw order of
-                                      getLightIndex / AreaLight::getPosition for deterministic shaders with several lights */
+    MRT_FLAG_REPLAY_SAMPLERS = 4   /* parity mode for NoShadows / Whitted: every Shader::getLightIndex (Shader.cpp:223-233) and
+                                      AreaLight::getPosition (AreaLight.cpp:17-26) draw reads the table entry the reference's
+                                      single-thread run reads (two counting passes per sample + host prefix sums, about 3x the
+                                      frame time). Up to 8 lights; rejected for the PathTracer, whose ray tree depends on the
+                                      draws; needs the reference's tables (mrt_sampler_tables) and mrt_set_replay_counter. */
 };
 
 typedef struct mrt_render_desc {
@@ -168,6 +171,11 @@ int mrt_set_stream(mrt_handle *h, void *cuda_stream);
 
 /* Replaces: Renderer::stopRender (Renderer.cpp:93-99), Renderer::getSample (:176-178),
  * Renderer::getTotalCastedRays (:204-207). Thread-safe; may be called while mrt_render_frame runs. */
+/* Shader::getLightIndex's counter is a function-static (Shader.cpp:224): it is never reset and is shared by every
+ * renderer of the process. With MRT_FLAG_REPLAY_SAMPLERS the handle mirrors it: starts at 0, advances with every frame
+ * it renders; a host that also runs the reference's CPU path in the same process sets the reference's value here first. */
+int mrt_set_replay_counter(mrt_handle *h, uint32_t light_index_counter);
+int mrt_get_replay_counter(mrt_handle *h, uint32_t *light_index_counter);
 int mrt_stop(mrt_handle *h);
 int mrt_get_sample(mrt_handle *h, int32_t *sample);
 int mrt_get_total_rays(mrt_handle *h, uint64_t *rays);

@@ -68,7 +68,7 @@ class Stats(C.Structure):
 
 # every symbol include/mobilert_b200.h declares
 SYMBOLS = ["mrt_create", "mrt_destroy", "mrt_render_frame", "mrt_render_frame_device", "mrt_render_accumulate_device",
-           "mrt_resolve_device", "mrt_set_camera", "mrt_set_stream", "mrt_stop", "mrt_get_sample", "mrt_get_total_rays", "mrt_get_stats",
+           "mrt_resolve_device", "mrt_set_camera", "mrt_set_stream", "mrt_stop", "mrt_set_replay_counter", "mrt_get_replay_counter", "mrt_get_sample", "mrt_get_total_rays", "mrt_get_stats",
            "mrt_last_error", "mrt_trace_rays", "mrt_generate_rays", "mrt_shade_rays", "mrt_test_triangle_intersect",
            "mrt_test_sphere_intersect", "mrt_test_plane_intersect", "mrt_test_aabb_intersect", "mrt_test_incremental_avg",
            "mrt_test_halton", "mrt_device_count", "mrt_version"]
@@ -101,6 +101,8 @@ def lib():
         L.mrt_set_camera.argtypes = [vp, C.POINTER(CameraDesc)]
         L.mrt_set_stream.argtypes = [vp, vp]
         L.mrt_stop.argtypes = [vp]
+        L.mrt_set_replay_counter.argtypes = [vp, C.c_uint32]
+        L.mrt_get_replay_counter.argtypes = [vp, C.POINTER(C.c_uint32)]
         L.mrt_get_sample.argtypes = [vp, C.POINTER(i32)]
         L.mrt_get_total_rays.argtypes = [vp, C.POINTER(C.c_uint64)]
         L.mrt_get_stats.argtypes = [vp, C.POINTER(Stats)]

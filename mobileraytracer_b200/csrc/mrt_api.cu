@@ -40,6 +40,7 @@ struct DevMem {
 struct mrt_handle {
     bool naive = false;              // MRT_ACC_NAIVE semantics for planes / spheres / the triangle root box
     uint32_t roots_per_sample = 0;   // valid pixels of one sample (wavefront path slots)
+    uint32_t replay_index_counter = 0;   // MRT_FLAG_REPLAY_SAMPLERS: value of Shader::getLightIndex's counter at the next frame's first draw
     int device = 0;
     cudaStream_t stream = nullptr;       // stream in use (own_stream unless mrt_set_stream installed the caller's)
     cudaStream_t own_stream = nullptr;
@@ -372,6 +373,10 @@ int mrt_create(const mrt_scene_desc *scene, const mrt_camera_desc *camera, const
     if (scene->n_triangles < 0 || scene->n_spheres < 0 || scene->n_planes < 0 || scene->n_materials < 0 || scene->n_lights < 0) { return fail(nullptr, MRT_ERR_INVALID, "negative count"); }
     if ((scene->n_triangles && !scene->triangles) || (scene->n_spheres && !scene->spheres) || (scene->n_planes && !scene->planes) ||
         (scene->n_materials && !scene->materials) || (scene->n_lights && !scene->lights)) { return fail(nullptr, MRT_ERR_INVALID, "null array with non-zero count"); }
+    if (render->flags & MRT_FLAG_REPLAY_SAMPLERS) {
+        if (render->shader == MRT_SHADER_PATHTRACER) { return fail(nullptr, MRT_ERR_INVALID, "MRT_FLAG_REPLAY_SAMPLERS: the PathTracer's ray tree depends on the draws themselves; only NoShadows / Whitted can be replayed"); }
+        if (scene->n_lights > kReplayMaxLights) { return fail(nullptr, MRT_ERR_INVALID, "MRT_FLAG_REPLAY_SAMPLERS supports up to 8 lights"); }
+    }
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) { cudaGetLastError(); return fail(nullptr, MRT_ERR_CUDA, "no CUDA device: this library has no CPU fallback"); }
     mrt_handle *h = new (std::nothrow) mrt_handle;
@@ -433,6 +438,14 @@ int mrt_set_stream(mrt_handle *h, void *cuda_stream) {
     return MRT_OK;
 }
 
+int mrt_set_replay_counter(mrt_handle *h, uint32_t light_index_counter) {
+    if (!h) { return MRT_ERR_INVALID; }
+    h->replay_index_counter = light_index_counter; errno = 0; return MRT_OK;
+}
+int mrt_get_replay_counter(mrt_handle *h, uint32_t *light_index_counter) {
+    if (!h || !light_index_counter) { return MRT_ERR_INVALID; }
+    *light_index_counter = h->replay_index_counter; errno = 0; return MRT_OK;
+}
 int mrt_stop(mrt_handle *h) { if (!h) { return MRT_ERR_INVALID; } h->stop.store(1); errno = 0; return MRT_OK; }
 int mrt_get_sample(mrt_handle *h, int32_t *sample) { if (!h || !sample) { return MRT_ERR_INVALID; } *sample = h->sample.load(); errno = 0; return MRT_OK; }
 int mrt_get_total_rays(mrt_handle *h, uint64_t *rays) { if (!h || !rays) { return MRT_ERR_INVALID; } *rays = h->total_rays.load(); errno = 0; return MRT_OK; }
@@ -476,14 +489,53 @@ int render_samples(mrt_handle *h, int32_t *d_bitmap, float4 *d_accum, int sample
     } else {
         const size_t depth = 4;   // samples in flight, so that mrt_stop() takes effect within a few samples
         int k = 0;
+        // Exact replay (MRT_FLAG_REPLAY_SAMPLERS). The ray tree of NoShadows / Whitted does not depend on the draws, so
+        // two counting passes per sample find how many draws of each counter precede every pixel-sample in the
+        // reference's single-thread order: Shader::getLightIndex's counter (function-static, Shader.cpp:224: it runs on
+        // across frames and renderers) and each AreaLight's own sampler (reset per frame, Renderer.cpp:58-59).
+        const bool replay = (h->flags & MRT_FLAG_REPLAY_SAMPLERS) && h->scene.n_lights > 0 &&
+                            (h->rp.shader == MRT_SHADER_NOSHADOWS || h->rp.shader == MRT_SHADER_WHITTED);
+        const int nl = h->scene.n_lights;
+        const size_t slots = static_cast<size_t>(kNumberOfTiles) * h->rp.bsx * h->rp.bsy;
+        DevMem d_index, d_light;
+        std::vector<uint32_t> hv;
+        uint32_t light_counter[kReplayMaxLights] = {};
+        if (replay) {
+            if (sample_begin != 0 || sample_stride != 1) { return fail(h, MRT_ERR_INVALID, "MRT_FLAG_REPLAY_SAMPLERS needs every sample of the frame on this handle"); }
+            API_CUDA(h, d_index.alloc(slots * sizeof(uint32_t)));
+            API_CUDA(h, d_light.alloc(slots * nl * sizeof(uint32_t)));
+            hv.resize(slots * static_cast<size_t>(nl));
+        }
         for (int s = sample_begin; s < spp; s += sample_stride, ++k) {
             if (static_cast<size_t>(k) >= depth) {
                 API_CUDA(h, cudaEventSynchronize(h->sample_events[static_cast<size_t>(k) % depth]));
                 h->sample.store(s - static_cast<int>(depth - 1) * sample_stride);
             }
             if (h->stop.load()) { stopped = true; break; }
+            ReplayArgs rep {REPLAY_OFF, nl, d_index.as<uint32_t>(), d_light.as<uint32_t>()};
+            if (replay) {
+                const FrameTargets none {nullptr, nullptr};
+                API_CUDA(h, cudaMemsetAsync(d_index.p, 0, slots * sizeof(uint32_t), st));
+                rep.mode = REPLAY_COUNT_INDEX;
+                API_CUDA(h, launch_render_sample(h->scene, h->camera, h->rp, h->d_inv_tile.as<int2>(), s, 1, none, h->d_counters.as<DeviceCounters>(), st, rep));
+                API_CUDA(h, cudaMemcpyAsync(hv.data(), d_index.p, slots * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+                API_CUDA(h, cudaStreamSynchronize(st));
+                for (size_t i = 0; i < slots; ++i) { const uint32_t c = hv[i]; hv[i] = h->replay_index_counter; h->replay_index_counter += c; }
+                API_CUDA(h, cudaMemcpyAsync(d_index.p, hv.data(), slots * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+                API_CUDA(h, cudaMemsetAsync(d_light.p, 0, slots * nl * sizeof(uint32_t), st));
+                rep.mode = REPLAY_COUNT_LIGHTS;
+                API_CUDA(h, launch_render_sample(h->scene, h->camera, h->rp, h->d_inv_tile.as<int2>(), s, 1, none, h->d_counters.as<DeviceCounters>(), st, rep));
+                API_CUDA(h, cudaMemcpyAsync(hv.data(), d_light.p, slots * nl * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+                API_CUDA(h, cudaStreamSynchronize(st));
+                for (size_t i = 0; i < slots; ++i) {
+                    for (int l = 0; l < nl; ++l) { uint32_t &v = hv[i * nl + l]; const uint32_t c = v; v = light_counter[l]; light_counter[l] += c; }
+                }
+                API_CUDA(h, cudaMemcpyAsync(d_light.p, hv.data(), slots * nl * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+                rep.mode = REPLAY_EXACT;
+                launches += 2;
+            }
             API_CUDA(h, launch_render_sample(h->scene, h->camera, h->rp, h->d_inv_tile.as<int2>(), s, d_bitmap ? s + 1 : k + 1, tg,
-                                             h->d_counters.as<DeviceCounters>(), st));
+                                             h->d_counters.as<DeviceCounters>(), st, rep));
             ++launches;
             while (h->sample_events.size() < depth) { cudaEvent_t e; API_CUDA(h, cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); h->sample_events.push_back(e); }
             API_CUDA(h, cudaEventRecord(h->sample_events[static_cast<size_t>(k) % depth], st));

@@ -19,7 +19,7 @@ MRT_D void flush_counters(const RayCounters &rc, DeviceCounters *dc) {
 // Shader::rayTrace, incrementalAvg. A warp covers an 8x4 pixel patch of one tile so that its rays stay coherent.
 template <int SHADER>
 __global__ void __launch_bounds__(128) k_render_sample(SceneDev s, CameraRec cam, RenderParams rp, const int2 *__restrict__ tile_origin,
-                                                       int sample, int avg_n, FrameTargets tg, DeviceCounters *dc) {
+                                                       int sample, int avg_n, FrameTargets tg, DeviceCounters *dc, ReplayArgs rep) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int patch = blockIdx.x * 4 + warp;
     RayCounters rc = {0u, 0u, 0u};
@@ -41,7 +41,29 @@ __global__ void __launch_bounds__(128) k_render_sample(SceneDev s, CameraRec cam
         generate_ray(cam, u, v, deviationU, deviationV, o, d);
         rc.primary = 1u;
         DrawState ds = {q, 0u, rp.seed};
-        const v3 rgb = ray_trace<SHADER>(s, rp, o, d, 1, ds, rc, &overflow);
+        bool counting = false;
+        if (rep.mode != REPLAY_OFF) {
+            // position of this pixel-sample in the reference's order within the sample (q counts across samples)
+            const uint32_t qi = q - static_cast<uint32_t>(sample) * static_cast<uint32_t>(kNumberOfTiles * rp.bsx * rp.bsy);
+            ds.mode = rep.mode;
+            if (rep.mode >= REPLAY_COUNT_LIGHTS) { ds.a_next = rep.index_draws[qi]; }
+            if (rep.mode == REPLAY_EXACT) {
+#pragma unroll
+                for (int k = 0; k < kReplayMaxLights; ++k) { if (k < rep.n_lights) { ds.l_next[k] = rep.light_draws[qi * rep.n_lights + k]; } }
+            }
+            if (rep.mode != REPLAY_EXACT) {
+                RayCounters scratch = {0u, 0u, 0u};
+                (void) ray_trace<SHADER>(s, rp, o, d, 1, ds, scratch, &overflow);
+                if (rep.mode == REPLAY_COUNT_INDEX) { rep.index_draws[qi] = ds.a_next; }
+                else {
+#pragma unroll
+                    for (int k = 0; k < kReplayMaxLights; ++k) { if (k < rep.n_lights) { rep.light_draws[qi * rep.n_lights + k] = ds.l_next[k]; } }
+                }
+                counting = true; rc.primary = 0u;
+            }
+        }
+        const v3 rgb = counting ? mk3(0.0f, 0.0f, 0.0f) : ray_trace<SHADER>(s, rp, o, d, 1, ds, rc, &overflow);
+        // (the counting passes are launched without targets)
         if (tg.bitmap != nullptr) { tg.bitmap[pix] = incremental_avg(rgb, tg.bitmap[pix], avg_n); }
         if (tg.accum != nullptr) {
             float4 a = tg.accum[pix];
@@ -163,15 +185,15 @@ __global__ void k_test_halton(uint32_t first, int64_t n, uint32_t base, float *o
 
 // ---- launchers ------------------------------------------------------------------------------------------------
 cudaError_t launch_render_sample(const SceneDev &s, const CameraRec &cam, const RenderParams &rp, const int2 *d_tile_origin,
-                                 int sample, int avg_n, FrameTargets tg, DeviceCounters *dc, cudaStream_t st) {
+                                 int sample, int avg_n, FrameTargets tg, DeviceCounters *dc, cudaStream_t st, ReplayArgs rep) {
     const int patches = kNumberOfTiles * ((rp.bsx + 7) / 8) * ((rp.bsy + 3) / 4);
     if (patches == 0) { return cudaSuccess; }
     const int blocks = (patches + 3) / 4;
     switch (rp.shader) {
-        case 1: k_render_sample<1><<<blocks, 128, 0, st>>>(s, cam, rp, d_tile_origin, sample, avg_n, tg, dc); break;
-        case 3: k_render_sample<3><<<blocks, 128, 0, st>>>(s, cam, rp, d_tile_origin, sample, avg_n, tg, dc); break;
-        case 4: k_render_sample<4><<<blocks, 128, 0, st>>>(s, cam, rp, d_tile_origin, sample, avg_n, tg, dc); break;
-        default: k_render_sample<0><<<blocks, 128, 0, st>>>(s, cam, rp, d_tile_origin, sample, avg_n, tg, dc); break;
+        case 1: k_render_sample<1><<<blocks, 128, 0, st>>>(s, cam, rp, d_tile_origin, sample, avg_n, tg, dc, rep); break;
+        case 3: k_render_sample<3><<<blocks, 128, 0, st>>>(s, cam, rp, d_tile_origin, sample, avg_n, tg, dc, rep); break;
+        case 4: k_render_sample<4><<<blocks, 128, 0, st>>>(s, cam, rp, d_tile_origin, sample, avg_n, tg, dc, rep); break;
+        default: k_render_sample<0><<<blocks, 128, 0, st>>>(s, cam, rp, d_tile_origin, sample, avg_n, tg, dc, rep); break;
     }
     return cudaGetLastError();
 }

@@ -16,9 +16,19 @@ struct DeviceCounters {   // device memory, zeroed per frame
     int pad;
 };
 
+// Exact replay of the reference's draw order (MRT_FLAG_REPLAY_SAMPLERS): arrays indexed by the pixel-sample's position
+// in the reference's single-thread order within one sample (tile, then row-major inside the tile).
+struct ReplayArgs {
+    int32_t mode;            // ReplayMode (mrt_shade.cuh)
+    int32_t n_lights;
+    uint32_t *index_draws;   // [P] mode 1 writes the count, modes 2/3 read the counter value at the pixel-sample's first draw
+    uint32_t *light_draws;   // [P * n_lights] mode 2 writes the counts, mode 3 reads the counter values
+};
+
 // One sample of every pixel through the fused megakernel (deterministic shaders: NoShadows, Whitted, DepthMap, Diffuse).
 cudaError_t launch_render_sample(const SceneDev &s, const CameraRec &cam, const RenderParams &rp, const int2 *d_tile_origin,
-                                 int sample, int sample_number_for_avg, FrameTargets tg, DeviceCounters *d_counters, cudaStream_t st);
+                                 int sample, int sample_number_for_avg, FrameTargets tg, DeviceCounters *d_counters, cudaStream_t st,
+                                 ReplayArgs replay = ReplayArgs {0, 0, nullptr, nullptr});
 cudaError_t launch_resolve(const float4 *accum, int32_t *bitmap, int n_pixels, cudaStream_t st);
 
 cudaError_t launch_trace_rays(const SceneDev &s, int64_t n, const float *o, const float *d, const int32_t *okind, const int32_t *oidx,

@@ -65,6 +65,9 @@ struct DrawState {
     uint32_t q;         // pixel-sample sequence id
     uint32_t e;         // running event counter of this pixel-sample
     uint32_t seed;
+    int32_t mode;       // ReplayMode
+    uint32_t a_next;    // value of Shader::getLightIndex's counter (Shader.cpp:224) at this pixel-sample's next draw
+    uint32_t l_next[kReplayMaxLights];   // per light: value of its sampler's counter (AreaLight.cpp:18-19) at the next draw
 };
 enum DrawStream : uint32_t { DS_LIGHT_INDEX = 1, DS_LIGHT_POS = 2, DS_HEMI = 3, DS_RR = 4 };
 
@@ -140,14 +143,24 @@ MRT_D void resolve_surface(const SceneDev &s, v3 o, v3 d, const HitRec &h, Surfa
 
 // Shader::getLightIndex (Shader.cpp:223-233)
 MRT_D uint32_t light_index(const SceneDev &s, DrawState &ds) {
-    const float r = draw(s.shader_table, ds, DS_LIGHT_INDEX);
+    const float r = ds.mode == REPLAY_OFF ? draw(s.shader_table, ds, DS_LIGHT_INDEX)
+                                          : __ldg(s.shader_table + ((ds.a_next++) & kArrayMask));
     return static_cast<uint32_t>(floorf(r * static_cast<float>(static_cast<uint32_t>(s.n_lights)) * 0.99999f));
 }
 // PointLight::getPosition (PointLight.cpp:16-18) / AreaLight::getPosition (AreaLight.cpp:17-26)
-MRT_D v3 light_position(const SceneDev &s, const LightRec &l, DrawState &ds) {
+MRT_D v3 light_position(const SceneDev &s, const LightRec &l, DrawState &ds, uint32_t chosen) {
     if (l.kind == 0) { return mk3(l.A[0], l.A[1], l.A[2]); }
-    float r = draw(s.static_halton, ds, DS_LIGHT_POS);
-    float q = draw(s.static_halton, ds, DS_LIGHT_POS);
+    float r, q;
+    if (ds.mode == REPLAY_OFF) {
+        r = draw(s.static_halton, ds, DS_LIGHT_POS);
+        q = draw(s.static_halton, ds, DS_LIGHT_POS);
+    } else {
+        uint32_t c = 0u;   // l_next[chosen] without dynamic indexing (keeps the array in registers)
+#pragma unroll
+        for (int k = 0; k < kReplayMaxLights; ++k) { if (static_cast<uint32_t>(k) == chosen) { c = ds.l_next[k]; ds.l_next[k] = c + 2u; } }
+        r = __ldg(s.static_halton + (c & kArrayMask));
+        q = __ldg(s.static_halton + ((c + 1u) & kArrayMask));
+    }
     if (r + q >= 1.0f) { r = 1.0f - r; q = 1.0f - q; }
     return (mk3(l.A[0], l.A[1], l.A[2]) + r * mk3(l.AB[0], l.AB[1], l.AB[2])) + q * mk3(l.AC[0], l.AC[1], l.AC[2]);
 }
@@ -159,10 +172,12 @@ template <bool SHADOWS>
 MRT_D v3 direct_light(const SceneDev &s, const RenderParams &rp, const Surface &sf, DrawState &ds, RayCounters &rc, int *overflow) {
     v3 rgb = mk3(0.0f, 0.0f, 0.0f);
     if (has_positive(sf.Kd) && s.n_lights > 0) {
+        if (ds.mode == REPLAY_COUNT_INDEX) { ds.a_next += static_cast<uint32_t>(rp.spl); return rgb; }
         for (int i = 0; i < rp.spl; ++i) {
             const uint32_t chosen = light_index(s, ds);
             const LightRec &l = s.lights[chosen];
-            const v3 lightPosition = light_position(s, l, ds);
+            const v3 lightPosition = light_position(s, l, ds, chosen);
+            if (ds.mode == REPLAY_COUNT_LIGHTS) { continue; }
             v3 vectorToLight = lightPosition - sf.point;
             const float distanceToLight = length(vectorToLight);
             vectorToLight = normalize(vectorToLight);

@@ -85,4 +85,13 @@ struct RenderParams {
     uint32_t seed;
 };
 
+// MRT_FLAG_REPLAY_SAMPLERS (mrt_shade.cuh DrawState, mrt_render.h ReplayArgs)
+constexpr int kReplayMaxLights = 8;
+enum ReplayMode : int32_t {
+    REPLAY_OFF = 0,           // hashed slots
+    REPLAY_COUNT_INDEX = 1,   // count this pixel-sample's Shader::getLightIndex draws, shade nothing
+    REPLAY_COUNT_LIGHTS = 2,  // getLightIndex draws exact; count the draws each light's own sampler receives
+    REPLAY_EXACT = 3          // every draw at the reference's counter value
+};
+
 }  // namespace mrt

@@ -454,7 +454,7 @@ __global__ void __launch_bounds__(kWfThreads, MRT_SHADE_MIN_BLOCKS) k_wf_shade(S
             for (int k = 0; k < rp.spl; ++k) {
                 const uint32_t chosen = light_index(s, ds);
                 const LightRec &l = s.lights[chosen];
-                const v3 lightPosition = light_position(s, l, ds);
+                const v3 lightPosition = light_position(s, l, ds, chosen);
                 v3 vectorToLight = lightPosition - sf.point;
                 const float distanceToLight = length(vectorToLight);
                 vectorToLight = normalize(vectorToLight);

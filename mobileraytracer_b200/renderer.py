@@ -104,6 +104,15 @@ class Renderer:
     def stopRender(self):
         capi.lib().mrt_stop(self._h)
 
+    def setReplayCounter(self, light_index_counter):
+        """FLAG_REPLAY_SAMPLERS: value of Shader::getLightIndex's process-global counter at the next frame's first draw."""
+        capi.check(capi.lib().mrt_set_replay_counter(self._h, C.c_uint32(int(light_index_counter) & 0xFFFFFFFF)), self._h)
+
+    def getReplayCounter(self):
+        v = C.c_uint32(0)
+        capi.check(capi.lib().mrt_get_replay_counter(self._h, C.byref(v)), self._h)
+        return v.value
+
     def getSample(self):
         v = C.c_int32(0)
         capi.lib().mrt_get_sample(self._h, C.byref(v))

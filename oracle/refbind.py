@@ -77,6 +77,8 @@ def lib():
             f = getattr(L, "mrt_ref_table_" + t)
             f.restype = C.POINTER(C.c_float)
             f.argtypes = [C.POINTER(C.c_uint)]
+        L.mrt_ref_light_index_counter.restype = C.c_uint
+        L.mrt_ref_light_index_counter.argtypes = []
         _lib = L
     return _lib
 
@@ -95,6 +97,11 @@ def table(which):
     n = C.c_uint(0)
     ptr = getattr(lib(), "mrt_ref_table_" + which)(C.byref(n))
     return np.ctypeslib.as_array(ptr, shape=(n.value,)).copy()
+
+
+def light_index_counter():
+    """Value of the function-static counter inside Shader::getLightIndex (Shader.cpp:224): process-global, never reset."""
+    return int(lib().mrt_ref_light_index_counter())
 
 
 class RefRenderer:

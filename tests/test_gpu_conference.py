@@ -231,7 +231,7 @@ def test_conference_incoherent_rays_match_reference(mrt, ref, conf, shader):
 def test_deterministic_shaders_with_area_lights_agree_statistically(mrt, ref, shader):
     """Scene 2 has two area lights, so Whitted / NoShadows draw light indices and light positions from the reference's
     global counters in its execution order (Shader.cpp:223-233, AreaLight.cpp:17-26): without a replay of that order
-    (MRT_FLAG_REPLAY_SAMPLERS, reserved) the frames can only agree as Monte-Carlo estimates. Same bars as the path tracer:
+    (MRT_FLAG_REPLAY_SAMPLERS, tested below) the frames can only agree as Monte-Carlo estimates. Same bars as the path tracer:
     mean luminance within 1 %, block means within the noise measured between two reference renders, ray counts within 1 %."""
     w = h = 96
     spp = 128
@@ -252,4 +252,42 @@ def test_deterministic_shaders_with_area_lights_agree_statistically(mrt, ref, sh
     ratio = g.getTotalCastedRays() / float(r.casted_rays())     # a shadow ray is only cast when the sampled light point is in front
     assert 0.99 < ratio < 1.01, ratio
     g.close()
+    r.close()
+
+
+@pytest.mark.parametrize("shader,spp,spl", [(1, 1, 1), (0, 1, 1), (1, 3, 2)])
+def test_replay_samplers_reproduces_reference_draw_order(mrt, ref, shader, spp, spl):
+    """MRT_FLAG_REPLAY_SAMPLERS: on scene 2 (two area lights) every getLightIndex / AreaLight::getPosition draw reads the
+    table entry the reference's single-thread frame reads (Shader.cpp:223-233, AreaLight.cpp:17-26), so the frames agree
+    like the single-light scenes do: bit for bit. Two frames in a row: the getLightIndex counter runs on across frames
+    (function-static), the lights' own counters restart (Renderer.cpp:58-59)."""
+    from mobileraytracer_b200 import capi
+    w = h = 128
+    r = ref.RefRenderer(w, h, shader, 2, spp=spp, spl=spl)
+    c0 = ref.light_index_counter()
+    bm_ref1, _ = r.render(threads=1)
+    c1, rays1 = ref.light_index_counter(), r.casted_rays()
+    bm_ref2, _ = r.render(threads=1)
+    c2, rays2 = ref.light_index_counter(), r.casted_rays() - rays1
+    assert c1 > c0
+    g = H.gpu_from_ref(ref, r, 2, shader, w, h, spp=spp, spl=spl, flags=capi.FLAG_REPLAY_SAMPLERS)
+    g.setReplayCounter(c0)
+    bm1 = g.renderFrame().copy()
+    assert g.getReplayCounter() == c1 & 0xFFFFFFFF       # as many index draws as the reference made
+    assert g.getTotalCastedRays() == rays1               # shadow rays are cast only towards sampled points in front
+    bm2 = g.renderFrame().copy()
+    assert g.getReplayCounter() == c2 & 0xFFFFFFFF
+    assert g.getTotalCastedRays() == rays2
+    for bm, bm_ref in ((bm1, bm_ref1), (bm2, bm_ref2)):
+        c = H.compare_bitmaps(bm, bm_ref)
+        assert c["exact"] >= 0.999 and c["max"] <= 1 or c["exact"] >= 0.9999, c
+    g.close()
+    r.close()
+
+
+def test_replay_samplers_rejected_for_path_tracer(mrt, ref):
+    from mobileraytracer_b200 import capi
+    r = ref.RefRenderer(32, 32, 2, 2, spp=1)
+    with pytest.raises(Exception):
+        H.gpu_from_ref(ref, r, 2, 2, 32, 32, flags=capi.FLAG_REPLAY_SAMPLERS)
     r.close()
