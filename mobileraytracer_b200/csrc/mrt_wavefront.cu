@@ -12,6 +12,7 @@
 //   ended on emitter     : total = sum over depths <= first depth with direct light (+ the emitter term if there is none)
 #include "mrt_wavefront.h"
 #include "mrt_shade.cuh"
+#include <cstdlib>
 #include <vector>
 
 namespace mrt {
@@ -55,6 +56,13 @@ struct Wavefront {
     std::vector<WfMark> marks;        // one event after every launch; the class says what ran before it
     std::vector<cudaEvent_t> pool;
     size_t used = 0;
+    // shadow(level) and extend(level + 1) only share the scene; with MRT_B200_OVERLAP=1 they run on two streams so that
+    // each persistent kernel's CTAs move into the SM slots the other's finished CTAs leave. Measured on the bench frame:
+    // 249.4 -> 248.2 ms (the dynamic work counter already keeps the tails short), so it is off by default, which keeps
+    // the per-kernel event times free of sharing.
+    cudaStream_t side = nullptr;
+    cudaEvent_t shaded = nullptr, shadowed = nullptr;
+    bool overlap = false;
 };
 
 // A fresh chain record, written as eight full 16-byte stores: all four 32-byte sectors of the line are completely
@@ -522,12 +530,16 @@ __global__ void __launch_bounds__(kWfThreads, MRT_SHADE_MIN_BLOCKS) k_wf_shade(S
     if (overflow) { dc->overflow = 1; }
 }
 
-__global__ void k_wf_end_level(Queues Q, int level, DeviceCounters *dc) {
+// bookkeeping after shade(level) (main stream) and after shadow(level) (side stream); the two touch disjoint words
+__global__ void k_wf_after_shade(Queues Q, int level, DeviceCounters *dc) {
     dc->extend_traced += min(Q.counts[level], Q.cap_rays);
-    dc->shadow_traced += min(Q.counts[8], Q.cap_shadow);
-    Q.counts[kCounterExtend] = 0u; Q.counts[kCounterShadow] = 0u;   // work counters of the persistent traversal kernels
-    Q.counts[8] = 0u;                         // shadow queue consumed
+    Q.counts[kCounterExtend] = 0u;            // work counter of the persistent extend kernel
     Q.counts[10 + level] = min(Q.counts[9], Q.cap_chains);   // chain pool size after this level
+}
+__global__ void k_wf_after_shadow(Queues Q, DeviceCounters *dc) {
+    dc->shadow_traced += min(Q.counts[8], Q.cap_shadow);
+    Q.counts[kCounterShadow] = 0u;
+    Q.counts[8] = 0u;                         // shadow queue consumed
 }
 
 // The whole 128-byte record comes in as eight independent 16-byte loads (one dependent scalar load after the other made
@@ -630,6 +642,11 @@ cudaError_t wavefront_create(int width, int height, int batch, Wavefront **out) 
     WF_TRY(wf_alloc(w, &q.s0, q.cap_shadow)); WF_TRY(wf_alloc(w, &q.s1, q.cap_shadow)); WF_TRY(wf_alloc(w, &q.s2, q.cap_shadow));
     WF_TRY(wf_alloc(w, &q.chains, q.cap_chains));
     WF_TRY(wf_alloc(w, &q.counts, kWfCounts));
+    const char *ov = std::getenv("MRT_B200_OVERLAP");
+    w->overlap = ov && std::atoi(ov) != 0;
+    WF_TRY(cudaStreamCreateWithFlags(&w->side, cudaStreamNonBlocking));
+    WF_TRY(cudaEventCreateWithFlags(&w->shaded, cudaEventDisableTiming));
+    WF_TRY(cudaEventCreateWithFlags(&w->shadowed, cudaEventDisableTiming));
     return cudaSuccess;
 }
 
@@ -637,6 +654,9 @@ void wavefront_destroy(Wavefront *w) {
     if (!w) { return; }
     WavefrontHost *hst = host_of(w);
     for (cudaEvent_t e : hst->pool) { cudaEventDestroy(e); }
+    if (w->shaded) { cudaEventDestroy(w->shaded); }
+    if (w->shadowed) { cudaEventDestroy(w->shadowed); }
+    if (w->side) { cudaStreamDestroy(w->side); }
     for (void *p : w->allocs) { cudaFree(p); }
     delete w;
 }
@@ -693,16 +713,24 @@ cudaError_t wavefront_render_batch(Wavefront *w, const SceneDev &s, const Camera
     k_wf_begin_levels<<<1, 1, 0, st>>>(Q, static_cast<uint32_t>(n_samples), roots_per_sample);
     WF_TRY(wf_mark(hst, WF_OTHER, st));
     *launches += 1;
+    // per level: extend -> shade on the main stream; shadow(level) on the side stream, concurrent with extend(level + 1);
+    // shade(level + 1) pushes into the shadow queue, so it waits for shadow(level)
+    cudaStream_t sb = hst->overlap ? hst->side : st;
     for (int level = 0; level < kLevels; ++level) {
         k_wf_extend<<<grid, kWfThreads, 0, st>>>(s, Q, level, dc);
         WF_TRY(wf_mark(hst, WF_EXTEND, st));
+        if (hst->overlap && level > 0) { WF_TRY(cudaStreamWaitEvent(st, hst->shadowed, 0)); WF_TRY(wf_mark(hst, -1, st)); }
         k_wf_shade<<<hst->sm_count * MRT_SHADE_MIN_BLOCKS, kWfThreads, 0, st>>>(s, rp, Q, level, dc);
         WF_TRY(wf_mark(hst, WF_SHADE, st));
-        k_wf_shadow<<<grid, kWfThreads, 0, st>>>(s, Q, dc);
-        WF_TRY(wf_mark(hst, WF_SHADOW, st));
-        k_wf_end_level<<<1, 1, 0, st>>>(Q, level, dc);
-        *launches += 4;
+        k_wf_after_shade<<<1, 1, 0, st>>>(Q, level, dc);
+        if (hst->overlap) { WF_TRY(cudaEventRecord(hst->shaded, st)); WF_TRY(cudaStreamWaitEvent(sb, hst->shaded, 0)); WF_TRY(wf_mark(hst, -1, sb)); }
+        k_wf_shadow<<<grid, kWfThreads, 0, sb>>>(s, Q, dc);
+        WF_TRY(wf_mark(hst, WF_SHADOW, sb));
+        k_wf_after_shadow<<<1, 1, 0, sb>>>(Q, dc);
+        if (hst->overlap) { WF_TRY(cudaEventRecord(hst->shadowed, sb)); WF_TRY(wf_mark(hst, -1, st)); }
+        *launches += 5;
     }
+    if (hst->overlap) { WF_TRY(cudaStreamWaitEvent(st, hst->shadowed, 0)); WF_TRY(wf_mark(hst, -1, st)); }
     for (int level = kLevels - 1; level >= 0; --level) {
         k_wf_finalize_level<<<grid, kWfThreads, 0, st>>>(Q, level);
         *launches += 1;
