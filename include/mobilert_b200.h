@@ -82,7 +82,8 @@ enum { MRT_SHADER_NOSHADOWS = 0, MRT_SHADER_WHITTED = 1, MRT_SHADER_PATHTRACER =
 /* MobileRT/Shader.hpp:20-24 plus the new value a front-end selects to get this library */
 enum { MRT_ACC_NAIVE = 1, MRT_ACC_REGULAR_GRID = 2, MRT_ACC_BVH = 3, MRT_ACC_B200 = 4 };
 /* pixel-jitter sampler (C_wrapper.cpp:144-148 picks Constant(0.5) for spp==1, StaticHaltonSeq otherwise) */
-enum { MRT_SAMPLER_AUTO = 0, MRT_SAMPLER_CONSTANT = 1, MRT_SAMPLER_STATIC_HALTON = 2, MRT_SAMPLER_STATIC_MT = 3 };
+enum { MRT_SAMPLER_AUTO = 0, MRT_SAMPLER_CONSTANT = 1, MRT_SAMPLER_STATIC_HALTON = 2, MRT_SAMPLER_STATIC_MT = 3,
+       MRT_SAMPLER_STATIC_PCG = 4 /* the Android front-end's choice (JNI_layer.cpp:601,616-618,636; Components/Samplers/StaticPCG.cpp) */ };
 
 enum {
     MRT_FLAG_FP32_ACCUMULATE = 1,  /* accumulate radiance in fp32 and quantise once (needed for multi-GPU partitions);
@@ -110,17 +111,22 @@ typedef struct mrt_render_desc {
     uint32_t flags;                 /* MRT_FLAG_* */
     float depth_max_point[3];       /* DepthMap's maxPoint (Components/Shaders/DepthMap.cpp:7-10) */
     int32_t device;                 /* CUDA device ordinal; -1 = current */
+    int32_t light_sampler;          /* table behind the samplers the front-end creates itself, i.e. the area lights of an OBJ scene
+                                       (OBJLoader::fillScene's lambda) and the PathTracer's russian roulette: MRT_SAMPLER_AUTO or
+                                       _STATIC_HALTON (C_wrapper.cpp:109,176), or MRT_SAMPLER_STATIC_PCG (JNI_layer.cpp:601,636) */
 } mrt_render_desc;
 
 /* The reference's shuffled tables, when the caller wants the very same sequences (parity runs):
  * tile_order = Renderer.cpp:12 (256 floats); shader_table = Shader.cpp:20 (1<<20 floats, getLightIndex and
  * getCosineSampleHemisphere); static_halton = Components/Samplers/StaticHaltonSeq.cpp:7 (1<<20, pixel jitter, area
- * lights, russian roulette); static_mt = StaticMersenneTwister.cpp:7. Any pointer may be NULL. */
+ * lights, russian roulette); static_mt = StaticMersenneTwister.cpp:7; static_pcg = StaticPCG.cpp:8. Any pointer may be
+ * NULL: the library then fills its own table the way the reference does (Utils.hpp:209-252) from mrt_render_desc::seed. */
 typedef struct mrt_sampler_tables {
     const float *tile_order;
     const float *shader_table;
     const float *static_halton;
     const float *static_mt;
+    const float *static_pcg;
 } mrt_sampler_tables;
 
 typedef struct mrt_stats {

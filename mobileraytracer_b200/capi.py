@@ -10,7 +10,7 @@ LIB_PATH = os.environ.get("MRT_B200_LIB") or os.path.join(_HERE, "libmobilert_b2
 MRT_OK, MRT_ERR_INVALID, MRT_ERR_CUDA, MRT_ERR_OOM, MRT_ERR_STOPPED, MRT_ERR_OVERFLOW = range(6)
 SHADER_NOSHADOWS, SHADER_WHITTED, SHADER_PATHTRACER, SHADER_DEPTHMAP, SHADER_DIFFUSE = range(5)
 ACC_NAIVE, ACC_REGULAR_GRID, ACC_BVH, ACC_B200 = 1, 2, 3, 4
-SAMPLER_AUTO, SAMPLER_CONSTANT, SAMPLER_STATIC_HALTON, SAMPLER_STATIC_MT = range(4)
+SAMPLER_AUTO, SAMPLER_CONSTANT, SAMPLER_STATIC_HALTON, SAMPLER_STATIC_MT, SAMPLER_STATIC_PCG = range(5)
 FLAG_FP32_ACCUMULATE, FLAG_SORT_BY_MATERIAL, FLAG_REPLAY_SAMPLERS = 1, 2, 4
 CAMERA_PERSPECTIVE, CAMERA_ORTHOGRAPHIC = 0, 1
 LIGHT_POINT, LIGHT_AREA = 0, 1
@@ -46,12 +46,12 @@ class CameraDesc(C.Structure):
 class RenderDesc(C.Structure):
     _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("samples_pixel", C.c_int32), ("samples_light", C.c_int32),
                 ("shader", C.c_int32), ("accelerator", C.c_int32), ("pixel_sampler", C.c_int32), ("seed", C.c_uint32),
-                ("flags", C.c_uint32), ("depth_max_point", C.c_float * 3), ("device", C.c_int32)]
+                ("flags", C.c_uint32), ("depth_max_point", C.c_float * 3), ("device", C.c_int32), ("light_sampler", C.c_int32)]
 
 
 class SamplerTables(C.Structure):
     _fields_ = [("tile_order", C.c_void_p), ("shader_table", C.c_void_p), ("static_halton", C.c_void_p),
-                ("static_mt", C.c_void_p)]
+                ("static_mt", C.c_void_p), ("static_pcg", C.c_void_p)]
 
 
 class Stats(C.Structure):

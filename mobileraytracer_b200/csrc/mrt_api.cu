@@ -52,7 +52,7 @@ struct mrt_handle {
     uint32_t flags = 0;
     Bvh8 bvh {};
     DevMem d_tris9, d_tri_shade, d_sphere_nodes, d_spheres, d_plane_nodes, d_planes, d_materials, d_lights;
-    DevMem d_tile, d_shader_table, d_static_halton, d_static_mt, d_inv_tile, d_tile_base, d_textures, d_texels, d_bitmap, d_accum, d_counters, d_scratch;
+    DevMem d_tile, d_shader_table, d_static_halton, d_static_mt, d_static_pcg, d_inv_tile, d_tile_base, d_textures, d_texels, d_bitmap, d_accum, d_counters, d_scratch;
     std::vector<int> plane_slot_of_id, sphere_slot_of_id;
     int32_t *h_pinned_bitmap = nullptr;
     size_t pinned_bytes = 0;
@@ -114,6 +114,24 @@ void make_mt_table(std::vector<float> &t, size_t n, uint32_t seed) {
     std::uniform_real_distribution<float> dist(0.0f, 1.0f);
     std::mt19937 gen(seed);
     for (size_t i = 0; i < n; ++i) { t[i] = dist(gen); }
+}
+
+// fillArrayWithPCG (Utils.hpp:246-252): pcg32 (XSH-RR 64/32, pcg_random.hpp) through uniform_real_distribution<float>,
+// i.e. one 32-bit draw / 2^32 (libstdc++ generate_canonical<float, 24>), kept below 1; seeded by the caller here
+void make_pcg_table(std::vector<float> &t, size_t n, uint32_t seed) {
+    t.resize(n);
+    const uint64_t mult = 6364136223846793005ull, inc = 1442695040888963407ull;
+    uint64_t state = 0ull;
+    state = state * mult + inc; state += seed; state = state * mult + inc;
+    for (size_t i = 0; i < n; ++i) {
+        const uint64_t old = state;
+        state = old * mult + inc;
+        const uint32_t xs = static_cast<uint32_t>(((old >> 18) ^ old) >> 27), rot = static_cast<uint32_t>(old >> 59);
+        const uint32_t r = (xs >> rot) | (xs << ((32u - rot) & 31u));
+        float f = static_cast<float>(r) / 4294967296.0f;
+        if (f >= 1.0f) { f = std::nextafter(1.0f, 0.0f); }
+        t[i] = f;
+    }
 }
 
 int upload_scene(mrt_handle *h, const mrt_scene_desc &sc) {
@@ -280,7 +298,7 @@ int upload_scene(mrt_handle *h, const mrt_scene_desc &sc) {
 
 int upload_tables(mrt_handle *h, const mrt_render_desc &rd, const mrt_sampler_tables *tb) {
     cudaStream_t st = h->stream;
-    std::vector<float> tile, shader, sh, smt;
+    std::vector<float> tile, shader, sh, smt, spcg;
     const float *p_tile = tb ? tb->tile_order : nullptr, *p_shader = tb ? tb->shader_table : nullptr;
     const float *p_sh = tb ? tb->static_halton : nullptr, *p_smt = tb ? tb->static_mt : nullptr;
     if (!p_tile) { make_halton_table(tile, kNumberOfTiles, rd.seed * 4u + 0u); p_tile = tile.data(); }
@@ -288,6 +306,9 @@ int upload_tables(mrt_handle *h, const mrt_render_desc &rd, const mrt_sampler_ta
     if (!p_sh) { make_halton_table(sh, kArraySize, rd.seed * 4u + 2u); p_sh = sh.data(); }
     const bool need_mt = rd.pixel_sampler == MRT_SAMPLER_STATIC_MT;
     if (need_mt && !p_smt) { make_mt_table(smt, kArraySize, rd.seed * 4u + 3u); p_smt = smt.data(); }
+    const float *p_pcg = tb ? tb->static_pcg : nullptr;
+    const bool need_pcg = rd.pixel_sampler == MRT_SAMPLER_STATIC_PCG || rd.light_sampler == MRT_SAMPLER_STATIC_PCG;
+    if (need_pcg && !p_pcg) { make_pcg_table(spcg, kArraySize, rd.seed * 4u + 5u); p_pcg = spcg.data(); }
     // Renderer::renderScene's tile -> first pixel mapping (Renderer.cpp:125-133), integer for integer
     std::vector<int2> origin(kNumberOfTiles, make_int2(0, 0));
     std::vector<uint32_t> tile_base(kNumberOfTiles + 1, 0u);   // valid pixels before each tile (the wavefront's deterministic path slots)
@@ -318,6 +339,7 @@ int upload_tables(mrt_handle *h, const mrt_render_desc &rd, const mrt_sampler_ta
     API_CUDA(h, h->d_shader_table.upload(p_shader, kArraySize * sizeof(float), st));
     API_CUDA(h, h->d_static_halton.upload(p_sh, kArraySize * sizeof(float), st));
     if (need_mt) { API_CUDA(h, h->d_static_mt.upload(p_smt, kArraySize * sizeof(float), st)); }
+    if (need_pcg) { API_CUDA(h, h->d_static_pcg.upload(p_pcg, kArraySize * sizeof(float), st)); }
     API_CUDA(h, h->d_inv_tile.upload(origin.data(), origin.size() * sizeof(int2), st));
     API_CUDA(h, h->d_tile_base.upload(tile_base.data(), tile_base.size() * sizeof(uint32_t), st));
     h->roots_per_sample = tile_base[kNumberOfTiles];
@@ -327,7 +349,11 @@ int upload_tables(mrt_handle *h, const mrt_render_desc &rd, const mrt_sampler_ta
     int ps = rd.pixel_sampler;
     if (ps == MRT_SAMPLER_AUTO) { ps = rd.samples_pixel > 1 ? MRT_SAMPLER_STATIC_HALTON : MRT_SAMPLER_CONSTANT; }  // C_wrapper.cpp:144-148
     h->rp.pixel_sampler = ps;
-    s.pixel_table = ps == MRT_SAMPLER_STATIC_HALTON ? s.static_halton : (ps == MRT_SAMPLER_STATIC_MT ? h->d_static_mt.as<float>() : nullptr);
+    s.pixel_table = ps == MRT_SAMPLER_STATIC_HALTON ? s.static_halton
+                  : ps == MRT_SAMPLER_STATIC_MT ? h->d_static_mt.as<float>()
+                  : ps == MRT_SAMPLER_STATIC_PCG ? h->d_static_pcg.as<float>() : nullptr;
+    // from here on `static_halton` is the table of the area lights' and the russian roulette's samplers
+    if (rd.light_sampler == MRT_SAMPLER_STATIC_PCG) { s.static_halton = h->d_static_pcg.as<float>(); }
     return MRT_OK;
 }
 
@@ -373,6 +399,10 @@ int mrt_create(const mrt_scene_desc *scene, const mrt_camera_desc *camera, const
     if (scene->n_triangles < 0 || scene->n_spheres < 0 || scene->n_planes < 0 || scene->n_materials < 0 || scene->n_lights < 0) { return fail(nullptr, MRT_ERR_INVALID, "negative count"); }
     if ((scene->n_triangles && !scene->triangles) || (scene->n_spheres && !scene->spheres) || (scene->n_planes && !scene->planes) ||
         (scene->n_materials && !scene->materials) || (scene->n_lights && !scene->lights)) { return fail(nullptr, MRT_ERR_INVALID, "null array with non-zero count"); }
+    if (render->pixel_sampler < MRT_SAMPLER_AUTO || render->pixel_sampler > MRT_SAMPLER_STATIC_PCG) { return fail(nullptr, MRT_ERR_INVALID, "unknown pixel_sampler"); }
+    if (render->light_sampler != MRT_SAMPLER_AUTO && render->light_sampler != MRT_SAMPLER_STATIC_HALTON && render->light_sampler != MRT_SAMPLER_STATIC_PCG) {
+        return fail(nullptr, MRT_ERR_INVALID, "light_sampler must be MRT_SAMPLER_AUTO, _STATIC_HALTON or _STATIC_PCG");
+    }
     if (render->flags & MRT_FLAG_REPLAY_SAMPLERS) {
         if (render->shader == MRT_SHADER_PATHTRACER) { return fail(nullptr, MRT_ERR_INVALID, "MRT_FLAG_REPLAY_SAMPLERS: the PathTracer's ray tree depends on the draws themselves; only NoShadows / Whitted can be replayed"); }
         if (scene->n_lights > kReplayMaxLights) { return fail(nullptr, MRT_ERR_INVALID, "MRT_FLAG_REPLAY_SAMPLERS supports up to 8 lights"); }

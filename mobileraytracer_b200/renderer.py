@@ -44,7 +44,7 @@ class Renderer:
 
     def __init__(self, scene, camera, width, height, samplesPixel, samplesLight=1, shader=capi.SHADER_WHITTED,
                  accelerator=capi.ACC_B200, depth_max_point=(1, 1, 1), pixel_sampler=capi.SAMPLER_AUTO, seed=1, flags=0,
-                 tables=None, device=-1):
+                 tables=None, device=-1, light_sampler=capi.SAMPLER_AUTO):
         L = capi.lib()
         arr = scene.arrays() if isinstance(scene, S.Scene) else scene
         self._keep = arr
@@ -66,6 +66,7 @@ class Renderer:
         rd = capi.RenderDesc()
         rd.width, rd.height, rd.samples_pixel, rd.samples_light = width, height, samplesPixel, samplesLight
         rd.shader, rd.accelerator, rd.pixel_sampler, rd.seed, rd.flags, rd.device = shader, accelerator, pixel_sampler, seed, flags, device
+        rd.light_sampler = light_sampler
         for k in range(3):
             rd.depth_max_point[k] = float(depth_max_point[k])
         tb = None

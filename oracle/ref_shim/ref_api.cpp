@@ -15,6 +15,7 @@
 #include "Components/Loaders/OBJLoader.hpp"
 #include "Components/Samplers/Constant.hpp"
 #include "Components/Samplers/StaticHaltonSeq.hpp"
+#include "Components/Samplers/StaticPCG.hpp"
 #include "Components/Shaders/DepthMap.hpp"
 #include "Components/Shaders/DiffuseMaterial.hpp"
 #include "Components/Shaders/NoShadows.hpp"
@@ -36,6 +37,7 @@ using namespace MobileRT;
 struct RefConfig {
     int width, height, threads, shader, scene, spp, spl, accelerator;
     const char *obj, *mtl, *cam;
+    int samplers;   // 0: the Linux front-end's choice (StaticHaltonSeq, C_wrapper.cpp:144-148,176); 1: Android's (StaticPCG, JNI_layer.cpp:601,616-618,636)
 };
 
 struct RefHandle {
@@ -105,8 +107,11 @@ void *ref_create(const RefConfig *c) {
                 if (!objLoader.isProcessed()) { delete h; return nullptr; }
                 const double t1 = now();
                 ::std::unordered_map<::std::string, Texture> texturesCache {};
+                const bool pcg {c->samplers == 1};
                 if (!objLoader.fillScene(&scene,
-                        []() { return ::MobileRT::std::make_unique<::Components::StaticHaltonSeq>(); },
+                        [pcg]() -> ::std::unique_ptr<Sampler> {
+                            if (pcg) { return ::MobileRT::std::make_unique<::Components::StaticPCG>(); }
+                            return ::MobileRT::std::make_unique<::Components::StaticHaltonSeq>(); },
                         c->obj, texturesCache)) { delete h; return nullptr; }
                 const double t2 = now();
                 h->secsLoad = t1 - t0; h->secsFill = t2 - t1;
@@ -119,7 +124,9 @@ void *ref_create(const RefConfig *c) {
             } break;
         }
         if (dynamic_cast<::Components::Orthographic *>(camera.get()) != nullptr) { h->cameraKind = 1; }
-        if (c->spp > 1) {
+        if (c->spp > 1 && c->samplers == 1) {
+            samplerPixel = ::MobileRT::std::make_unique<::Components::StaticPCG>();
+        } else if (c->spp > 1) {
             samplerPixel = ::MobileRT::std::make_unique<::Components::StaticHaltonSeq>();
         } else {
             samplerPixel = ::MobileRT::std::make_unique<::Components::Constant>(0.5F);
@@ -129,7 +136,9 @@ void *ref_create(const RefConfig *c) {
         switch (c->shader) {
             case 1: shader = ::MobileRT::std::make_unique<::Components::Whitted>(::std::move(scene), c->spl, acc); break;
             case 2: {
-                ::std::unique_ptr<Sampler> rr {::MobileRT::std::make_unique<::Components::StaticHaltonSeq>()};
+                ::std::unique_ptr<Sampler> rr {};
+                if (c->samplers == 1) { rr = ::MobileRT::std::make_unique<::Components::StaticPCG>(); }
+                else { rr = ::MobileRT::std::make_unique<::Components::StaticHaltonSeq>(); }
                 shader = ::MobileRT::std::make_unique<::Components::PathTracer>(::std::move(scene), ::std::move(rr), c->spl, acc);
             } break;
             case 3: shader = ::MobileRT::std::make_unique<::Components::DepthMap>(::std::move(scene), maxDist, acc); break;

@@ -22,7 +22,7 @@ assert TRI_DTYPE.itemsize == 100 and SPH_DTYPE.itemsize == 20 and PLA_DTYPE.item
 class RefConfig(C.Structure):
     _fields_ = [("width", C.c_int), ("height", C.c_int), ("threads", C.c_int), ("shader", C.c_int),
                 ("scene", C.c_int), ("spp", C.c_int), ("spl", C.c_int), ("accelerator", C.c_int),
-                ("obj", C.c_char_p), ("mtl", C.c_char_p), ("cam", C.c_char_p)]
+                ("obj", C.c_char_p), ("mtl", C.c_char_p), ("cam", C.c_char_p), ("samplers", C.c_int)]
 
 
 def available():
@@ -108,10 +108,11 @@ class RefRenderer:
     """Scene -> Shader -> Renderer assembled like C_wrapper.cpp's work_thread and kept alive."""
 
     def __init__(self, width, height, shader, scene, spp=1, spl=1, accelerator=3, threads=1,
-                 obj=None, mtl=None, cam=None):
+                 obj=None, mtl=None, cam=None, samplers=0):
+        """samplers: 0 = the Linux front-end's (StaticHaltonSeq), 1 = Android's (StaticPCG) for pixel jitter, OBJ lights, RR."""
         self.cfg = RefConfig(width, height, threads, shader, scene, spp, spl, accelerator,
                              obj.encode() if obj else None, mtl.encode() if mtl else None,
-                             cam.encode() if cam else None)
+                             cam.encode() if cam else None, samplers)
         self.width, self.height, self.spp, self.spl = width, height, spp, spl
         self.h = lib().ref_create(C.byref(self.cfg))
         if not self.h:
@@ -131,7 +132,13 @@ class RefRenderer:
     def render(self, threads=1, repeats=1, bitmap=None):
         if bitmap is None:
             bitmap = np.zeros(self.width * self.height, np.int32)
-        secs = lib().ref_render(self.h, _p(bitmap), threads, repeats)
+        # For sizes that are not multiples of 16 the reference writes past the end of the bitmap (Renderer.cpp:149, the
+        # pixel index is not clamped): render into a padded copy so that those writes land in our own slack.
+        n = self.width * self.height
+        work = np.zeros(n + 2 * self.width * (self.height // 16 + 2) + 64, np.int32)
+        work[:n] = bitmap.reshape(-1)
+        secs = lib().ref_render(self.h, _p(work), threads, repeats)
+        bitmap.reshape(-1)[:] = work[:n]
         return bitmap.reshape(self.height, self.width), secs
 
     def casted_rays(self):

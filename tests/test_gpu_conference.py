@@ -291,3 +291,26 @@ def test_replay_samplers_rejected_for_path_tracer(mrt, ref):
     with pytest.raises(Exception):
         H.gpu_from_ref(ref, r, 2, 2, 32, 32, flags=capi.FLAG_REPLAY_SAMPLERS)
     r.close()
+
+
+@pytest.mark.parametrize("samplers", [0, 1])
+def test_conference_whitted_with_eight_area_lights_replayed_exactly(mrt, ref, conf, samplers):
+    """The conference stand-in has 8 area lights created by the front-end's sampler lambda (OBJLoader::fillScene):
+    samplers=0 is the Linux front-end's StaticHaltonSeq (C_wrapper.cpp:109,145), samplers=1 the Android front-end's
+    StaticPCG for pixel jitter and lights (JNI_layer.cpp:601,616-618). With MRT_FLAG_REPLAY_SAMPLERS the Whitted frame
+    (2 spp, jittered) is the reference's single-thread frame bit for bit, and the casted-ray counts are equal."""
+    from mobileraytracer_b200 import capi
+    obj, mtl, cam = conf
+    w, h = 256, 144
+    r = ref.RefRenderer(w, h, 1, -1, obj=obj, mtl=mtl, cam=cam, spp=2, samplers=samplers)
+    c0 = ref.light_index_counter()
+    bm_ref, _ = r.render(threads=1)
+    g = H.gpu_from_ref(ref, r, -1, 1, w, h, spp=2, cam_file=cam, flags=capi.FLAG_REPLAY_SAMPLERS, samplers=samplers)
+    g.setReplayCounter(c0)
+    bm = g.renderFrame()
+    c = H.compare_bitmaps(bm, bm_ref)
+    assert c["exact"] >= 0.9995 and c["within1"] >= 0.9999, c
+    assert g.getReplayCounter() == ref.light_index_counter() & 0xFFFFFFFF
+    assert abs(g.getTotalCastedRays() - r.casted_rays()) <= 4      # an exact-t tie on a shared edge may pick the other triangle
+    g.close()
+    r.close()

@@ -267,3 +267,37 @@ def test_empty_scene_renders_black(mrt, shader):
     t = g.traceRays(np.zeros((5, 3), np.float32), np.tile(np.array([[0, 0, 1]], np.float32), (5, 1)))
     assert (t["kind"] == 0).all() and (t["t"] == np.float32(1e30)).all()
     g.close()
+
+
+def test_android_front_end_pixel_sampler_static_pcg(mrt, ref):
+    """The Android front-end jitters pixels with StaticPCG (JNI_layer.cpp:616-618): scene 3, Whitted, 4 spp, the
+    reference's PCG table handed over through mrt_sampler_tables::static_pcg -> same frame."""
+    w = h = 256
+    r = ref.RefRenderer(w, h, 1, 3, spp=4, samplers=1)
+    bm_ref, _ = r.render(threads=1)
+    g = H.gpu_from_ref(ref, r, 3, 1, w, h, spp=4, samplers=1)
+    bm = g.renderFrame()
+    c = H.compare_bitmaps(bm, bm_ref)
+    assert c["within1"] >= 0.999 and c["exact"] >= 0.995, c
+    assert g.getTotalCastedRays() == r.casted_rays()
+    # and it is not the Halton jitter in disguise
+    g2 = H.gpu_from_ref(ref, r, 3, 1, w, h, spp=4, samplers=0)
+    assert not np.array_equal(g2.renderFrame(), bm)
+    g.close(); g2.close()
+    r.close()
+
+
+def test_own_pcg_table_is_seeded_and_reproducible(mrt):
+    """Without caller tables the library fills its own StaticPCG table (pcg32 XSH-RR, Utils.hpp:246-252): a jittered frame
+    must be reproducible from the seed, change with it, and differ from the un-jittered frame."""
+    import mobileraytracer_b200 as m
+    from mobileraytracer_b200 import capi, scene as S
+    make_scene, make_cam, mp = S.BUILTIN[3]
+    frames = []
+    for seed, sampler in ((5, capi.SAMPLER_STATIC_PCG), (5, capi.SAMPLER_STATIC_PCG), (6, capi.SAMPLER_STATIC_PCG), (5, capi.SAMPLER_CONSTANT)):
+        r = m.Renderer(make_scene(), make_cam(np.float32(1.0)), 128, 128, 4, 1, capi.SHADER_WHITTED, depth_max_point=mp,
+                       pixel_sampler=sampler, seed=seed)
+        frames.append(r.renderFrame().copy())
+        r.close()
+    assert np.array_equal(frames[0], frames[1])
+    assert not np.array_equal(frames[0], frames[2]) and not np.array_equal(frames[0], frames[3])
