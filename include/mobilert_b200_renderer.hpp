@@ -63,7 +63,10 @@ public:
      * (before it is moved into the Shader), the camera with its lookAt / up, the Config fields. */
     B200Renderer(const Scene &scene, const Camera &camera, const ::glm::vec3 &lookAt, const ::glm::vec3 &up,
                  ::std::int32_t width, ::std::int32_t height, ::std::int32_t samplesPixel, ::std::int32_t samplesLight,
-                 ::std::int32_t shader) {
+                 ::std::int32_t shader,
+                 // which static table the front-end's own samplers read: MRT_SAMPLER_AUTO = StaticHaltonSeq as in
+                 // C_wrapper.cpp:109,145,176; the Android layer passes MRT_SAMPLER_STATIC_PCG (JNI_layer.cpp:601,616-618,636)
+                 ::std::int32_t frontEndSampler = MRT_SAMPLER_AUTO) {
         ::std::vector<mrt_triangle> tris; tris.reserve(scene.triangles_.size());
         for (const Triangle &t : scene.triangles_) { tris.push_back(flatten(t)); }
         ::std::vector<mrt_sphere> spheres;
@@ -119,6 +122,10 @@ public:
         rd.shader = shader; rd.accelerator = MRT_ACC_B200; rd.pixel_sampler = MRT_SAMPLER_AUTO; rd.seed = 1u;
         rd.depth_max_point[0] = rd.depth_max_point[1] = rd.depth_max_point[2] = 1.0F;   // C_wrapper.cpp:138
         rd.device = -1;
+        if (frontEndSampler == MRT_SAMPLER_STATIC_PCG) {
+            rd.light_sampler = MRT_SAMPLER_STATIC_PCG;
+            rd.pixel_sampler = samplesPixel > 1 ? MRT_SAMPLER_STATIC_PCG : MRT_SAMPLER_CONSTANT;
+        }
         if (mrt_create(&sd, &cd, &rd, nullptr, &handle_) != MRT_OK) {
             // the front-ends catch ::std::exception around construction (C_wrapper.cpp:257-263, JNI_layer.cpp:706-715)
             throw ::std::runtime_error(::std::string("B200Renderer: ") + mrt_last_error(nullptr));
