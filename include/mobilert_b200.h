@@ -91,6 +91,11 @@ enum {
     MRT_FLAG_SORT_BY_MATERIAL = 2, /* accepted and ignored: every material runs the same shading routine (materials are data,
                                       Material.hpp), so the shade kernel has no per-material divergence to sort away; it is
                                       bound by gather latency (profiles/), which a sort of the 16-byte hit records would not help */
+    MRT_FLAG_PROGRESSIVE = 8,      /* mrt_render_frame refreshes the caller's HOST bitmap after every sample (wavefront: every pass)
+                                      from a second stream, so that a UI thread polling the buffer sees the frame build up as it
+                                      does with the reference, whose workers write finished pixels in place (Renderer.cpp:149-157;
+                                      JNI_layer.cpp:818-821, Qt mainwindow.cpp:45-66). A refresh is skipped while the previous one
+                                      is in flight. The final content is identical with and without the flag. */
     MRT_FLAG_REPLAY_SAMPLERS = 4   /* parity mode for NoShadows / Whitted: every Shader::getLightIndex (Shader.cpp:223-233) and
                                       AreaLight::getPosition (AreaLight.cpp:17-26) draw reads the table entry the reference's
                                       single-thread run reads (two counting passes per sample + host prefix sums, about 3x the

@@ -66,7 +66,8 @@ public:
                  ::std::int32_t shader,
                  // which static table the front-end's own samplers read: MRT_SAMPLER_AUTO = StaticHaltonSeq as in
                  // C_wrapper.cpp:109,145,176; the Android layer passes MRT_SAMPLER_STATIC_PCG (JNI_layer.cpp:601,616-618,636)
-                 ::std::int32_t frontEndSampler = MRT_SAMPLER_AUTO) {
+                 ::std::int32_t frontEndSampler = MRT_SAMPLER_AUTO,
+                 ::std::uint32_t flags = 0u /* MRT_FLAG_*, e.g. MRT_FLAG_PROGRESSIVE for a UI that shows the bitmap while it renders */) {
         ::std::vector<mrt_triangle> tris; tris.reserve(scene.triangles_.size());
         for (const Triangle &t : scene.triangles_) { tris.push_back(flatten(t)); }
         ::std::vector<mrt_sphere> spheres;
@@ -121,7 +122,7 @@ public:
         rd.width = width; rd.height = height; rd.samples_pixel = samplesPixel; rd.samples_light = samplesLight;
         rd.shader = shader; rd.accelerator = MRT_ACC_B200; rd.pixel_sampler = MRT_SAMPLER_AUTO; rd.seed = 1u;
         rd.depth_max_point[0] = rd.depth_max_point[1] = rd.depth_max_point[2] = 1.0F;   // C_wrapper.cpp:138
-        rd.device = -1;
+        rd.device = -1; rd.flags = flags;
         if (frontEndSampler == MRT_SAMPLER_STATIC_PCG) {
             rd.light_sampler = MRT_SAMPLER_STATIC_PCG;
             rd.pixel_sampler = samplesPixel > 1 ? MRT_SAMPLER_STATIC_PCG : MRT_SAMPLER_CONSTANT;

@@ -11,7 +11,7 @@ MRT_OK, MRT_ERR_INVALID, MRT_ERR_CUDA, MRT_ERR_OOM, MRT_ERR_STOPPED, MRT_ERR_OVE
 SHADER_NOSHADOWS, SHADER_WHITTED, SHADER_PATHTRACER, SHADER_DEPTHMAP, SHADER_DIFFUSE = range(5)
 ACC_NAIVE, ACC_REGULAR_GRID, ACC_BVH, ACC_B200 = 1, 2, 3, 4
 SAMPLER_AUTO, SAMPLER_CONSTANT, SAMPLER_STATIC_HALTON, SAMPLER_STATIC_MT, SAMPLER_STATIC_PCG = range(5)
-FLAG_FP32_ACCUMULATE, FLAG_SORT_BY_MATERIAL, FLAG_REPLAY_SAMPLERS = 1, 2, 4
+FLAG_FP32_ACCUMULATE, FLAG_SORT_BY_MATERIAL, FLAG_REPLAY_SAMPLERS, FLAG_PROGRESSIVE = 1, 2, 4, 8
 CAMERA_PERSPECTIVE, CAMERA_ORTHOGRAPHIC = 0, 1
 LIGHT_POINT, LIGHT_AREA = 0, 1
 

@@ -55,6 +55,12 @@ struct mrt_handle {
     DevMem d_tile, d_shader_table, d_static_halton, d_static_mt, d_static_pcg, d_inv_tile, d_tile_base, d_textures, d_texels, d_bitmap, d_accum, d_counters, d_scratch;
     std::vector<int> plane_slot_of_id, sphere_slot_of_id;
     int32_t *h_pinned_bitmap = nullptr;
+    // MRT_FLAG_PROGRESSIVE: the caller's host bitmap is refreshed while the frame renders (set for the duration of a frame)
+    int32_t *progress_host = nullptr;
+    bool progress_pinned = false;
+    size_t progress_bytes = 0;
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_progress = nullptr, ev_copied = nullptr;
     size_t pinned_bytes = 0;
     std::atomic<int> stop {0};
     std::atomic<int> sample {0};
@@ -380,6 +386,9 @@ void mrt_destroy(mrt_handle *h) {
     for (cudaEvent_t e : h->sample_events) { cudaEventDestroy(e); }
     if (h->ev0) { cudaEventDestroy(h->ev0); }
     if (h->ev1) { cudaEventDestroy(h->ev1); }
+    if (h->copy_stream) { cudaStreamSynchronize(h->copy_stream); cudaStreamDestroy(h->copy_stream); }
+    if (h->ev_progress) { cudaEventDestroy(h->ev_progress); }
+    if (h->ev_copied) { cudaEventDestroy(h->ev_copied); }
     if (h->h_pinned_bitmap) { cudaFreeHost(h->h_pinned_bitmap); }
     cudaStream_t st = h->own_stream;
     delete h;   // DevMem destructors free the device arrays
@@ -494,6 +503,25 @@ namespace {
 // Frame driver shared by the three render entry points. Exactly one of bitmap / accum is the target:
 //   bitmap: the reference's in-place integer running average, samples applied in order (Renderer.cpp:117-157)
 //   accum : fp32 sums of the selected samples (multi-GPU partitions), resolved later
+// The reference's worker threads write every finished pixel straight into the caller's bitmap, which the UI thread shows
+// while the frame renders (DrawView / MainRenderer on Android, mainwindow.cpp:45-66 on Qt). Here the bitmap lives on the
+// device; with MRT_FLAG_PROGRESSIVE a second stream copies it to the caller's buffer after every sample (or wavefront
+// pass), skipping a refresh while the previous one is still in flight.
+void CUDART_CB progress_to_caller(void *p) {
+    mrt_handle *h = static_cast<mrt_handle *>(p);
+    if (h->progress_host) { std::memcpy(h->progress_host, h->h_pinned_bitmap, h->progress_bytes); }
+}
+cudaError_t progress_refresh(mrt_handle *h, const int32_t *d_bitmap) {
+    if (!h->progress_host || !d_bitmap) { return cudaSuccess; }
+    if (cudaEventQuery(h->ev_copied) != cudaSuccess) { cudaGetLastError(); return cudaSuccess; }
+    cudaError_t e = cudaEventRecord(h->ev_progress, h->stream);
+    if (e == cudaSuccess) { e = cudaStreamWaitEvent(h->copy_stream, h->ev_progress, 0); }
+    if (e == cudaSuccess) { e = cudaMemcpyAsync(h->progress_pinned ? h->progress_host : h->h_pinned_bitmap, d_bitmap, h->progress_bytes, cudaMemcpyDeviceToHost, h->copy_stream); }
+    if (e == cudaSuccess && !h->progress_pinned) { e = cudaLaunchHostFunc(h->copy_stream, progress_to_caller, h); }
+    if (e == cudaSuccess) { e = cudaEventRecord(h->ev_copied, h->copy_stream); }
+    return e;
+}
+
 int render_samples(mrt_handle *h, int32_t *d_bitmap, float4 *d_accum, int sample_begin, int sample_stride) {
     cudaStream_t st = h->stream;
     API_CUDA(h, cudaSetDevice(h->device));
@@ -515,6 +543,7 @@ int render_samples(mrt_handle *h, int32_t *d_bitmap, float4 *d_accum, int sample
             API_CUDA(h, wavefront_render_batch(h->wavefront, h->scene, h->camera, h->rp, h->d_inv_tile.as<int2>(), h->d_tile_base.as<uint32_t>(), h->roots_per_sample, nb, samples, avg_n,
                                                tg, h->d_counters.as<DeviceCounters>(), &wt, &launches, st));
             h->sample.store(samples[nb - 1] + 1);
+            API_CUDA(h, progress_refresh(h, d_bitmap));
         }
     } else {
         const size_t depth = 4;   // samples in flight, so that mrt_stop() takes effect within a few samples
@@ -567,6 +596,7 @@ int render_samples(mrt_handle *h, int32_t *d_bitmap, float4 *d_accum, int sample
             API_CUDA(h, launch_render_sample(h->scene, h->camera, h->rp, h->d_inv_tile.as<int2>(), s, d_bitmap ? s + 1 : k + 1, tg,
                                              h->d_counters.as<DeviceCounters>(), st, rep));
             ++launches;
+            API_CUDA(h, progress_refresh(h, d_bitmap));
             while (h->sample_events.size() < depth) { cudaEvent_t e; API_CUDA(h, cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); h->sample_events.push_back(e); }
             API_CUDA(h, cudaEventRecord(h->sample_events[static_cast<size_t>(k) % depth], st));
         }
@@ -634,7 +664,20 @@ int mrt_render_frame(mrt_handle *h, int32_t *host_bitmap) {
         if (pinned) { API_CUDA(h, cudaMemcpyAsync(h->d_bitmap.p, host_bitmap, bytes, cudaMemcpyHostToDevice, h->stream)); }
         else { std::memcpy(h->h_pinned_bitmap, host_bitmap, bytes); API_CUDA(h, cudaMemcpyAsync(h->d_bitmap.p, h->h_pinned_bitmap, bytes, cudaMemcpyHostToDevice, h->stream)); }
     }
+    if (h->flags & MRT_FLAG_PROGRESSIVE) {
+        if (!h->copy_stream) {
+            API_CUDA(h, cudaStreamCreateWithFlags(&h->copy_stream, cudaStreamNonBlocking));
+            API_CUDA(h, cudaEventCreateWithFlags(&h->ev_progress, cudaEventDisableTiming));
+            API_CUDA(h, cudaEventCreateWithFlags(&h->ev_copied, cudaEventDisableTiming));
+        }
+        if (!covers_all) { API_CUDA(h, cudaStreamSynchronize(h->stream)); }   // the staging buffer is free again
+        h->progress_pinned = pinned; h->progress_bytes = bytes; h->progress_host = host_bitmap;
+    }
     const int rc = render_to_device_bitmap(h, h->d_bitmap.as<int32_t>());
+    if (h->progress_host) {
+        cudaStreamSynchronize(h->copy_stream);   // no refresh may land after the final copy below
+        h->progress_host = nullptr;
+    }
     if (rc != MRT_OK && rc != MRT_ERR_STOPPED) { return rc; }
     if (pinned) {
         API_CUDA(h, cudaMemcpyAsync(host_bitmap, h->d_bitmap.p, bytes, cudaMemcpyDeviceToHost, h->stream));

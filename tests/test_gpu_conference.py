@@ -191,6 +191,37 @@ def test_stop_and_progress_polling(mrt):
     r.close()
 
 
+@pytest.mark.parametrize("shader,scene,spp", [(1, 3, 12000), (2, 0, 2048)])
+def test_progressive_bitmap_builds_up_while_rendering(mrt, shader, scene, spp):
+    """MRT_FLAG_PROGRESSIVE: the caller's HOST bitmap shows the frame while renderFrame is still running, as the
+    reference's in-place pixel writes do for the Android / Qt UI threads (Renderer.cpp:149-157, JNI_layer.cpp:818-821);
+    the finished frame is the same as without the flag. Megakernel (Whitted) and wavefront (PathTracer) paths."""
+    import threading
+    import time
+    from mobileraytracer_b200 import capi
+    w = h = 512
+    plain = mrt.build_renderer(mrt.Config(width=w, height=h, shader=shader, sceneIndex=scene, samplesPixel=spp, printStdOut=False))
+    expect = plain.renderFrame().copy()
+    plain.close()
+    r = mrt.build_renderer(mrt.Config(width=w, height=h, shader=shader, sceneIndex=scene, samplesPixel=spp, printStdOut=False,
+                                      flags=capi.FLAG_PROGRESSIVE))
+    bm = np.zeros(w * h, np.int32)
+    th = threading.Thread(target=lambda: r.renderFrame(bm))
+    th.start()
+    partial_seen, deadline = 0, time.time() + 120.0
+    while th.is_alive() and time.time() < deadline:
+        s = r.getSample()
+        filled = bool((bm != 0).mean() > 0.5)
+        if filled and s < spp and th.is_alive():
+            partial_seen += 1
+        time.sleep(0.002)
+    th.join(timeout=120)
+    assert not th.is_alive()
+    assert partial_seen > 0, "the host bitmap never showed a partial frame"
+    assert np.array_equal(bm.reshape(h, w), expect)
+    r.close()
+
+
 @pytest.mark.parametrize("shader", [2, 0])
 def test_conference_incoherent_rays_match_reference(mrt, ref, conf, shader):
     """Secondary-ray shaped work: 200 k rays from random points inside the room in random directions (closest hit, some
