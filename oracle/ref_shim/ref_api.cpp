@@ -51,12 +51,20 @@ static_assert(sizeof(Sphere) == 20, "reference Sphere layout changed");
 static_assert(sizeof(Plane) == 28, "reference Plane layout changed");
 
 namespace {
+// Discards the reference's log lines while a call runs. The sink has no state: the reference's render threads log
+// concurrently (LOG_ERROR in checkSystemError when a worker finds errno set), and a shared stringbuf under cout / cerr
+// is not thread-safe (it corrupted the heap in about one of four multi-threaded renders).
+struct NullBuf final : ::std::streambuf {
+    int_type overflow(int_type c) override { return traits_type::not_eof(c); }
+    ::std::streamsize xsputn(const char *, ::std::streamsize n) override { return n; }
+};
 struct Quiet {
-    ::std::ostringstream ss;
+    static NullBuf sink;
     ::std::streambuf *o, *e;
-    Quiet() : o(::std::cout.rdbuf(ss.rdbuf())), e(::std::cerr.rdbuf(ss.rdbuf())) {}
+    Quiet() : o(::std::cout.rdbuf(&sink)), e(::std::cerr.rdbuf(&sink)) {}
     ~Quiet() { ::std::cout.rdbuf(o); ::std::cerr.rdbuf(e); }
 };
+NullBuf Quiet::sink;
 double now() {
     return ::std::chrono::duration<double>(::std::chrono::steady_clock::now().time_since_epoch()).count();
 }
@@ -165,7 +173,12 @@ double ref_render(void *p, int32_t *bitmap, int threads, int repeats) {
     Quiet q;
     errno = 0;
     const double t0 = now();
-    do { h->renderer->renderFrame(bitmap, threads); } while (--repeats > 0);
+    try {
+        do { h->renderer->renderFrame(bitmap, threads); } while (--repeats > 0);
+    } catch (...) {
+        errno = 0;
+        return -1.0;
+    }
     const double t1 = now();
     errno = 0;
     return t1 - t0;

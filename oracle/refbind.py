@@ -138,6 +138,8 @@ class RefRenderer:
         work = np.zeros(n + 2 * self.width * (self.height // 16 + 2) + 64, np.int32)
         work[:n] = bitmap.reshape(-1)
         secs = lib().ref_render(self.h, _p(work), threads, repeats)
+        if secs < 0:
+            raise RuntimeError("the reference's renderFrame threw")
         bitmap.reshape(-1)[:] = work[:n]
         return bitmap.reshape(self.height, self.width), secs
 
