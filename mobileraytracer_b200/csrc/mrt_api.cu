@@ -883,3 +883,24 @@ int mrt_test_halton(uint32_t first, int64_t n, uint32_t base, float *out) {
 }
 
 }  // extern "C"
+
+#ifdef MRT_TRAVERSAL_STATS
+// diagnostic library only: out[0..8] = nodes with k valid children, out[9..16] = leaf slots holding 0..7 triangles, out[17] = inner children
+extern "C" int mrt_debug_bvh_stats(mrt_handle *h, unsigned long long out[18]) {
+    std::vector<mrt::Node8> nodes(h->bvh.n_nodes);
+    cudaMemcpy(nodes.data(), h->bvh.nodes, nodes.size() * sizeof(mrt::Node8), cudaMemcpyDeviceToHost);
+    for (int i = 0; i < 18; ++i) { out[i] = 0; }
+    for (const mrt::Node8 &n : nodes) {
+        const uint32_t *w = reinterpret_cast<const uint32_t *>(&n);
+        const uint32_t imask = w[3] >> 24;
+        const uint8_t *meta = reinterpret_cast<const uint8_t *>(w + 6);
+        int valid = 0;
+        for (int k = 0; k < 8; ++k) {
+            if (imask & (1u << k)) { ++valid; ++out[17]; }
+            else if (meta[k] != 0) { ++valid; ++out[9 + (meta[k] >> 5)]; }
+        }
+        ++out[valid];
+    }
+    return 0;
+}
+#endif
