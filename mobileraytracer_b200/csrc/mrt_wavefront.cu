@@ -266,9 +266,12 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
     } while (0)
 
     while (true) {
-        // retire: node work done and no item of the lane left in the list
+        // retire: node work done and no item of the lane left in the list. A finished lane idles until the next refill
+        // anyway, so the (divergent) retire block runs together with the refill instead of once per finished lane
+        // (it ran in 45 % of the iterations with 4.7 lanes active, profiles/r1_extend_s31).
         const uint32_t done = hasmask & ~busy & ~outmask;
-        if (done) {
+        const bool refill_now = !exhausted && __popc(~hasmask | done) > 32 - s.tune_refill;
+        if (done && (refill_now || exhausted)) {
             if (done & lane_bit) {
                 const unsigned long long k = w.key[lane], key0 = w.key0[lane];
                 const uint32_t cur = w.cur[lane];
@@ -293,7 +296,7 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
             hasmask &= ~done;
         }
         // refill the idle lanes
-        if (!exhausted && __popc(~hasmask) > 32 - s.tune_refill) {
+        if (refill_now) {
             const uint32_t idle = ~hasmask;
             uint32_t base = 0;
             if (lane == 0) { base = atomicAdd(work, static_cast<uint32_t>(__popc(idle))); }
