@@ -149,7 +149,8 @@ __global__ void k_wf_begin_levels(Queues Q, uint32_t n_samples, uint32_t roots_p
 // A lane whose node work is finished may still own items in the list; it retires once the list has been emptied, which
 // is forced when s.tune_wait lanes are waiting or nobody has node work left.
 constexpr int kCounterExtend = 20, kCounterShadow = 21;   // Queues::counts slots used as work counters
-constexpr uint32_t kItemCap = 128;                        // leaf items per warp; one node step adds at most 8 per lane
+constexpr uint32_t kNodeCap = 64;                         // node items per warp: < 32 left after a pass + at most one per lane and step
+constexpr uint32_t kTriCap = 256;                         // triangle entries of one (sub-)pass
 
 struct __align__(16) WarpShared {
     unsigned long long key[32];   // per lane: best hit so far, (float bits of t) << 32 | primitive id
@@ -161,9 +162,8 @@ struct __align__(16) WarpShared {
     int32_t skip[32];             // primitive id the ray leaves (Triangle.cpp:64), or -1
     uint32_t cur[32];             // queue index of the lane's ray
     uint32_t pre[32];             // packed plane / sphere hit found before the triangles (kind << 28 | idx)
-    uint2 items[kItemCap];        // x = first triangle slot of the leaf, y = owner lane | triangle count << 8
-    uint32_t count;               // items in the list
-    uint32_t pad[3];
+    uint4 nitems[kNodeCap];       // one per node step that hit leaves: triangle base | hit leaf slots + owner lane << 8 | meta words
+    uint16_t tris[kTriCap];       // the triangles of one pass: lane holding the node item << 5 | offset in the node's triangle run
 };
 
 MRT_D uint32_t pack_hit(const HitRec &h) { return (static_cast<uint32_t>(h.kind) << 28) | (static_cast<uint32_t>(h.idx) & 0x0fffffffu); }
@@ -178,41 +178,74 @@ MRT_D void shadow_unoccluded(const Queues &Q, uint32_t i) {
     if (tag & 0x80000000u) { atomicOr(&ch->ldmask, 1u << dz); }
 }
 
-// The warp tests the leaves items[first, first + n), n <= 32, one per lane. Must be called by all 32 lanes.
+// The warp tests the triangles of the node items nitems[first, first + n), n <= 32. Must be called by all 32 lanes.
+// Every lane expands one node item (hit leaf slots + meta bytes) into the bit mask of its triangles within the node's
+// run of <= 24; a warp scan gives every item its range in the triangle list, then the lanes take one TRIANGLE each per
+// round. The expansion used to happen per leaf at append time, in a loop that ran with 3.8 of 32 lanes active and cost
+// 6 % of the kernel's instructions, and the per-leaf triangle loop kept 9-15 lanes busy (profiles/r1_extend_s31).
 template <bool ANY>
 MRT_D void coop_triangle_pass(const SceneDev &s, WarpShared &w, uint32_t first, uint32_t n, int lane) {
+    const uint32_t full = 0xffffffffu;
     const bool valid = static_cast<uint32_t>(lane) < n;
-    const uint2 item = valid ? w.items[first + lane] : make_uint2(0u, static_cast<uint32_t>(lane));
-    const int owner = static_cast<int>(item.y & 31u);
-    const uint32_t cnt = item.y >> 8;        // 0 for a lane without an item
-    const v3 o = mk3(w.ox[owner], w.oy[owner], w.oz[owner]);
-    const v3 d = mk3(w.dx[owner], w.dy[owner], w.dz[owner]);
-    const int skip = w.skip[owner];
-    unsigned long long mykey = ~0ull;
-    float bu = 0.0f, bv = 0.0f;
-    if (cnt != 0u) {
-        float tbest = __uint_as_float(reinterpret_cast<const uint2 *>(&w.key[owner])->y);
-        const float4 *tp = reinterpret_cast<const float4 *>(s.tri_geom) + 3ull * item.x;
-        for (uint32_t j = 0; j < cnt; ++j, tp += 3) {
-            const float4 g0 = __ldg(tp), g1 = __ldg(tp + 1), g2 = __ldg(tp + 2);
-            const uint32_t prim = __float_as_uint(g2.y);
-            // self-hit skip (Triangle.cpp:64); area lights do not occlude (Shader.cpp:132-158)
-            if (static_cast<int>(prim) == skip || (ANY && static_cast<int>(prim) >= s.n_triangles)) { continue; }
-            MRT_STAT(atomicAdd(&g_stat_tris, 1ull);)
-            float tt, u, v;
-            if (tri_hit(g0, g1, g2, o, d, tbest, tt, u, v)) {
-                const unsigned long long k = (static_cast<unsigned long long>(__float_as_uint(tt)) << 32) | prim;
-                if (k < mykey) { mykey = k; bu = u; bv = v; tbest = fminf(tbest, tt); }
+    const uint4 it = valid ? w.nitems[first + lane] : make_uint4(0u, 0u, 0u, 0u);
+    const uint32_t owner = (it.y >> 8) & 31u;
+    uint32_t tm = 0u;
+    for (uint32_t lh = it.y & 0xffu; lh != 0u; lh &= lh - 1u) {
+        const uint32_t mb = leaf_meta(it.z, it.w, __ffs(lh) - 1u);
+        tm |= ((1u << (mb >> 5)) - 1u) << (mb & 31u);
+    }
+    const uint32_t cnt_all = __popc(tm);
+    const uint32_t total = __reduce_add_sync(full, cnt_all);
+    const uint32_t step = total <= kTriCap ? 32u : 8u;      // 8 node items hold at most 192 triangles
+    for (uint32_t lo = 0; lo < n; lo += step) {
+        const uint32_t cnt = (static_cast<uint32_t>(lane) - lo < step) ? cnt_all : 0u;
+        uint32_t incl = cnt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t v = __shfl_up_sync(full, incl, d);
+            if (lane >= d) { incl += v; }
+        }
+        const uint32_t tot = __shfl_sync(full, incl, 31);
+        {
+            uint32_t pos = incl - cnt;
+            for (uint32_t m = cnt ? tm : 0u; m != 0u; m &= m - 1u) {
+                w.tris[pos++] = static_cast<uint16_t>((static_cast<uint32_t>(lane) << 5) | (__ffs(m) - 1u));
             }
         }
-    }
-    bool won = false;
-    if (mykey != ~0ull) { won = atomicMin(&w.key[owner], mykey) > mykey; }
-    if (!ANY) {
         __syncwarp();
-        if (won && w.key[owner] == mykey) { w.uv[owner] = make_float2(bu, bv); }   // the one final winner of this pass
+        for (uint32_t base = 0; base < tot; base += 32u) {
+            const uint32_t idx = base + static_cast<uint32_t>(lane);
+            const bool have = idx < tot;
+            const uint32_t e = have ? w.tris[idx] : 0u;
+            const uint32_t tb = __shfl_sync(full, it.x, e >> 5);
+            const int ow = static_cast<int>(__shfl_sync(full, owner, e >> 5));
+            unsigned long long mykey = ~0ull;
+            float bu = 0.0f, bv = 0.0f;
+            if (have) {
+                const float4 *tp = reinterpret_cast<const float4 *>(s.tri_geom) + 3ull * (tb + (e & 31u));
+                const float4 g0 = __ldg(tp), g1 = __ldg(tp + 1), g2 = __ldg(tp + 2);
+                const uint32_t prim = __float_as_uint(g2.y);
+                // self-hit skip (Triangle.cpp:64); area lights do not occlude (Shader.cpp:132-158)
+                if (!(static_cast<int>(prim) == w.skip[ow] || (ANY && static_cast<int>(prim) >= s.n_triangles))) {
+                    MRT_STAT(atomicAdd(&g_stat_tris, 1ull);)
+                    const v3 o = mk3(w.ox[ow], w.oy[ow], w.oz[ow]);
+                    const v3 d = mk3(w.dx[ow], w.dy[ow], w.dz[ow]);
+                    const float tbest = __uint_as_float(reinterpret_cast<const uint2 *>(&w.key[ow])->y);
+                    float tt, u, v;
+                    if (tri_hit(g0, g1, g2, o, d, tbest, tt, u, v)) {
+                        mykey = (static_cast<unsigned long long>(__float_as_uint(tt)) << 32) | prim; bu = u; bv = v;
+                    }
+                }
+            }
+            bool won = false;
+            if (mykey != ~0ull) { won = atomicMin(&w.key[ow], mykey) > mykey; }
+            if (!ANY) {
+                __syncwarp();
+                if (won && w.key[ow] == mykey) { w.uv[ow] = make_float2(bu, bv); }   // the one final winner of this round
+            }
+            __syncwarp();
+        }
     }
-    __syncwarp();
 }
 
 // ANY = false: closest hit for every ray of the level (Shader::rayTrace's geometric part, Shader.cpp:86-111) -> Q.hit
@@ -233,14 +266,12 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
     uint32_t hasmask = 0u;           // lanes holding a ray (warp-uniform)
     uint32_t outmask = 0u;           // lanes that may own items in the list (warp-uniform)
     uint32_t busy = 0u;              // ballot of node_work (warp-uniform)
-    uint32_t count = 0;              // items in the warp's list (warp-uniform copy of w.count)
+    uint32_t count = 0;              // node items in the warp's list (warp-uniform)
     Trav8 t;
     TravMem tmem;
     t.o = mk3(0.0f, 0.0f, 0.0f);
     t.ngroup = make_uint2(0u, 0u); t.sp = 0; t.tbest = 0.0f;
     MRT_STAT(t.n_nodes = 0u; t.n_tris = 0u;)
-    if (lane == 0) { w.count = 0u; }
-    __syncwarp();
 
     // empties the warp's item list (top chunk first); afterwards nobody owns pending items
 #define MRT_FLUSH_ITEMS()                                                                         \
@@ -250,8 +281,6 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
             coop_triangle_pass<ANY>(s, w, count - m_, m_, lane);                               \
             count -= m_;                                                                          \
         }                                                                                         \
-        if (lane == 0) { w.count = 0u; }                                                          \
-        __syncwarp();                                                                             \
         outmask = 0u;                                                                             \
     } while (0)
     // after triangle passes: the lane's own best hit bounds its further node tests; an occluded shadow ray stops
@@ -367,33 +396,16 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
 #endif
             }
         }
-        // append the hit leaves to the warp's list: one shared-memory atomic per lane that hit a leaf
-        uint32_t emit = __ballot_sync(full, lh != 0u);
-        while (emit != 0u) {
-            uint32_t pos = 0xffffffffu;
-            if (lh != 0u) {
-                const uint32_t nl = __popc(lh);
-                pos = atomicAdd(&w.count, nl);
-                if (pos + nl <= kItemCap) {
-                    do {
-                        const uint32_t k = __ffs(lh) - 1u;
-                        lh &= lh - 1u;
-                        const uint32_t mb = leaf_meta(m0, m1, k);
-                        w.items[pos++] = make_uint2(tbase + (mb & 31u), static_cast<uint32_t>(lane) | ((mb >> 5) << 8));
-                    } while (lh != 0u);
-                    pos = 0xffffffffu;   // appended
+        // append one node item per lane that hit leaves: positions from the ballot, no atomics, no loop
+        {
+            const uint32_t emit = __ballot_sync(full, lh != 0u);
+            if (emit != 0u) {
+                if (lh != 0u) {
+                    w.nitems[count + __popc(emit & (lane_bit - 1u))] = make_uint4(tbase, lh | (static_cast<uint32_t>(lane) << 8), m0, m1);
                 }
-            }
-            outmask |= emit;
-            __syncwarp();
-            count = w.count;
-            emit = 0u;
-            if (count > kItemCap) {
-                // list full (rare): the appended items are exactly [0, lowest refused position); empty it and let the others retry
-                count = __reduce_min_sync(full, pos);
-                MRT_FLUSH_ITEMS();
-                MRT_REFRESH_BEST();
-                emit = __ballot_sync(full, lh != 0u);
+                count += __popc(emit);
+                outmask |= emit;
+                __syncwarp();
             }
         }
         // triangle phase: full chunks only
@@ -402,8 +414,6 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
                 coop_triangle_pass<ANY>(s, w, count - 32u, 32u, lane);
                 count -= 32u;
             } while (count >= 32u);
-            if (lane == 0) { w.count = count; }
-            __syncwarp();
             if (count == 0u) { outmask = 0u; }
             MRT_REFRESH_BEST();
         } else {
