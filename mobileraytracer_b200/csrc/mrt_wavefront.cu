@@ -139,16 +139,22 @@ __global__ void k_wf_begin_levels(Queues Q, uint32_t n_samples, uint32_t roots_p
 // Node tests and triangle tests are scheduled separately, because after any single node step only a few lanes have hit
 // a leaf (ncu, profiles/r1_s25_extend_*: 7 of 32 threads active in per-lane triangle code, which then cost a third of
 // the kernel for 3 % of its arithmetic):
-//   node phase     : every lane with pending inner nodes visits one BVH8 node; each leaf child it hits is appended as an
-//                    item (owner lane, first triangle slot, triangle count) to a per-warp list in shared memory;
-//   triangle phase : whenever 32 items are waiting, the warp tests them together, one leaf per lane. The ray of the
-//                    owner comes through warp shuffles; a hit is committed with one 64-bit atomicMin on the owner's
-//                    key (t bits << 32 | primitive id) in shared memory, which implements "nearest t, then lowest
-//                    primitive id" (the reference keeps the first hit of its left-first walk at equal t, mrt_traverse.cuh)
-//                    independently of the order the items are processed in.
+//   node phase     : every lane with pending inner nodes visits one BVH8 node; a lane that hit leaf children appends ONE
+//                    node item (owner lane, triangle base, hit leaf slots, the node's meta words) to a per-warp list in
+//                    shared memory, at a position taken from the ballot (no atomics, no per-leaf loop);
+//   triangle phase : whenever 32 node items are waiting, every lane expands one item into the bit mask of its triangles, a
+//                    warp scan lays the triangles out in a list, and the lanes test one TRIANGLE each per round. The
+//                    ray of the owner is read from shared memory; a hit is committed with one 64-bit atomicMin on the
+//                    owner's key (t bits << 32 | primitive id), which implements "nearest t, then lowest primitive id"
+//                    (the reference keeps the first hit of its left-first walk at equal t, mrt_traverse.cuh)
+//                    independently of the order the triangles are processed in.
 // A lane whose node work is finished may still own items in the list; it retires once the list has been emptied, which
 // is forced when s.tune_wait lanes are waiting or nobody has node work left.
 constexpr int kCounterExtend = 20, kCounterShadow = 21;   // Queues::counts slots used as work counters
+#ifndef MRT_QUEUE_AHEAD
+#define MRT_QUEUE_AHEAD 2048
+#endif
+constexpr uint32_t kQueueAhead = MRT_QUEUE_AHEAD;          // rays between a refill and the queue entries it prefetches
 constexpr uint32_t kNodeCap = 64;                         // node items per warp: < 32 left after a pass + at most one per lane and step
 constexpr uint32_t kTriCap = 256;                         // triangle entries of one (sub-)pass
 
@@ -337,6 +343,14 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
                 if (cur < n) {
                     HitRec h;
                     const float4 a = ANY ? Q.s0[cur] : Q.r0[b][cur], c = ANY ? Q.s1[cur] : Q.r1[b][cur];
+#ifndef MRT_NO_QUEUE_PREFETCH
+                    // the ray that somebody will fetch kQueueAhead refills from now: start its trip from HBM to L2 (the refill
+                    // is a divergent block the whole warp waits for; every queue entry is prefetched exactly once)
+                    if (cur + kQueueAhead < n) {
+                        asm volatile("prefetch.global.L2 [%0];" :: "l"((ANY ? Q.s0 : Q.r0[b]) + cur + kQueueAhead));
+                        asm volatile("prefetch.global.L2 [%0];" :: "l"((ANY ? Q.s1 : Q.r1[b]) + cur + kQueueAhead));
+                    }
+#endif
                     const v3 o = mk3(a.x, a.y, a.z), d = mk3(a.w, c.x, c.y);
                     int sk, si;
                     unpack_skip(__float_as_uint(ANY ? c.w : c.z), sk, si);
