@@ -272,7 +272,7 @@ int upload_scene(mrt_handle *h, const mrt_scene_desc &sc) {
     // binned-SAH hierarchy by default; MRT_B200_BVH=lbvh selects the Morton-order hierarchy (build-speed / quality experiments)
     const char *bvh_env = std::getenv("MRT_B200_BVH");
     const char *leaf_env = std::getenv("MRT_B200_LEAF");   // triangles per leaf slot, 1..7 (tuning experiments)
-    const uint32_t leaf = leaf_env ? static_cast<uint32_t>(std::atoi(leaf_env)) & 7u : 3u;
+    const uint32_t leaf = leaf_env ? static_cast<uint32_t>(std::atoi(leaf_env)) & 7u : 4u;
     const char *fat_env = std::getenv("MRT_B200_FATLEAF");   // 1: never split a subtree that fits one leaf slot (tuning experiments)
     const uint32_t build_flags = ((bvh_env && std::strcmp(bvh_env, "lbvh") == 0) ? 0u : 1u) | (leaf << 8) | ((fat_env && std::atoi(fat_env)) ? 2u : 0u);
     API_CUDA(h, build_bvh8(h->d_tris9.as<float>(), static_cast<int>(nprims), build_flags, st, &h->bvh));
@@ -286,11 +286,13 @@ int upload_scene(mrt_handle *h, const mrt_scene_desc &sc) {
     {
         const char *tp = std::getenv("MRT_B200_POSTPONE"), *tr = std::getenv("MRT_B200_REFILL");   // tuning experiments only
         s.tune_postpone = tp ? std::atoi(tp) : 12;
-        s.tune_refill = tr ? std::atoi(tr) : 22;
+        s.tune_refill = tr ? std::atoi(tr) : 26;
         s.prmt_one = 0x3F800000u;
         s.naive = h->naive ? 1 : 0;
         const char *tw = std::getenv("MRT_B200_WAIT");
-        s.tune_wait = tw ? std::atoi(tw) : 8;
+        s.tune_wait = tw ? std::atoi(tw) : 20;
+        const char *twa = std::getenv("MRT_B200_WAIT_ANY");
+        s.tune_wait_any = twa ? std::atoi(twa) : (tw ? std::atoi(tw) : 24);
     }
     s.nodes = h->bvh.nodes; s.tri_geom = h->bvh.tri_geom; s.tri_shade = h->d_tri_shade.as<TriShade>();
     s.n_triangles = static_cast<int32_t>(nt); s.n_bvh_prims = static_cast<int32_t>(nprims);

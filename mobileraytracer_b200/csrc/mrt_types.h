@@ -71,7 +71,7 @@ struct SceneDev {
     const float *tile_order;     // 256
     const float *shader_table;   // 1 << 20
     const float *static_halton;  // 1 << 20
-    int32_t tune_postpone, tune_refill, tune_wait;   // traversal scheduling thresholds in lanes (see mrt_traverse.cuh / mrt_wavefront.cu)
+    int32_t tune_postpone, tune_refill, tune_wait, tune_wait_any;   // traversal scheduling thresholds in lanes (see mrt_traverse.cuh / mrt_wavefront.cu)
     int32_t naive;               // 1: Naive accelerator semantics (no triangle root-box test; planes / spheres behind an unbounded box)
     uint32_t prmt_one;           // 0x3F800000, deliberately a run-time value (mrt_traverse.cuh, u8_to_unit)
     const float *pixel_table;    // table the pixel sampler reads (static_halton or static_mt), or null for Constant

@@ -149,7 +149,7 @@ __global__ void k_wf_begin_levels(Queues Q, uint32_t n_samples, uint32_t roots_p
 //                    (the reference keeps the first hit of its left-first walk at equal t, mrt_traverse.cuh)
 //                    independently of the order the triangles are processed in.
 // A lane whose node work is finished may still own items in the list; it retires once the list has been emptied, which
-// is forced when s.tune_wait lanes are waiting or nobody has node work left.
+// is forced when s.tune_wait (closest hit) / s.tune_wait_any (any hit) lanes are waiting or nobody has node work left.
 constexpr int kCounterExtend = 20, kCounterShadow = 21;   // Queues::counts slots used as work counters
 #ifndef MRT_QUEUE_AHEAD
 #define MRT_QUEUE_AHEAD 2048
@@ -397,7 +397,7 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
                 if (!(t.ngroup.y & 0xff000000u)) { t.ngroup = top; --t.sp; }
                 if (!trav8_node_core(s, t, tmem, tbase, lh, m0, m1, &overflow)) { t.ngroup.y = 0u; t.sp = 0; lh = 0u; }
                 node_work = (t.ngroup.y & 0xff000000u) != 0u || t.sp > 0;
-#ifndef MRT_NO_NODE_PREFETCH
+#ifdef MRT_NODE_PREFETCH   // paid off while the kernel waited on L1 misses; now it is ALU bound and the 14 extra instructions per step cost 3-4 %
                 if (t.ngroup.y & 0xff000000u) {
                     // the node this lane visits next is known now: pull it into L1 while the warp does the list / triangle work
                     const uint32_t nbit = 31u - __clz(t.ngroup.y);
@@ -434,7 +434,7 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
             busy = __ballot_sync(full, node_work);
         }
         // lanes that only wait for their items: force the triangle phase when enough of them pile up
-        if (__popc(hasmask & ~busy & outmask) >= s.tune_wait) { MRT_FLUSH_ITEMS(); MRT_REFRESH_BEST(); }
+        if (__popc(hasmask & ~busy & outmask) >= (ANY ? s.tune_wait_any : s.tune_wait)) { MRT_FLUSH_ITEMS(); MRT_REFRESH_BEST(); }
     }
 #undef MRT_FLUSH_ITEMS
 #undef MRT_REFRESH_BEST
