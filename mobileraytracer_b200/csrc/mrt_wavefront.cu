@@ -19,6 +19,9 @@ namespace mrt {
 
 constexpr int kLevels = kRayDepthMax;          // depths 1..6 are traced; a depth-7 ray contributes nothing (PathTracer.cpp:24-26)
 constexpr int kWfThreads = 128;
+#ifndef MRT_TRAV_MIN_BLOCKS
+#define MRT_TRAV_MIN_BLOCKS 8     // CTAs per SM of the persistent traversal kernels (64 registers per thread)
+#endif
 #ifndef MRT_SHADE_MIN_BLOCKS
 #define MRT_SHADE_MIN_BLOCKS 8
 #endif
@@ -441,8 +444,8 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
     if (overflow) { dc->overflow = 1; }
 }
 
-__global__ void __launch_bounds__(kWfThreads, 8) k_wf_extend(SceneDev s, Queues Q, int level, DeviceCounters *dc) { wf_traverse<false>(s, Q, level, dc); }
-__global__ void __launch_bounds__(kWfThreads, 8) k_wf_shadow(SceneDev s, Queues Q, DeviceCounters *dc) { wf_traverse<true>(s, Q, 0, dc); }
+__global__ void __launch_bounds__(kWfThreads, MRT_TRAV_MIN_BLOCKS) k_wf_extend(SceneDev s, Queues Q, int level, DeviceCounters *dc) { wf_traverse<false>(s, Q, level, dc); }
+__global__ void __launch_bounds__(kWfThreads, MRT_TRAV_MIN_BLOCKS) k_wf_shadow(SceneDev s, Queues Q, DeviceCounters *dc) { wf_traverse<true>(s, Q, 0, dc); }
 
 // Shader::getCosineSampleHemisphere (Shader.cpp:188-216)
 MRT_D v3 cosine_sample_hemisphere(v3 normal, float uniformRandom1, float uniformRandom2) {
@@ -726,7 +729,7 @@ cudaError_t wavefront_render_batch(Wavefront *w, const SceneDev &s, const Camera
     WavefrontHost *hst = host_of(w);
     Queues &Q = w->q;
     if (n_samples < 1 || n_samples > hst->batch) { return cudaErrorInvalidValue; }
-    const int grid = hst->sm_count * 8;
+    const int grid = hst->sm_count * MRT_TRAV_MIN_BLOCKS;
     WF_TRY(wf_mark(hst, -1, st));
     WF_TRY(cudaMemsetAsync(Q.counts, 0, kWfCounts * sizeof(uint32_t), st));
     const int patches = kNumberOfTiles * ((rp.bsx + 7) / 8) * ((rp.bsy + 3) / 4);
@@ -846,7 +849,7 @@ cudaError_t wavefront_trace_rays(Wavefront *w, const SceneDev &s, int64_t n, con
     if (n < 0 || static_cast<uint64_t>(n) > Q.cap_rays || static_cast<uint64_t>(n) > Q.cap_shadow) { return cudaErrorInvalidValue; }
     if (n == 0) { return cudaSuccess; }
     WF_TRY(cudaMemsetAsync(Q.counts, 0, kWfCounts * sizeof(uint32_t), st));
-    const int blocks = static_cast<int>((n + 255) / 256), grid = w->sm_count * 8;
+    const int blocks = static_cast<int>((n + 255) / 256), grid = w->sm_count * MRT_TRAV_MIN_BLOCKS;
     k_wf_test_fill<<<blocks, 256, 0, st>>>(Q, n, d_o, d_d, d_okind, d_oidx, d_sdist);
     k_wf_test_save_counts<<<1, 1, 0, st>>>(Q);
     k_wf_extend<<<grid, kWfThreads, 0, st>>>(s, Q, 0, dc);
