@@ -157,7 +157,10 @@ MRT_D bool child_hit(uint32_t nx, uint32_t ny, uint32_t nz, uint32_t fx, uint32_
 // 1e-6 (|(p - o) r| + |A|) (about 2^-20, four times the bound) on the near side downwards and on the far side upwards.
 // The test is conservative: it can only accept more children than exact arithmetic would, never fewer.
 // Core: leaves the hit leaf slots in `lh` (bit k = slot k) with the node's meta words m0 / m1 and triangle base.
-MRT_D bool trav8_node_core(const SceneDev &s, Trav8 &t, TravMem &tm_, uint32_t &tbase, uint32_t &lh, uint32_t &m0, uint32_t &m1, int *overflow) {
+// `perm`: optional 8 x 256 byte table perm[o * 256 + m] = the mask m with every bit k moved to k ^ o (shared memory of the
+// wavefront kernels: one LDS instead of three predicated swaps on the ALU pipe, which bounds those kernels).
+MRT_D bool trav8_node_core(const SceneDev &s, Trav8 &t, TravMem &tm_, uint32_t &tbase, uint32_t &lh, uint32_t &m0, uint32_t &m1, int *overflow,
+                           const uint8_t *perm = nullptr) {
     MRT_STAT(++t.n_nodes;)
     const uint32_t bit = 31u - __clz(t.ngroup.y);
     t.ngroup.y &= ~(1u << bit);
@@ -202,9 +205,13 @@ MRT_D bool trav8_node_core(const SceneDev &s, Trav8 &t, TravMem &tm_, uint32_t &
     // inner children: bit (slot ^ octinv), so that the highest pending bit is always the nearest child along the ray
     // (slot s of a node holds the child lying towards +axis k for every set bit k of s, see k_collapse8)
     uint32_t in = hits & imask;
-    if (octinv & 1u) { in = ((in & 0x55u) << 1) | ((in & 0xaau) >> 1); }
-    if (octinv & 2u) { in = ((in & 0x33u) << 2) | ((in & 0xccu) >> 2); }
-    if (octinv & 4u) { in = ((in & 0x0fu) << 4) | ((in & 0xf0u) >> 4); }
+    if (perm != nullptr) {
+        in = perm[(octinv << 8) | in];
+    } else {
+        if (octinv & 1u) { in = ((in & 0x55u) << 1) | ((in & 0xaau) >> 1); }
+        if (octinv & 2u) { in = ((in & 0x33u) << 2) | ((in & 0xccu) >> 2); }
+        if (octinv & 4u) { in = ((in & 0x0fu) << 4) | ((in & 0xf0u) >> 4); }
+    }
     t.ngroup.x = __float_as_uint(n1.x);
     t.ngroup.y = (in << 24) | imask;
     // leaf children: meta byte = (triangle count 1..7 << 5) | offset 0..23 into the node's triangle run (0 for an empty slot)

@@ -262,6 +262,19 @@ MRT_D void coop_triangle_pass(const SceneDev &s, WarpShared &w, uint32_t first, 
 template <bool ANY>
 MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCounters *dc) {
     __shared__ WarpShared wsh[kWfThreads / 32];
+#ifndef MRT_NO_PERM_TABLE
+    __shared__ uint8_t perm[8 * 256];   // perm[o * 256 + m]: bit k of m moved to k ^ o (ray-octant order of a node's children)
+    for (uint32_t i = threadIdx.x; i < 8u * 256u; i += kWfThreads) {
+        const uint32_t o = i >> 8, m = i & 255u;
+        uint32_t r = 0u;
+        for (uint32_t k = 0; k < 8u; ++k) { if (m & (1u << k)) { r |= 1u << (k ^ o); } }
+        perm[i] = static_cast<uint8_t>(r);
+    }
+    __syncthreads();
+    const uint8_t *permp = perm;
+#else
+    const uint8_t *permp = nullptr;
+#endif
     WarpShared &w = wsh[threadIdx.x >> 5];
     const uint32_t full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
@@ -398,7 +411,7 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
             const uint2 top = tmem.stack[t.sp > 0 ? t.sp - 1 : 0];
             if (node_work) {
                 if (!(t.ngroup.y & 0xff000000u)) { t.ngroup = top; --t.sp; }
-                if (!trav8_node_core(s, t, tmem, tbase, lh, m0, m1, &overflow)) { t.ngroup.y = 0u; t.sp = 0; lh = 0u; }
+                if (!trav8_node_core(s, t, tmem, tbase, lh, m0, m1, &overflow, permp)) { t.ngroup.y = 0u; t.sp = 0; lh = 0u; }
                 node_work = (t.ngroup.y & 0xff000000u) != 0u || t.sp > 0;
 #ifdef MRT_NODE_PREFETCH   // paid off while the kernel waited on L1 misses; now it is ALU bound and the 14 extra instructions per step cost 3-4 %
                 if (t.ngroup.y & 0xff000000u) {
