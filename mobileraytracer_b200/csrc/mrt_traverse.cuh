@@ -101,7 +101,29 @@ struct Trav8 {
 struct TravMem {
     uint2 stack[kStack8];      // node groups still to visit
     uint2 pend[kPend];         // parked leaf groups (x = triangle base, y = pending triangle bits); per-thread callers only
+#ifdef MRT_SMEM_STACK
+    uint32_t sh = 0u;          // wavefront kernels: shared-window address of this thread's column of the CTA's short stack (entry stride kShStackStride)
+    int lim = 0;               // entries [0, lim) live in shared memory, the rest in stack[] (0 for the per-thread callers)
+#endif
 };
+#ifdef MRT_SMEM_STACK
+constexpr int kShStackStride = 128;   // = kWfThreads: lane-consecutive 8-byte entries, two conflict-free wavefronts per warp access
+MRT_D void stack_put(TravMem &tm, int i, uint2 v) {
+    if (i < tm.lim) {
+        asm volatile("st.shared.v2.u32 [%0], {%1, %2};" :: "r"(tm.sh + static_cast<uint32_t>(i) * (kShStackStride * 8u)), "r"(v.x), "r"(v.y) : "memory");
+    } else { tm.stack[i - tm.lim] = v; }
+}
+MRT_D uint2 stack_get(const TravMem &tm, int i) {
+    uint2 v;
+    if (i < tm.lim) {
+        asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(tm.sh + static_cast<uint32_t>(i) * (kShStackStride * 8u)) : "memory");
+    } else { v = tm.stack[i - tm.lim]; }
+    return v;
+}
+#else
+MRT_D void stack_put(TravMem &tm, int i, uint2 v) { tm.stack[i] = v; }
+MRT_D uint2 stack_get(const TravMem &tm, int i) { return tm.stack[i]; }
+#endif
 
 #ifdef MRT_TRAVERSAL_STATS
 static __device__ unsigned long long g_stat_nodes, g_stat_tris, g_stat_rays;   // one copy per translation unit
@@ -167,7 +189,7 @@ MRT_D bool trav8_node_core(const SceneDev &s, Trav8 &t, TravMem &tm_, uint32_t &
     {   // the rest of the group goes to the stack: an unconditional store plus a conditional bump of sp (no divergent branch)
         const bool push = (t.ngroup.y & 0xff000000u) != 0u;
         if (push && t.sp >= kStack8) { *overflow = 1; return false; }
-        tm_.stack[t.sp < kStack8 ? t.sp : kStack8 - 1] = t.ngroup;
+        stack_put(tm_, t.sp < kStack8 ? t.sp : kStack8 - 1, t.ngroup);
         t.sp += push ? 1 : 0;
     }
     const uint32_t one = s.prmt_one;
@@ -303,7 +325,7 @@ MRT_D bool trav8_triangle_step(const SceneDev &s, Trav8 &t) {
 constexpr int kPostponeLanes = 12;
 template <bool ANY>
 MRT_D bool trav8_step(const SceneDev &s, Trav8 &t, TravMem &tm_, int *overflow) {
-    if (!(t.ngroup.y & 0xff000000u) && t.sp > 0) { t.ngroup = tm_.stack[--t.sp]; }
+    if (!(t.ngroup.y & 0xff000000u) && t.sp > 0) { t.ngroup = stack_get(tm_, --t.sp); }
     bool node_work = (t.ngroup.y & 0xff000000u) != 0u;
     if (node_work) {
         uint2 tnew;

@@ -291,6 +291,12 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
     uint32_t count = 0;              // node items in the warp's list (warp-uniform)
     Trav8 t;
     TravMem tmem;
+#ifdef MRT_SMEM_STACK
+    __shared__ uint2 shstack[MRT_SMEM_STACK * kWfThreads];
+    static_assert(kShStackStride == kWfThreads, "short-stack stride");
+    tmem.sh = static_cast<uint32_t>(__cvta_generic_to_shared(shstack + threadIdx.x));
+    tmem.lim = MRT_SMEM_STACK;
+#endif
     t.o = mk3(0.0f, 0.0f, 0.0f);
     t.ngroup = make_uint2(0u, 0u); t.sp = 0; t.tbest = 0.0f;
     MRT_STAT(t.n_nodes = 0u; t.n_tris = 0u;)
@@ -408,7 +414,7 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
         uint32_t tbase = 0u, lh = 0u, m0 = 0u, m1 = 0u;
         {
             // pop speculatively (the load does not wait inside a divergent branch)
-            const uint2 top = tmem.stack[t.sp > 0 ? t.sp - 1 : 0];
+            const uint2 top = stack_get(tmem, t.sp > 0 ? t.sp - 1 : 0);
             if (node_work) {
                 if (!(t.ngroup.y & 0xff000000u)) { t.ngroup = top; --t.sp; }
                 if (!trav8_node_core(s, t, tmem, tbase, lh, m0, m1, &overflow, permp)) { t.ngroup.y = 0u; t.sp = 0; lh = 0u; }
@@ -743,6 +749,16 @@ cudaError_t wavefront_render_batch(Wavefront *w, const SceneDev &s, const Camera
     Queues &Q = w->q;
     if (n_samples < 1 || n_samples > hst->batch) { return cudaErrorInvalidValue; }
     const int grid = hst->sm_count * MRT_TRAV_MIN_BLOCKS;
+#ifdef MRT_SMEM_STACK
+    {   // the short stack needs a shared-memory carve-out that still holds MRT_TRAV_MIN_BLOCKS CTAs per SM
+        static bool carved = false;
+        if (!carved) {
+            WF_TRY(cudaFuncSetAttribute(k_wf_extend, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+            WF_TRY(cudaFuncSetAttribute(k_wf_shadow, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+            carved = true;
+        }
+    }
+#endif
     WF_TRY(wf_mark(hst, -1, st));
     WF_TRY(cudaMemsetAsync(Q.counts, 0, kWfCounts * sizeof(uint32_t), st));
     const int patches = kNumberOfTiles * ((rp.bsx + 7) / 8) * ((rp.bsy + 3) / 4);
