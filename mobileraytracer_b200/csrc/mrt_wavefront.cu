@@ -749,8 +749,8 @@ cudaError_t wavefront_render_batch(Wavefront *w, const SceneDev &s, const Camera
     Queues &Q = w->q;
     if (n_samples < 1 || n_samples > hst->batch) { return cudaErrorInvalidValue; }
     const int grid = hst->sm_count * MRT_TRAV_MIN_BLOCKS;
-#ifdef MRT_SMEM_STACK
-    {   // the short stack needs a shared-memory carve-out that still holds MRT_TRAV_MIN_BLOCKS CTAs per SM
+#if defined(MRT_SMEM_STACK) && MRT_SMEM_STACK > 3
+    {   // above 3 entries the short stack needs a larger shared-memory carve-out than the default build's 164 KB to hold MRT_TRAV_MIN_BLOCKS CTAs per SM
         static bool carved = false;
         if (!carved) {
             WF_TRY(cudaFuncSetAttribute(k_wf_extend, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
