@@ -2,9 +2,13 @@
 
   metric   : Mrays/s (rays as the reference counts them: every Ray constructed = primary + shadow + secondary,
              app/MobileRT/Ray.cpp:11,26; printed as "Total Millions rays per second", C_wrapper.cpp:246-256) and ms/frame
-  workload : BASELINE config 4 — conference scene (procedural stand-in, the .obj is missing from the reference snapshot),
-             PathTracer, 1 sample per light, 1920x1072 (1080 rounded down to x16 as both front-ends do), 64 samples per
-             pixel PER GPU; rank g renders samples g, g+N, ... of 64*N, one NCCL reduce, rank 0 quantises ("weak").
+  workload : --workload c4 (default) = BASELINE config 4 as written: conference scene (procedural stand-in, the .obj is
+             missing from the reference snapshot; conference.mtl's own materials), PathTracer, 1 sample per light,
+             1920x1072 (1080 rounded down to x16 as both front-ends do), 64 samples per pixel IN TOTAL, sample-partitioned
+             over the N GPUs (rank g renders samples g, g+N, ...), one NCCL reduce, rank 0 quantises: STRONG scaling,
+             ms_per_step is the 64-spp frame.
+             --workload c5 = BASELINE config 5: the stand-in replicated 30x (9.8 M triangles), 3840x2160, 16 spp in total,
+             tiles x samples over the N GPUs, GPU BVH build time reported.
   step     : one frame.
 
   python bench.py [--gpus N --steps K --warmup W]           this library (sm_100a CUDA through the C-ABI)
@@ -12,6 +16,7 @@
 
 Prints ONE JSON line (rank 0)."""
 import argparse
+import ctypes
 import json
 import os
 import subprocess
@@ -28,7 +33,13 @@ sys.path.insert(0, ROOT)
 WIDTH, HEIGHT_ASKED, SPP, SPL = 1920, 1080, 64, 1
 SHADER_PATHTRACER = 2
 BYTES_PER_CLOSEST_RAY = 48     # 32 B ray record read + 16 B hit record written
-BYTES_PER_SHADOW_RAY = 36      # 32 B read + 4 B visibility
+BYTES_PER_SHADOW_RAY = 36      # 32 B read + 4 B visibility (this library writes 1 B)
+WORKLOADS = {
+    "c4": {"width": 1920, "height_asked": 1080, "spp": 64, "copies": 1,
+           "name": "BASELINE config 4: conference (stand-in), PathTracer, 1 spl, %dx%d, 64 spp in total, sample-partitioned over the GPUs, NCCL reduce"},
+    "c5": {"width": 3840, "height_asked": 2160, "spp": 16, "copies": 30,
+           "name": "BASELINE config 5: conference stand-in replicated 30x (flattened), PathTracer, 1 spl, %dx%d, 16 spp in total, tiles x samples over the GPUs, NCCL reduce"},
+}
 
 
 def round_down16(v):
@@ -41,13 +52,23 @@ def scene_files():
     """Writes the conference stand-in once per box (deterministic bytes) and returns its paths."""
     from tools import make_conference_standin as gen
     out = os.environ.get("MRT_SCENE_DIR", os.path.join(tempfile.gettempdir(), "mrt_b200_scenes"))
-    marker = os.path.join(out, "conference_standin.v2.ok")
+    marker = os.path.join(out, "conference_standin.v3.ok")
     if not os.path.exists(marker):
         info = gen.write(out)
         with open(marker, "w") as fh:
             fh.write(str(info["triangles"]))
     base = os.path.join(out, "conference_standin")
     return base + ".obj", base + ".mtl", base + ".cam"
+
+
+def tile_groups_for(workload, gpus):
+    """c4: samples only. c5: tiles x samples, at most 4 tile groups (8 GPUs = 4 tile groups x 2 sample groups)."""
+    if workload != "c5":
+        return 1
+    for tg in (4, 2, 1):
+        if gpus % tg == 0:
+            return tg
+    return 1
 
 
 class ClockSampler(threading.Thread):
@@ -75,6 +96,7 @@ class ClockSampler(threading.Thread):
         self.join(timeout=15)
         sm = [float(r[1]) for r in self.rows if len(r) > 2 and r[1].replace(".", "").isdigit()]
         mx = [float(r[2]) for r in self.rows if len(r) > 2 and r[2].replace(".", "").isdigit()]
+        pw = [float(r[3]) for r in self.rows if len(r) > 3 and r[3].replace(".", "").isdigit()]
         reasons = set()
         for r in self.rows:
             if len(r) >= 9:
@@ -82,16 +104,31 @@ class ClockSampler(threading.Thread):
                     if val.lower().startswith("active"):
                         reasons.add(name)
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": sorted(reasons), "samples": len(self.rows)}
+                "power_w_median": float(np.median(pw)) if pw else None, "reasons": sorted(reasons), "samples": len(self.rows)}
 
 
-def base_line(args, height):
+def base_line(args, wl, height):
+    tg = tile_groups_for(args.workload, args.gpus)
     return {"metric": "Mrays/s (primary+shadow+secondary rays, reference definition) on the conference path tracer", "unit": "Mrays/s",
-            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic (procedural conference stand-in, seed 7, 328120 triangles; conference.obj is absent from the reference snapshot)",
-            "config": {"workload": "BASELINE config 4: conference (stand-in), PathTracer, 1 spl, %dx%d, %d spp per GPU (sample-partitioned, NCCL reduce)" % (WIDTH, height, SPP),
-                       "width": WIDTH, "height": height, "spp_per_gpu": SPP, "spp_total": SPP * args.gpus, "samples_light": SPL,
-                       "shader": "PathTracer", "accelerator": "BVH", "parallelism": "sample-partition x%d" % args.gpus}}
+            "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic (procedural conference stand-in, seed 7, 328120 triangles x %d, materials of the reference's conference.mtl; conference.obj is absent from the reference snapshot)" % wl["copies"],
+            "config": {"workload": wl["name"] % (wl["width"], height), "width": wl["width"], "height": height, "spp_total": wl["spp"],
+                       "spp_per_gpu": wl["spp"] / (args.gpus / tg), "samples_light": SPL, "shader": "PathTracer", "accelerator": "BVH",
+                       "parallelism": "%d tile group(s) x %d sample group(s)" % (tg, args.gpus // tg)}}
+
+
+def load_scene(wl, rank, world, dist):
+    from mobileraytracer_b200 import loaders
+    obj, mtl, cam_path = scene_files() if rank == 0 else (None, None, None)
+    if world > 1:
+        dist.barrier()
+        obj, mtl, cam_path = scene_files()
+    arrays = loaders.load_obj(obj, mtl).arrays()
+    if wl["copies"] > 1:
+        arrays = loaders.replicate_scene(arrays, 6, 5)
+    camera = loaders.load_camera(cam_path, np.float32(wl["width"]) / np.float32(round_down16(wl["height_asked"])))
+    return arrays, camera
 
 
 # ---- the reference's own CPU renderer (oracle/_ref): the --impl reference arm and the cpu_baseline leg --------------
@@ -99,17 +136,17 @@ class ReferenceCpu:
     """The unmodified reference engine (compiled from /root/reference by oracle/Makefile into oracle/_ref), driven like
     C_wrapper.cpp's work_thread: OBJ scene, BVH accelerator, PathTracer, all host threads."""
 
-    def __init__(self, height, spp):
+    def __init__(self, width, height, spp):
         from oracle import refbind
         if not refbind.available():
             raise RuntimeError("oracle/_ref/libmobilert_ref.so missing (built by __graft_entry__.build() where /root/reference exists)")
         obj, mtl, cam = scene_files()
         self.threads = os.cpu_count() or 1
-        self.spp = spp
+        self.spp, self.width, self.height = spp, width, height
         t0 = time.perf_counter()
-        self.r = refbind.RefRenderer(WIDTH, height, SHADER_PATHTRACER, -1, spp=spp, spl=SPL, obj=obj, mtl=mtl, cam=cam)
+        self.r = refbind.RefRenderer(width, height, SHADER_PATHTRACER, -1, spp=spp, spl=SPL, obj=obj, mtl=mtl, cam=cam)
         self.create_s = time.perf_counter() - t0
-        self.bitmap = np.zeros(WIDTH * height, np.int32)
+        self.bitmap = np.zeros(width * height, np.int32)
         self.rays_before = self.r.casted_rays()
 
     def frame(self):
@@ -120,29 +157,31 @@ class ReferenceCpu:
         return secs, rays
 
 
-def cpu_baseline_sample(height):
+def cpu_baseline_sample(wl, height):
     """Bounded sample of the same workload on the host cores: full resolution, 1 spp warm-up, then as many samples per
-    pixel as fit in about 10 s (1..4)."""
-    ref = ReferenceCpu(height, 1)
+    pixel as fit in about 10 s (1..4). (c5: the reference's single-threaded BVH build over 9.8 M triangles does not fit
+    a bench run, so its sample is the un-replicated room at the c5 resolution; said in `sample`.)"""
+    ref = ReferenceCpu(wl["width"], height, 1)
     s1, _ = ref.frame()
     spp = int(max(1, min(4, round(10.0 / max(s1, 1e-3)))))
     ref.r.close()
-    ref = ReferenceCpu(height, spp)
+    ref = ReferenceCpu(wl["width"], height, spp)
     secs, rays = ref.frame()
     out = {"value": rays / secs / 1e6, "unit": "Mrays/s", "cores": ref.threads, "kind": "reference",
-           "sample": "same scene, PathTracer, %dx%d, %d spp (of 64), 1 frame, %d threads, %.2f s; reference BVH+scene create %.2f s" % (
-               WIDTH, height, spp, ref.threads, secs, ref.create_s),
-           "ms_per_frame_at_64spp_extrapolated": secs * 1e3 * SPP / spp}
+           "sample": "%s, PathTracer, %dx%d, %d spp (of %d), 1 frame, %d threads, %.2f s; reference BVH+scene create %.2f s" % (
+               "same scene" if wl["copies"] == 1 else "ONE copy of the room (the reference's single-threaded build of the 30x scene is out of reach)",
+               wl["width"], height, spp, wl["spp"], ref.threads, secs, ref.create_s),
+           "ms_per_frame_at_full_spp_extrapolated": secs * 1e3 * wl["spp"] / spp}
     ref.r.close()
     return out
 
 
-def run_reference(args, height):
+def run_reference(args, wl, height):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     spp = 1
-    ref = ReferenceCpu(height, spp)
+    ref = ReferenceCpu(wl["width"], height, spp)
     for _ in range(args.warmup):
         ref.frame()
     tot_s, tot_rays = 0.0, 0
@@ -150,9 +189,10 @@ def run_reference(args, height):
         s, r = ref.frame()
         tot_s += s
         tot_rays += r
-    line = base_line(args, height)
+    line = base_line(args, wl, height)
     v = tot_rays / tot_s / 1e6
-    sample = "each step = one %dx%d PathTracer frame at %d spp (bounded sample of the 64-spp frame), %d host threads" % (WIDTH, height, spp, ref.threads)
+    sample = "each step = one %dx%d PathTracer frame at %d spp (bounded sample of the %d-spp frame%s), %d host threads" % (
+        wl["width"], height, spp, wl["spp"], "" if wl["copies"] == 1 else ", one copy of the room", ref.threads)
     line.update({"impl": "reference", "value": v, "ms_per_step": tot_s * 1e3 / args.steps,
                  "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": ref.threads, "kind": "reference", "sample": sample},
                  "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -161,14 +201,61 @@ def run_reference(args, height):
     print(json.dumps(line))
 
 
+# ---- roofs -------------------------------------------------------------------------------------------------------
+def measured_gather_peaks():
+    """Own microbenchmark (tools/microbench/l2_gather.cu): random 80-byte and 48-byte record gathers with the launch shape
+    of the traversal kernels, from an L2-resident 20 MB buffer and from a 2 GB buffer (HBM)."""
+    path = os.path.join(ROOT, "mobileraytracer_b200", "libmrt_microbench.so")
+    if not os.path.exists(path):
+        return None
+    L = ctypes.CDLL(path)
+    L.mrt_microbench_gather.restype = ctypes.c_double
+    L.mrt_microbench_gather.argtypes = [ctypes.c_int, ctypes.c_longlong, ctypes.c_int, ctypes.c_int]
+    out = {}
+    for name, rec, size in (("l2_80B", 80, 20 << 20), ("l2_48B", 48, 20 << 20), ("hbm_80B", 80, 2 << 30), ("hbm_48B", 48, 2 << 30)):
+        out[name + "_gbs"] = L.mrt_microbench_gather(rec, size, 256, 3)
+    out["how"] = "tools/microbench/l2_gather.cu: 148x8 CTAs x 128 threads, every lane gathers random records (5 or 3 x LDG.128), 256 steps, best of 3"
+    return out
+
+
+def roofline_block(kernel, rays, ms, bytes_per_ray, inputs, clk, hbm_peak, hbm_src, gather):
+    """The three roofs of one traversal kernel: issue rate (what ncu shows to bind), L2 gather, HBM.
+    inputs = profiles/roofline_inputs.json[kernel]: warp instructions per ray and gathered bytes per ray from the ncu /
+    counting-build captures named there; rays and ms are measured live with CUDA events."""
+    if not ms or not rays:
+        return None
+    secs = ms * 1e-3
+    sm_mhz = (clk or {}).get("sm_mhz") or (clk or {}).get("sm_max_mhz") or 1965.0
+    issue_peak = 148 * 4 * sm_mhz * 1e6 / 1e9          # G warp-instructions/s: 4 schedulers per SM, one instruction per cycle each
+    blk = {"kernel": kernel, "rays": rays, "ms": ms, "grays_per_s": rays / secs / 1e9}
+    hbm = bytes_per_ray * rays / secs / 1e9
+    blk["hbm"] = {"achieved": hbm, "peak": hbm_peak, "unit": "GB/s", "frac": hbm / hbm_peak, "bytes_per_ray": bytes_per_ray,
+                  "peak_source": hbm_src, "traffic": (inputs or {}).get("dram_bytes_per_ray_measured")}
+    fr = {"hbm": blk["hbm"]["frac"]}
+    if inputs and inputs.get("warp_inst_per_ray"):
+        ach = inputs["warp_inst_per_ray"] * rays / secs / 1e9
+        blk["issue"] = {"achieved": ach, "peak": issue_peak, "unit": "G warp-inst/s", "frac": ach / issue_peak,
+                        "warp_inst_per_ray": inputs["warp_inst_per_ray"], "threads_per_inst": inputs.get("threads_per_inst"),
+                        "sm_mhz": sm_mhz, "source": inputs.get("source")}
+        fr["issue"] = blk["issue"]["frac"]
+    if inputs and inputs.get("gather_bytes_per_ray") and gather and gather.get("l2_80B_gbs", 0) > 0:
+        ach = inputs["gather_bytes_per_ray"] * rays / secs / 1e9
+        blk["l2_gather"] = {"achieved": ach, "peak": gather["l2_80B_gbs"], "unit": "GB/s", "frac": ach / gather["l2_80B_gbs"],
+                            "gather_bytes_per_ray": inputs["gather_bytes_per_ray"], "source": inputs.get("gather_source")}
+        fr["l2_gather"] = blk["l2_gather"]["frac"]
+    blk["bound"] = max(fr, key=fr.get)
+    return blk
+
+
 # ---- this library -----------------------------------------------------------------------------------------------
-def run_b200(args, height):
+def run_b200(args, wl, height):
     import torch
     import torch.distributed as dist
     import mobileraytracer_b200 as mrt
-    from mobileraytracer_b200 import capi, loaders
+    from mobileraytracer_b200 import capi
     from mobileraytracer_b200.multigpu import DistributedRenderer
 
+    width, spp = wl["width"], wl["spp"]
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -180,18 +267,13 @@ def run_b200(args, height):
         dist.init_process_group("nccl", device_id=dev)
     assert world == args.gpus, "launch with torchrun --nproc-per-node %d" % args.gpus
 
-    obj, mtl, cam_path = scene_files() if rank == 0 else (None, None, None)
-    if world > 1:
-        dist.barrier()
-        obj, mtl, cam_path = scene_files()
-    scene = loaders.load_obj(obj, mtl)
-    camera = loaders.load_camera(cam_path, np.float32(WIDTH) / np.float32(height))
-    arrays = scene.arrays()
+    arrays, camera = load_scene(wl, rank, world, dist)
     n_tri, n_lights = len(arrays["triangles"]), len(arrays["lights"])
-    stream = torch.cuda.current_stream(dev)
+    tg = tile_groups_for(args.workload, world)
 
-    # value: device-resident frame (scene, queues, accumulator and bitmap all in HBM)
-    dr = DistributedRenderer(arrays, camera, WIDTH, height, SPP * world, SPL, capi.SHADER_PATHTRACER, seed=1)
+    # value: device-resident frame (scene, queues, accumulator and bitmap all in HBM), all of it on dr.stream
+    dr = DistributedRenderer(arrays, camera, width, height, spp, SPL, capi.SHADER_PATHTRACER, seed=1, tile_groups=tg)
+    stream = dr.stream
     stats0 = dr.local.stats()
 
     def barrier():
@@ -217,42 +299,59 @@ def run_b200(args, height):
     clocks = ClockSampler(local_rank) if rank == 0 else None
     if clocks:
         clocks.start()
-    ext_ms = sh_ms = shade_ms = other_ms = 0.0
-    ext_rays = sh_rays = launches = 0
+    acc = {"extend_ms": 0.0, "shadow_ms": 0.0, "shade_ms": 0.0, "other_ms": 0.0, "rays_extend_traced": 0, "rays_shadow_traced": 0,
+           "launches": 0, "pass_retries": 0}
 
     def step_value():
-        nonlocal ext_ms, sh_ms, shade_ms, other_ms, ext_rays, sh_rays, launches
         dr.renderFrameDevice()
         st = dr.local.stats()     # host-side read of figures the library took with CUDA events on this stream
-        ext_ms += st["extend_ms"]; sh_ms += st["shadow_ms"]; shade_ms += st["shade_ms"]; other_ms += st["other_ms"]
-        ext_rays += st["rays_extend_traced"]; sh_rays += st["rays_shadow_traced"]
-        launches += st["launches"] + (1 if rank == 0 else 0)
+        for k in acc:
+            acc[k] += st[k]
+        acc["launches"] += (2 if rank == 0 else 1) + (1 if world > 1 else 0)   # zero, resolve, the NCCL kernel
 
+    dr.timePhases(True)
     total_ms = timed(step_value, args.steps)
+    phases = dr.phaseTimes()
+    dr.timePhases(False)
     clk = clocks.summary() if clocks else None
     rays_frame = dr.totalCastedRays()
     st = dr.local.stats()
     value = rays_frame * args.steps / (total_ms * 1e-3) / 1e6
+    # per-kind ray counts of the whole job
+    kinds = torch.tensor([st["rays_primary"], st["rays_shadow"], st["rays_secondary"], st["rays_extend_traced"], st["rays_shadow_traced"]],
+                         dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.all_reduce(kinds)
+    kinds = [int(x) for x in kinds.tolist()]
 
     # e2e: the reference-facing call with HOST buffers. N=1: mrt_set_camera + mrt_render_frame (exact integer running
     # average) into the caller's pinned bitmap; N>1: DistributedRenderer.renderFrame (reduce + resolve + D2H on rank 0).
-    host_bitmap = torch.zeros(WIDTH * height, dtype=torch.int32).pin_memory()
+    host_bitmap = torch.zeros(width * height, dtype=torch.int32).pin_memory()
+    clocks2 = ClockSampler(local_rank) if rank == 0 else None
+    r1 = None
     if world == 1:
-        r1 = mrt.Renderer(arrays, camera, WIDTH, height, SPP, SPL, capi.SHADER_PATHTRACER, seed=1)
+        dr.close()      # one set of queues at a time (c5: several GB)
+        r1 = mrt.Renderer(arrays, camera, width, height, spp, SPL, capi.SHADER_PATHTRACER, seed=1)
         r1.setStream(stream.cuda_stream)
         hb = host_bitmap.numpy()
 
         def step_e2e():
             r1.setCamera(camera)
             r1.renderFrame(hb)
-        rays_e2e_frame = None
     else:
         def step_e2e():
             dr.renderFrame(host_bitmap)
+        dr.timePhases(True)
     e2e_warm = max(1, min(args.warmup, 2))
     for _ in range(e2e_warm):
         step_e2e()
+    if world > 1:
+        dr.phaseTimes()
+    if clocks2:
+        clocks2.start()
     e2e_ms = timed(step_e2e, args.steps)
+    clk2 = clocks2.summary() if clocks2 else None
+    e2e_phases = dr.phaseTimes() if world > 1 else None
     rays_e2e_frame = r1.getTotalCastedRays() if world == 1 else dr.totalCastedRays()
     e2e_value = rays_e2e_frame * args.steps / (e2e_ms * 1e-3) / 1e6
 
@@ -262,46 +361,77 @@ def run_b200(args, height):
             peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (measured copy bandwidth)"
         else:
             peak, peak_src = 6650.0, "fallback 6.65 TB/s (B200_PROFILING.md)"
-        achieved = BYTES_PER_CLOSEST_RAY * ext_rays / (ext_ms * 1e-3) / 1e9 if ext_ms > 0 else None
-        traffic = None
-        tp = os.path.join(ROOT, "profiles", "roofline_traffic.json")
-        if os.path.exists(tp):
-            traffic = json.load(open(tp)).get("k_wf_extend_dram_bytes_per_launch")
-        n_ext_launch = st["extend_launches"] * args.steps
-        line = base_line(args, height)
+        inputs = {}
+        ip = os.path.join(ROOT, "profiles", "roofline_inputs.json")
+        if os.path.exists(ip):
+            inputs = json.load(open(ip)).get(args.workload, {})
+        gather = None
+        try:
+            gather = measured_gather_peaks()
+        except Exception as ex:
+            gather = {"error": str(ex)}
+        K = args.steps
+        rf_ext = roofline_block("k_wf_extend (closest-hit BVH8 traversal)", acc["rays_extend_traced"], acc["extend_ms"], BYTES_PER_CLOSEST_RAY,
+                                inputs.get("k_wf_extend"), clk, peak, peak_src, gather)
+        rf_sh = roofline_block("k_wf_shadow (any-hit BVH8 traversal)", acc["rays_shadow_traced"], acc["shadow_ms"], BYTES_PER_SHADOW_RAY,
+                               inputs.get("k_wf_shadow"), clk, peak, peak_src, gather)
+        # shade: streams the hit + ray records in and the shadow / continuation records out; HBM is its roof
+        shade_in = inputs.get("k_wf_shade", {})
+        shade_bytes = shade_in.get("algorithmic_bytes_per_hit", 176)
+        rf_shade = None
+        if acc["shade_ms"] > 0:
+            a = shade_bytes * acc["rays_extend_traced"] / (acc["shade_ms"] * 1e-3) / 1e9
+            rf_shade = {"kernel": "k_wf_shade", "bound": "hbm", "achieved": a, "peak": peak, "unit": "GB/s", "frac": a / peak,
+                        "bytes_per_hit": shade_bytes, "ms": acc["shade_ms"],
+                        "note": "16 B hit + 32..64 B ray read, 48 B shadow record + 64 B continuation ray written (upper bound: not every hit emits both)"}
+        line = base_line(args, wl, height)
+        bound = rf_ext["bound"] if rf_ext else "hbm"
+        top = dict(rf_ext[bound]) if rf_ext else {}
+        top.update({"kernel": "k_wf_extend (closest-hit BVH8 traversal)", "bound": bound, "hbm": rf_ext["hbm"] if rf_ext else None,
+                    "issue": rf_ext.get("issue") if rf_ext else None, "l2_gather": rf_ext.get("l2_gather") if rf_ext else None,
+                    "traffic": (inputs.get("k_wf_extend") or {}).get("dram_bytes_per_launch"),
+                    "rays_per_launch": acc["rays_extend_traced"] / max(st["extend_launches"] * K, 1),
+                    "launch_ms_avg": acc["extend_ms"] / max(st["extend_launches"] * K, 1),
+                    "note": "the scene is L2-resident at c4, so the kernel is issue-bound (ncu: profiles/); HBM (compulsory queue bytes) is the stated secondary roof"})
         line.update({
-            "value": value, "ms_per_step": total_ms / args.steps,
-            "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_frame": e2e_ms / args.steps, "h2d_bytes_per_step": 52,
-                    "d2h_bytes_per_step": WIDTH * height * 4,
+            "value": value, "ms_per_step": total_ms / K,
+            "e2e": {"value": e2e_value, "unit": "Mrays/s", "ms_per_frame": e2e_ms / K, "h2d_bytes_per_step": 52,
+                    "d2h_bytes_per_step": width * height * 4,
                     "path": "mrt_set_camera + mrt_render_frame (pinned host ABGR8888 bitmap)" if world == 1 else
-                            "DistributedRenderer.renderFrame: mrt_render_accumulate_device per rank + NCCL reduce + mrt_resolve_device + D2H on rank 0"},
-            "gpu_launches": int(launches),
+                            "DistributedRenderer.renderFrame: mrt_render_accumulate_device per rank + NCCL reduce + mrt_resolve_device + D2H on rank 0",
+                    "phases_ms_per_frame_rank0": {k: v / K for k, v in e2e_phases.items()} if e2e_phases else None,
+                    "clocks": clk2},
+            "gpu_launches": int(acc["launches"]),
             "clocks": clk,
-            "roofline": {"kernel": "k_wf_extend (closest-hit BVH8 traversal)", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak if achieved else None, "traffic": traffic, "peak_source": peak_src,
-                         "bytes_per_ray": BYTES_PER_CLOSEST_RAY, "rays_per_launch": ext_rays / max(n_ext_launch, 1),
-                         "launch_ms_avg": ext_ms / max(n_ext_launch, 1),
-                         "note": "compulsory queue bytes only; the 25 MB scene is L2-resident, so the kernel is L2-gather/latency bound, see profiles/"},
-            "kernel_ms_per_frame": {"extend": ext_ms / args.steps, "shadow": sh_ms / args.steps, "shade": shade_ms / args.steps, "other": other_ms / args.steps},
-            "rays_per_frame": {"total_all_gpus": rays_frame, "primary": st["rays_primary"], "shadow": st["rays_shadow"], "secondary": st["rays_secondary"],
-                               "extend_traced": st["rays_extend_traced"], "shadow_traced": st["rays_shadow_traced"]},
-            "kernel_grays_per_s": {"extend_closest_hit": ext_rays / (ext_ms * 1e-3) / 1e9 if ext_ms > 0 else None,
-                                   "shadow_any_hit": sh_rays / (sh_ms * 1e-3) / 1e9 if sh_ms > 0 else None,
-                                   "note": "rays traversed by the kernel / summed CUDA-event time of its launches, all ranks' average"},
-            "grays_per_s_primary_plus_shadow": (st["rays_primary"] + st["rays_shadow"]) * world * args.steps / (total_ms * 1e-3) / 1e9,
+            "roofline": top,
+            "roofline_shadow": rf_sh, "roofline_shade": rf_shade,
+            "gather_peaks": gather,
+            "phases_ms_per_frame_rank0": {k: v / K for k, v in phases.items()},
+            "kernel_ms_per_frame": {"extend": acc["extend_ms"] / K, "shadow": acc["shadow_ms"] / K, "shade": acc["shade_ms"] / K, "other": acc["other_ms"] / K,
+                                    "note": "rank 0's share; CUDA events around every launch on the frame stream"},
+            "rays_per_frame": {"total_all_gpus": rays_frame, "primary": kinds[0], "shadow": kinds[1], "secondary": kinds[2],
+                               "extend_traced": kinds[3], "shadow_traced": kinds[4]},
+            "kernel_grays_per_s": {"extend_closest_hit": rf_ext["grays_per_s"] if rf_ext else None, "shadow_any_hit": rf_sh["grays_per_s"] if rf_sh else None,
+                                   "note": "rays traversed by rank 0's kernel / summed CUDA-event time of its launches"},
+            "grays_per_s_primary_plus_shadow": (kinds[0] + kinds[1]) * K / (total_ms * 1e-3) / 1e9,
+            "pass_retries": acc["pass_retries"],
             "scene": {"triangles": n_tri, "area_lights": n_lights, "bvh_nodes": stats0["bvh_nodes"], "bvh_bytes": stats0["bvh_bytes"],
-                      "build_ms": stats0["build_ms"], "upload_ms": stats0["upload_ms"]},
+                      "build_ms": stats0["build_ms"], "upload_ms": stats0["upload_ms"], "queue_bytes": st["queue_bytes"]},
         })
         line["config"]["l2"] = ("not flushed between steps: every step streams its ray / hit / shadow queues (several GB per frame, far above the "
-                                "126 MB L2) while the %.0f MB scene stays L2-resident by design" % (stats0["scene_bytes"] / 1e6))
+                                "126 MB L2) while the %.0f MB scene stays L2-resident by design" % (stats0["scene_bytes"] / 1e6)
+                                if wl["copies"] == 1 else "inputs larger than L2: %.0f MB scene + several GB of queues per frame" % (stats0["scene_bytes"] / 1e6))
         if args.gpus == 1 and not args.no_cpu_baseline:
             try:
-                line["cpu_baseline"] = cpu_baseline_sample(height)
+                line["cpu_baseline"] = cpu_baseline_sample(wl, height)
             except Exception as ex:   # the checker is optional infrastructure; the GPU numbers stand without it
                 line["cpu_baseline"] = {"value": None, "unit": "Mrays/s", "cores": os.cpu_count(), "kind": "reference", "sample": "unavailable: %s" % ex}
         print(json.dumps(line))
     barrier()
-    dr.close()
+    if r1 is not None:
+        r1.close()
+    else:
+        dr.close()
     if world > 1:
         dist.destroy_process_group()
 
@@ -312,13 +442,15 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="c4", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
-    height = round_down16(HEIGHT_ASKED)
+    wl = WORKLOADS[args.workload]
+    height = round_down16(wl["height_asked"])
     if args.impl == "reference":
-        run_reference(args, height)
+        run_reference(args, wl, height)
     else:
-        run_b200(args, height)
+        run_b200(args, wl, height)
 
 
 if __name__ == "__main__":

@@ -83,7 +83,13 @@ enum { MRT_SHADER_NOSHADOWS = 0, MRT_SHADER_WHITTED = 1, MRT_SHADER_PATHTRACER =
 enum { MRT_ACC_NAIVE = 1, MRT_ACC_REGULAR_GRID = 2, MRT_ACC_BVH = 3, MRT_ACC_B200 = 4 };
 /* pixel-jitter sampler (C_wrapper.cpp:144-148 picks Constant(0.5) for spp==1, StaticHaltonSeq otherwise) */
 enum { MRT_SAMPLER_AUTO = 0, MRT_SAMPLER_CONSTANT = 1, MRT_SAMPLER_STATIC_HALTON = 2, MRT_SAMPLER_STATIC_MT = 3,
-       MRT_SAMPLER_STATIC_PCG = 4 /* the Android front-end's choice (JNI_layer.cpp:601,616-618,636; Components/Samplers/StaticPCG.cpp) */ };
+       MRT_SAMPLER_STATIC_PCG = 4 /* the Android front-end's choice (JNI_layer.cpp:601,616-618,636; Components/Samplers/StaticPCG.cpp) */,
+       MRT_SAMPLER_HALTON = 5     /* HaltonSeq(width, height, samples) (Components/Samplers/HaltonSeq.cpp:10-19): radical inverse of the
+                                     draw counter, 1.0 once Sampler::domainSize_ draws have been made */,
+       MRT_SAMPLER_STRATIFIED = 6 /* Stratified(width, height, samples) (Stratified.cpp:10-19): counter / domainSize_, then 1.0 */,
+       MRT_SAMPLER_STREAM = 7     /* the draws come from the caller (mrt_set_pixel_stream): MersenneTwister (MersenneTwister.cpp:5-11)
+                                     and PCG (PCG.cpp:6-13) keep hidden thread-local generator state, so the host takes the frame's
+                                     draws from the sampler object itself and hands them over, index for index */ };
 
 enum {
     MRT_FLAG_FP32_ACCUMULATE = 1,  /* accumulate radiance in fp32 and quantise once (needed for multi-GPU partitions);
@@ -119,6 +125,11 @@ typedef struct mrt_render_desc {
     int32_t light_sampler;          /* table behind the samplers the front-end creates itself, i.e. the area lights of an OBJ scene
                                        (OBJLoader::fillScene's lambda) and the PathTracer's russian roulette: MRT_SAMPLER_AUTO or
                                        _STATIC_HALTON (C_wrapper.cpp:109,176), or MRT_SAMPLER_STATIC_PCG (JNI_layer.cpp:601,636) */
+    int32_t tile_begin, tile_stride; /* multi-GPU tile partition: this handle renders tiles tile_begin,
+                                       tile_begin + tile_stride, ... of the 256 tiles of Renderer::renderScene's shuffled tile walk
+                                       (Renderer.cpp:119-135,189-197) and leaves every other pixel untouched; its queues are sized for
+                                       that share. 0 / 0 (or stride 1) = all tiles. The jitter draws of a pixel-sample do not depend
+                                       on the partition. Not available together with MRT_FLAG_REPLAY_SAMPLERS. */
 } mrt_render_desc;
 
 /* The reference's shuffled tables, when the caller wants the very same sequences (parity runs):
@@ -146,6 +157,9 @@ typedef struct mrt_stats {
                                                         (a depth-7 ray is constructed and counted but never traced) */
     uint64_t bvh_nodes, bvh_bytes, scene_bytes;
     int64_t  n_primitives;      /* JNI rtInitialize's return value (JNI_layer.cpp:676-680) */
+    uint64_t pass_retries;      /* wavefront: passes of the last frame that were repeated with fewer samples (or larger queues)
+                                   because a ray queue overflowed; the frame is still complete and correct */
+    uint64_t queue_bytes;       /* wavefront: device memory of the ray / shadow queues and path accumulators */
 } mrt_stats;
 
 typedef struct mrt_handle mrt_handle;
@@ -171,11 +185,17 @@ int mrt_render_accumulate_device(mrt_handle *h, void *device_accum_rgba32f, int3
 /* Quantises an fp32 RGBA accumulator (sum of per-sample trunc(255*c), .w = sample count) to ABGR8888 on the device. */
 int mrt_resolve_device(mrt_handle *h, const void *device_accum_rgba32f, void *device_bitmap);
 
+/* MRT_SAMPLER_STREAM: the pixel sampler's draws of the NEXT frame(s) in the order a single-threaded Renderer::renderScene makes
+ * them (Renderer.cpp:137-138: two per pixel-sample; tile walk, samples outermost). n >= 2 * samples_pixel * 256 * (width/16) *
+ * (height/16) serves a whole frame; a shorter stream wraps around. HOST array, copied. */
+int mrt_set_pixel_stream(mrt_handle *h, const float *draws, int64_t n);
+
 /* Replaces: the camera_ member the front-ends rebuild between frames (JNI_layer.cpp:164; C_wrapper.cpp:76-141). */
 int mrt_set_camera(mrt_handle *h, const mrt_camera_desc *camera);
 
 /* Makes every later call on this handle enqueue its kernels and copies on the caller's CUDA stream (a cudaStream_t passed
- * as void*; NULL restores the handle's own stream), so that a host runtime that owns streams and events (the JNI layer's
+ * as void*; NULL restores the handle's own stream, so the legacy default stream, whose handle is 0, has to be named by
+ * cudaStreamLegacy = (cudaStream_t)0x1), so that a host runtime that owns streams and events (the JNI layer's
  * render thread has none; a PyTorch / NCCL host does) can order and time the frame with its own events. Calls stay
  * blocking: they synchronise that stream before returning. */
 int mrt_set_stream(mrt_handle *h, void *cuda_stream);

@@ -10,7 +10,7 @@ LIB_PATH = os.environ.get("MRT_B200_LIB") or os.path.join(_HERE, "libmobilert_b2
 MRT_OK, MRT_ERR_INVALID, MRT_ERR_CUDA, MRT_ERR_OOM, MRT_ERR_STOPPED, MRT_ERR_OVERFLOW = range(6)
 SHADER_NOSHADOWS, SHADER_WHITTED, SHADER_PATHTRACER, SHADER_DEPTHMAP, SHADER_DIFFUSE = range(5)
 ACC_NAIVE, ACC_REGULAR_GRID, ACC_BVH, ACC_B200 = 1, 2, 3, 4
-SAMPLER_AUTO, SAMPLER_CONSTANT, SAMPLER_STATIC_HALTON, SAMPLER_STATIC_MT, SAMPLER_STATIC_PCG = range(5)
+SAMPLER_AUTO, SAMPLER_CONSTANT, SAMPLER_STATIC_HALTON, SAMPLER_STATIC_MT, SAMPLER_STATIC_PCG, SAMPLER_HALTON, SAMPLER_STRATIFIED, SAMPLER_STREAM = range(8)
 FLAG_FP32_ACCUMULATE, FLAG_SORT_BY_MATERIAL, FLAG_REPLAY_SAMPLERS, FLAG_PROGRESSIVE = 1, 2, 4, 8
 CAMERA_PERSPECTIVE, CAMERA_ORTHOGRAPHIC = 0, 1
 LIGHT_POINT, LIGHT_AREA = 0, 1
@@ -46,7 +46,8 @@ class CameraDesc(C.Structure):
 class RenderDesc(C.Structure):
     _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("samples_pixel", C.c_int32), ("samples_light", C.c_int32),
                 ("shader", C.c_int32), ("accelerator", C.c_int32), ("pixel_sampler", C.c_int32), ("seed", C.c_uint32),
-                ("flags", C.c_uint32), ("depth_max_point", C.c_float * 3), ("device", C.c_int32), ("light_sampler", C.c_int32)]
+                ("flags", C.c_uint32), ("depth_max_point", C.c_float * 3), ("device", C.c_int32), ("light_sampler", C.c_int32),
+                ("tile_begin", C.c_int32), ("tile_stride", C.c_int32)]
 
 
 class SamplerTables(C.Structure):
@@ -60,7 +61,7 @@ class Stats(C.Structure):
                 ("rays_primary", C.c_uint64), ("rays_shadow", C.c_uint64), ("rays_secondary", C.c_uint64),
                 ("launches", C.c_uint64), ("extend_launches", C.c_uint64), ("shadow_launches", C.c_uint64),
                 ("shade_launches", C.c_uint64), ("rays_extend_traced", C.c_uint64), ("rays_shadow_traced", C.c_uint64), ("bvh_nodes", C.c_uint64), ("bvh_bytes", C.c_uint64), ("scene_bytes", C.c_uint64),
-                ("n_primitives", C.c_int64)]
+                ("n_primitives", C.c_int64), ("pass_retries", C.c_uint64), ("queue_bytes", C.c_uint64)]
 
     def as_dict(self):
         return {k: getattr(self, k) for k, _ in self._fields_}
@@ -68,7 +69,7 @@ class Stats(C.Structure):
 
 # every symbol include/mobilert_b200.h declares
 SYMBOLS = ["mrt_create", "mrt_destroy", "mrt_render_frame", "mrt_render_frame_device", "mrt_render_accumulate_device",
-           "mrt_resolve_device", "mrt_set_camera", "mrt_set_stream", "mrt_stop", "mrt_set_replay_counter", "mrt_get_replay_counter", "mrt_get_sample", "mrt_get_total_rays", "mrt_get_stats",
+           "mrt_resolve_device", "mrt_set_camera", "mrt_set_pixel_stream", "mrt_set_stream", "mrt_stop", "mrt_set_replay_counter", "mrt_get_replay_counter", "mrt_get_sample", "mrt_get_total_rays", "mrt_get_stats",
            "mrt_last_error", "mrt_trace_rays", "mrt_generate_rays", "mrt_shade_rays", "mrt_test_triangle_intersect",
            "mrt_test_sphere_intersect", "mrt_test_plane_intersect", "mrt_test_aabb_intersect", "mrt_test_incremental_avg",
            "mrt_test_halton", "mrt_device_count", "mrt_version"]
@@ -100,6 +101,7 @@ def lib():
         L.mrt_resolve_device.argtypes = [vp, vp, vp]
         L.mrt_set_camera.argtypes = [vp, C.POINTER(CameraDesc)]
         L.mrt_set_stream.argtypes = [vp, vp]
+        L.mrt_set_pixel_stream.argtypes = [vp, vp, i64]
         L.mrt_stop.argtypes = [vp]
         L.mrt_set_replay_counter.argtypes = [vp, C.c_uint32]
         L.mrt_get_replay_counter.argtypes = [vp, C.POINTER(C.c_uint32)]

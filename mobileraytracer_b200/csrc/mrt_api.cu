@@ -5,6 +5,7 @@
 #include "mrt_refbvh.h"
 #include "mrt_render.h"
 #include "mrt_wavefront.h"
+#include <algorithm>
 #include <atomic>
 #include <cerrno>
 #include <cstdlib>
@@ -40,6 +41,7 @@ struct DevMem {
 struct mrt_handle {
     bool naive = false;              // MRT_ACC_NAIVE semantics for planes / spheres / the triangle root box
     uint32_t roots_per_sample = 0;   // valid pixels of one sample (wavefront path slots)
+    bool tiles_disjoint = true;      // no two path slots of a sample share a pixel (false for image sizes that are not multiples of 16)
     uint32_t replay_index_counter = 0;   // MRT_FLAG_REPLAY_SAMPLERS: value of Shader::getLightIndex's counter at the next frame's first draw
     int device = 0;
     cudaStream_t stream = nullptr;       // stream in use (own_stream unless mrt_set_stream installed the caller's)
@@ -52,7 +54,7 @@ struct mrt_handle {
     uint32_t flags = 0;
     Bvh8 bvh {};
     DevMem d_tris9, d_tri_shade, d_sphere_nodes, d_spheres, d_plane_nodes, d_planes, d_materials, d_lights;
-    DevMem d_tile, d_shader_table, d_static_halton, d_static_mt, d_static_pcg, d_inv_tile, d_tile_base, d_textures, d_texels, d_bitmap, d_accum, d_counters, d_scratch;
+    DevMem d_tile, d_shader_table, d_static_halton, d_static_mt, d_static_pcg, d_inv_tile, d_tile_base, d_textures, d_texels, d_bitmap, d_accum, d_counters, d_counters_saved, d_pixel_stream;
     std::vector<int> plane_slot_of_id, sphere_slot_of_id;
     int32_t *h_pinned_bitmap = nullptr;
     // MRT_FLAG_PROGRESSIVE: the caller's host bitmap is refreshed while the frame renders (set for the duration of a frame)
@@ -319,7 +321,8 @@ int upload_tables(mrt_handle *h, const mrt_render_desc &rd, const mrt_sampler_ta
     if (need_pcg && !p_pcg) { make_pcg_table(spcg, kArraySize, rd.seed * 4u + 5u); p_pcg = spcg.data(); }
     // Renderer::renderScene's tile -> first pixel mapping (Renderer.cpp:125-133), integer for integer
     std::vector<int2> origin(kNumberOfTiles, make_int2(0, 0));
-    std::vector<uint32_t> tile_base(kNumberOfTiles + 1, 0u);   // valid pixels before each tile (the wavefront's deterministic path slots)
+    std::vector<uint32_t> tile_base(kNumberOfTiles + 1, 0u);   // valid pixels before each tile this handle renders (the wavefront's deterministic path slots)
+    const int n_sel = h->rp.n_tiles;
     {
         const int w = rd.width, hgt = rd.height, bsx = h->rp.bsx, bsy = h->rp.bsy;
         if (bsx > 0 && bsy > 0) {
@@ -331,15 +334,16 @@ int upload_tables(mrt_handle *h, const mrt_render_desc &rd, const mrt_sampler_ta
                 const int startY = ((pixel / w) * bsy) % hgt;
                 origin[static_cast<size_t>(k)] = make_int2(pixel % w, startY);   // startX = (pixel + y * w) % w
             }
-            for (int k = 0; k < kNumberOfTiles; ++k) {
+            for (int j = 0; j < n_sel; ++j) {
                 // a pixel index past the end of the image is dropped (tile_pixel, mrt_shade.cuh); those are the last ones of the tile
+                const size_t k = static_cast<size_t>(h->rp.tile_begin + j * h->rp.tile_stride);
                 uint32_t valid = 0;
                 for (int ly = 0; ly < bsy; ++ly) {
-                    const long long first = static_cast<long long>(origin[static_cast<size_t>(k)].y + ly) * w + origin[static_cast<size_t>(k)].x;
+                    const long long first = static_cast<long long>(origin[k].y + ly) * w + origin[k].x;
                     const long long room = static_cast<long long>(resolution) - first;
                     valid += static_cast<uint32_t>(room <= 0 ? 0 : (room < bsx ? room : bsx));
                 }
-                tile_base[static_cast<size_t>(k) + 1] = tile_base[static_cast<size_t>(k)] + valid;
+                tile_base[static_cast<size_t>(j) + 1] = tile_base[static_cast<size_t>(j)] + valid;
             }
         }
     }
@@ -350,13 +354,26 @@ int upload_tables(mrt_handle *h, const mrt_render_desc &rd, const mrt_sampler_ta
     if (need_pcg) { API_CUDA(h, h->d_static_pcg.upload(p_pcg, kArraySize * sizeof(float), st)); }
     API_CUDA(h, h->d_inv_tile.upload(origin.data(), origin.size() * sizeof(int2), st));
     API_CUDA(h, h->d_tile_base.upload(tile_base.data(), tile_base.size() * sizeof(uint32_t), st));
-    h->roots_per_sample = tile_base[kNumberOfTiles];
+    h->roots_per_sample = tile_base[static_cast<size_t>(n_sel)];
+    {   // the wavefront's parallel resolve needs every pixel to belong to at most one path slot of a sample
+        bool disjoint = rd.width % 16 == 0 && rd.height % 16 == 0;
+        std::vector<long long> firsts;
+        for (int k = 0; k < kNumberOfTiles; ++k) { firsts.push_back(static_cast<long long>(origin[static_cast<size_t>(k)].y) * rd.width + origin[static_cast<size_t>(k)].x); }
+        std::sort(firsts.begin(), firsts.end());
+        if (std::adjacent_find(firsts.begin(), firsts.end()) != firsts.end()) { disjoint = false; }   // a caller's tile table may repeat a tile
+        h->tiles_disjoint = disjoint;
+    }
     API_CUDA(h, cudaStreamSynchronize(st));
     SceneDev &s = h->scene;
     s.tile_order = h->d_tile.as<float>(); s.shader_table = h->d_shader_table.as<float>(); s.static_halton = h->d_static_halton.as<float>();
     int ps = rd.pixel_sampler;
     if (ps == MRT_SAMPLER_AUTO) { ps = rd.samples_pixel > 1 ? MRT_SAMPLER_STATIC_HALTON : MRT_SAMPLER_CONSTANT; }  // C_wrapper.cpp:144-148
     h->rp.pixel_sampler = ps;
+    {   // Sampler::Sampler (MobileRT/Sampler.cpp:14-18): both factors divide by width / sqrt(NumberOfTiles)
+        const uint32_t w = static_cast<uint32_t>(rd.width), hgt = static_cast<uint32_t>(rd.height), per = w / 16u;
+        h->rp.sampler_domain = per > 0u ? (w / per) * (hgt / per) : 0u;
+        h->rp.pixel_stream_n = 1u;
+    }
     s.pixel_table = ps == MRT_SAMPLER_STATIC_HALTON ? s.static_halton
                   : ps == MRT_SAMPLER_STATIC_MT ? h->d_static_mt.as<float>()
                   : ps == MRT_SAMPLER_STATIC_PCG ? h->d_static_pcg.as<float>() : nullptr;
@@ -410,10 +427,14 @@ int mrt_create(const mrt_scene_desc *scene, const mrt_camera_desc *camera, const
     if (scene->n_triangles < 0 || scene->n_spheres < 0 || scene->n_planes < 0 || scene->n_materials < 0 || scene->n_lights < 0) { return fail(nullptr, MRT_ERR_INVALID, "negative count"); }
     if ((scene->n_triangles && !scene->triangles) || (scene->n_spheres && !scene->spheres) || (scene->n_planes && !scene->planes) ||
         (scene->n_materials && !scene->materials) || (scene->n_lights && !scene->lights)) { return fail(nullptr, MRT_ERR_INVALID, "null array with non-zero count"); }
-    if (render->pixel_sampler < MRT_SAMPLER_AUTO || render->pixel_sampler > MRT_SAMPLER_STATIC_PCG) { return fail(nullptr, MRT_ERR_INVALID, "unknown pixel_sampler"); }
+    if (render->pixel_sampler < MRT_SAMPLER_AUTO || render->pixel_sampler > MRT_SAMPLER_STREAM) { return fail(nullptr, MRT_ERR_INVALID, "unknown pixel_sampler"); }
     if (render->light_sampler != MRT_SAMPLER_AUTO && render->light_sampler != MRT_SAMPLER_STATIC_HALTON && render->light_sampler != MRT_SAMPLER_STATIC_PCG) {
         return fail(nullptr, MRT_ERR_INVALID, "light_sampler must be MRT_SAMPLER_AUTO, _STATIC_HALTON or _STATIC_PCG");
     }
+    if (render->tile_stride > 1 && (render->tile_begin < 0 || render->tile_begin >= render->tile_stride || render->tile_stride > kNumberOfTiles)) {
+        return fail(nullptr, MRT_ERR_INVALID, "tile partition: need 0 <= tile_begin < tile_stride <= 256");
+    }
+    if (render->tile_stride > 1 && (render->flags & MRT_FLAG_REPLAY_SAMPLERS)) { return fail(nullptr, MRT_ERR_INVALID, "MRT_FLAG_REPLAY_SAMPLERS needs every tile of the frame on this handle"); }
     if (render->flags & MRT_FLAG_REPLAY_SAMPLERS) {
         if (render->shader == MRT_SHADER_PATHTRACER) { return fail(nullptr, MRT_ERR_INVALID, "MRT_FLAG_REPLAY_SAMPLERS: the PathTracer's ray tree depends on the draws themselves; only NoShadows / Whitted can be replayed"); }
         if (scene->n_lights > kReplayMaxLights) { return fail(nullptr, MRT_ERR_INVALID, "MRT_FLAG_REPLAY_SAMPLERS supports up to 8 lights"); }
@@ -435,6 +456,9 @@ int mrt_create(const mrt_scene_desc *scene, const mrt_camera_desc *camera, const
         h->rp.width = render->width; h->rp.height = render->height; h->rp.spp = render->samples_pixel; h->rp.spl = render->samples_light;
         h->rp.shader = render->shader; h->rp.seed = render->seed;
         h->rp.bsx = render->width / 16; h->rp.bsy = render->height / 16;   // Renderer.cpp:33-34
+        h->rp.tile_stride = render->tile_stride > 1 ? render->tile_stride : 1;
+        h->rp.tile_begin = render->tile_stride > 1 ? render->tile_begin : 0;
+        h->rp.n_tiles = (kNumberOfTiles - h->rp.tile_begin + h->rp.tile_stride - 1) / h->rp.tile_stride;
         h->rp.depth_max_point = mk3(render->depth_max_point[0], render->depth_max_point[1], render->depth_max_point[2]);
         h->camera = make_camera(*camera);
         if ((rc = upload_scene(h, *scene)) != MRT_OK) { break; }
@@ -443,16 +467,17 @@ int mrt_create(const mrt_scene_desc *scene, const mrt_camera_desc *camera, const
         if ((e = h->d_bitmap.alloc(npix * sizeof(int32_t))) != cudaSuccess) { rc = cuda_fail(h, e, "bitmap"); break; }
         if ((e = h->d_accum.alloc(npix * sizeof(float4))) != cudaSuccess) { rc = cuda_fail(h, e, "accumulator"); break; }
         if ((e = h->d_counters.alloc(sizeof(DeviceCounters))) != cudaSuccess) { rc = cuda_fail(h, e, "counters"); break; }
+        if ((e = h->d_counters_saved.alloc(sizeof(DeviceCounters))) != cudaSuccess) { rc = cuda_fail(h, e, "counters"); break; }
         if ((e = cudaMemsetAsync(h->d_bitmap.p, 0, npix * sizeof(int32_t), h->stream)) != cudaSuccess) { rc = cuda_fail(h, e, "memset"); break; }
         if ((e = cudaMallocHost(reinterpret_cast<void **>(&h->h_pinned_bitmap), npix * sizeof(int32_t))) != cudaSuccess) { rc = cuda_fail(h, e, "pinned bitmap"); break; }
         h->pinned_bytes = npix * sizeof(int32_t);
         if (render->shader == MRT_SHADER_PATHTRACER) {
             const char *be = std::getenv("MRT_B200_BATCH");   // samples traced together per wavefront pass
-            // default: up to 16 samples per pass, as long as the queues (about 768 bytes per pixel and sample) stay below 32 GB
-            const double per_sample = 768.0 * static_cast<double>(render->width) * static_cast<double>(render->height);
+            // default: up to 16 samples per pass, as long as the queues (about 390 + 100 * samples_light bytes per pixel and sample) stay below 32 GB
+            const double per_sample = (390.0 + 100.0 * std::max(1, render->samples_light)) * static_cast<double>(std::max<uint32_t>(h->roots_per_sample, 1u));
             const int by_memory = static_cast<int>(std::max(1.0, std::min(16.0, 32.0e9 / std::max(per_sample, 1.0))));
             const int batch = std::max(1, std::min(be ? std::atoi(be) : by_memory, render->samples_pixel));
-            if ((e = wavefront_create(render->width, render->height, batch, &h->wavefront)) != cudaSuccess) { rc = cuda_fail(h, e, "wavefront queues"); break; }
+            if ((e = wavefront_create(h->roots_per_sample, batch, render->samples_light, &h->wavefront)) != cudaSuccess) { rc = cuda_fail(h, e, "wavefront queues"); break; }
         }
         if ((e = cudaStreamSynchronize(h->stream)) != cudaSuccess) { rc = cuda_fail(h, e, "create sync"); break; }
     } while (false);
@@ -470,10 +495,25 @@ int mrt_set_camera(mrt_handle *h, const mrt_camera_desc *camera) {
     return MRT_OK;
 }
 
+int mrt_set_pixel_stream(mrt_handle *h, const float *draws, int64_t n) {
+    if (!h || !draws || n < 1 || n > 0x7fffffffll) { return fail(h, MRT_ERR_INVALID, "bad argument"); }
+    if (h->rp.pixel_sampler != MRT_SAMPLER_STREAM) { return fail(h, MRT_ERR_INVALID, "the handle was not created with MRT_SAMPLER_STREAM"); }
+    std::lock_guard<std::mutex> lock(h->mutex);
+    API_CUDA(h, cudaSetDevice(h->device));
+    API_CUDA(h, cudaStreamSynchronize(h->stream));
+    API_CUDA(h, h->d_pixel_stream.upload(draws, static_cast<size_t>(n) * sizeof(float), h->stream));
+    API_CUDA(h, cudaStreamSynchronize(h->stream));
+    h->scene.pixel_table = h->d_pixel_stream.as<float>();
+    h->rp.pixel_stream_n = static_cast<uint32_t>(n);
+    errno = 0;
+    return MRT_OK;
+}
+
 int mrt_set_stream(mrt_handle *h, void *cuda_stream) {
     if (!h) { return MRT_ERR_INVALID; }
     std::lock_guard<std::mutex> lock(h->mutex);
     cudaStreamSynchronize(h->stream);
+    // NULL restores the handle's own stream; the legacy default stream is named by cudaStreamLegacy ((cudaStream_t)0x1)
     h->stream = cuda_stream ? static_cast<cudaStream_t>(cuda_stream) : h->own_stream;
     errno = 0;
     return MRT_OK;
@@ -527,6 +567,7 @@ cudaError_t progress_refresh(mrt_handle *h, const int32_t *d_bitmap) {
 int render_samples(mrt_handle *h, int32_t *d_bitmap, float4 *d_accum, int sample_begin, int sample_stride) {
     cudaStream_t st = h->stream;
     API_CUDA(h, cudaSetDevice(h->device));
+    if (h->rp.pixel_sampler == MRT_SAMPLER_STREAM && h->d_pixel_stream.p == nullptr) { return fail(h, MRT_ERR_INVALID, "MRT_SAMPLER_STREAM: call mrt_set_pixel_stream before rendering"); }
     h->stop.store(0);
     h->sample.store(0);
     API_CUDA(h, cudaMemsetAsync(h->d_counters.p, 0, sizeof(DeviceCounters), st));
@@ -535,16 +576,39 @@ int render_samples(mrt_handle *h, int32_t *d_bitmap, float4 *d_accum, int sample
     WavefrontTimes wt {};
     uint64_t launches = 0;
     const int spp = h->rp.spp;
+    h->stats.pass_retries = 0;
     bool stopped = false;
     if (h->rp.shader == MRT_SHADER_PATHTRACER) {
-        const int batch = wavefront_batch(h->wavefront);
-        for (int s = sample_begin, k = 0; s < spp;) {
+        // Passes of up to `batch` samples. A pass leaves its result in the per-path accumulators and only then is applied
+        // to the target, so a pass whose queues overflowed (a hit may emit up to three continuation rays and
+        // samples_light shadow rays; the reference accepts any material set and samplesLight) is repeated with half the
+        // samples, and a single sample with doubled queues, instead of failing the frame.
+        std::vector<int> todo_s, todo_n;
+        for (int s = sample_begin, k = 0; s < spp; s += sample_stride, ++k) { todo_s.push_back(s); todo_n.push_back(d_bitmap ? s + 1 : k + 1); }
+        int batch = wavefront_batch(h->wavefront);
+        DeviceCounters *dc = h->d_counters.as<DeviceCounters>();
+        for (size_t pos = 0; pos < todo_s.size();) {
             if (h->stop.load()) { stopped = true; break; }
-            int samples[kWfMaxBatch], avg_n[kWfMaxBatch], nb = 0;
-            for (; nb < batch && s < spp; s += sample_stride, ++k, ++nb) { samples[nb] = s; avg_n[nb] = d_bitmap ? s + 1 : k + 1; }
-            API_CUDA(h, wavefront_render_batch(h->wavefront, h->scene, h->camera, h->rp, h->d_inv_tile.as<int2>(), h->d_tile_base.as<uint32_t>(), h->roots_per_sample, nb, samples, avg_n,
-                                               tg, h->d_counters.as<DeviceCounters>(), &wt, &launches, st));
-            h->sample.store(samples[nb - 1] + 1);
+            const int nb = static_cast<int>(std::min<size_t>(static_cast<size_t>(batch), todo_s.size() - pos));
+            API_CUDA(h, cudaMemcpyAsync(h->d_counters_saved.p, dc, sizeof(DeviceCounters), cudaMemcpyDeviceToDevice, st));
+            API_CUDA(h, wavefront_trace_batch(h->wavefront, h->scene, h->camera, h->rp, h->d_inv_tile.as<int2>(), h->d_tile_base.as<uint32_t>(), h->roots_per_sample, nb,
+                                              todo_s.data() + pos, dc, &launches, st));
+            int overflow = 0;
+            API_CUDA(h, cudaMemcpyAsync(&overflow, &dc->overflow, sizeof(int), cudaMemcpyDeviceToHost, st));
+            API_CUDA(h, cudaStreamSynchronize(st));
+            if (overflow & 1) {   // bit 0: a ray / shadow / chain queue was full (bit 1: traversal stack, which no retry cures)
+                API_CUDA(h, cudaMemcpyAsync(dc, h->d_counters_saved.p, sizeof(DeviceCounters), cudaMemcpyDeviceToDevice, st));
+                ++h->stats.pass_retries;
+                if (nb > 1) { batch = std::max(1, nb / 2); continue; }
+                bool grown = false;
+                API_CUDA(h, wavefront_grow(h->wavefront, &grown));
+                if (!grown) { return fail(h, MRT_ERR_OVERFLOW, "ray queues overflowed at the largest size this library allocates"); }
+                continue;
+            }
+            if (overflow) { break; }   // reported below
+            API_CUDA(h, wavefront_resolve_batch(h->wavefront, h->d_tile_base.as<uint32_t>(), h->rp.n_tiles, h->roots_per_sample, h->tiles_disjoint, nb, todo_n.data() + pos, tg, &launches, st));
+            pos += static_cast<size_t>(nb);
+            h->sample.store(todo_s[pos - 1] + 1);
             API_CUDA(h, progress_refresh(h, d_bitmap));
         }
     } else {
@@ -619,6 +683,7 @@ int render_samples(mrt_handle *h, int32_t *d_bitmap, float4 *d_accum, int sample
         h->stats.rays_extend_traced = hc.extend_traced; h->stats.rays_shadow_traced = hc.shadow_traced;
         const uint64_t per_class = h->rp.shader == MRT_SHADER_PATHTRACER ? wt.extend_launches : 0u;   // 6 levels x (extend, shade, shadow) per pass
         h->stats.extend_launches = per_class; h->stats.shade_launches = per_class; h->stats.shadow_launches = per_class;
+        h->stats.queue_bytes = h->wavefront ? wavefront_bytes(h->wavefront) : 0u;
     }
     h->total_rays.store(hc.rays_primary + hc.rays_shadow + hc.rays_secondary);
     if (!stopped) { h->sample.store(spp); }

@@ -30,11 +30,7 @@ __global__ void __launch_bounds__(128) k_render_sample(SceneDev s, CameraRec cam
         const float invImgWidth = 1.0f / static_cast<float>(rp.width), invImgHeight = 1.0f / static_cast<float>(rp.height);
         const float pixelWidth = 0.5f / static_cast<float>(rp.width), pixelHeight = 0.5f / static_cast<float>(rp.height);
         const float u = static_cast<float>(x) * invImgWidth, v = static_cast<float>(y) * invImgHeight;
-        float r1 = 0.5f, r2 = 0.5f;
-        if (s.pixel_table != nullptr) {
-            r1 = __ldg(s.pixel_table + ((2u * q) & kArrayMask));
-            r2 = __ldg(s.pixel_table + ((2u * q + 1u) & kArrayMask));
-        }
+        const float r1 = pixel_draw(s, rp, 2u * q), r2 = pixel_draw(s, rp, 2u * q + 1u);
         const float deviationU = (r1 - 0.5f) * 2.0f * pixelWidth;
         const float deviationV = (r2 - 0.5f) * 2.0f * pixelHeight;
         v3 o, d;
@@ -186,7 +182,7 @@ __global__ void k_test_halton(uint32_t first, int64_t n, uint32_t base, float *o
 // ---- launchers ------------------------------------------------------------------------------------------------
 cudaError_t launch_render_sample(const SceneDev &s, const CameraRec &cam, const RenderParams &rp, const int2 *d_tile_origin,
                                  int sample, int avg_n, FrameTargets tg, DeviceCounters *dc, cudaStream_t st, ReplayArgs rep) {
-    const int patches = kNumberOfTiles * ((rp.bsx + 7) / 8) * ((rp.bsy + 3) / 4);
+    const int patches = rp.n_tiles * ((rp.bsx + 7) / 8) * ((rp.bsy + 3) / 4);
     if (patches == 0) { return cudaSuccess; }
     const int blocks = (patches + 3) / 4;
     switch (rp.shader) {

@@ -36,9 +36,10 @@ MRT_D int tile_patches_y(const RenderParams &rp) { return (rp.bsy + 3) >> 2; }
 MRT_D bool tile_pixel(const RenderParams &rp, const int2 *__restrict__ tile_origin, int patch, int lane, int sample,
                       int &x, int &y, int &pix, uint32_t &q, int *tile_out = nullptr, int *rank_out = nullptr) {
     const int ptx = tile_patches_x(rp), per_tile = ptx * tile_patches_y(rp);
-    const int k = patch / per_tile;
-    if (k >= kNumberOfTiles) { return false; }
-    const int r = patch - k * per_tile;
+    const int ksel = patch / per_tile;                        // position among the tiles this handle renders
+    if (ksel >= rp.n_tiles) { return false; }
+    const int k = rp.tile_begin + ksel * rp.tile_stride;      // position in the reference's shuffled tile walk
+    const int r = patch - ksel * per_tile;
     const int lx = (r % ptx) * 8 + (lane & 7), ly = (r / ptx) * 4 + (lane >> 3);
     if (lx >= rp.bsx || ly >= rp.bsy) { return false; }
     const int2 org = __ldg(tile_origin + k);
@@ -47,9 +48,25 @@ MRT_D bool tile_pixel(const RenderParams &rp, const int2 *__restrict__ tile_orig
     if (pix >= rp.width * rp.height) { return false; }        // the reference writes out of bounds here; this library does not
     q = (static_cast<uint32_t>(sample) * kNumberOfTiles + static_cast<uint32_t>(k)) * static_cast<uint32_t>(rp.bsx * rp.bsy) +
         static_cast<uint32_t>(ly * rp.bsx + lx);
-    if (tile_out) { *tile_out = k; }
+    if (tile_out) { *tile_out = ksel; }
     if (rank_out) { *rank_out = ly * rp.bsx + lx; }   // valid pixels of a tile are a prefix of its row-major order (pix is monotone in it)
     return true;
+}
+
+// The two jitter draws of pixel-sample q (Renderer.cpp:137-138): the pixel sampler's draws 2q and 2q + 1 of the frame, for every
+// sampler the reference has (Components/Samplers/*.cpp). The table samplers hand out table[counter++ & mask]
+// (Sampler.hpp:58-63); HaltonSeq / Stratified compute the value from the counter and return 1.0 once the counter has
+// reached their domain size (HaltonSeq.cpp:10-19, Stratified.cpp:10-19: called with sample = 0, so that is after
+// domainSize_ draws); the generators with hidden state (MersenneTwister.cpp:5-11, PCG.cpp:6-13) are served from a stream of
+// draws the host took from the sampler object itself (mrt_set_pixel_stream).
+MRT_D float pixel_draw(const SceneDev &s, const RenderParams &rp, uint32_t idx) {
+    switch (rp.pixel_sampler) {
+        case 2: case 3: case 4: return __ldg(s.pixel_table + (idx & kArrayMask));                        // Static{HaltonSeq, MersenneTwister, PCG}
+        case 5: return idx < rp.sampler_domain ? halton_sequence(idx, 2u) : 1.0f;                        // HaltonSeq
+        case 6: return idx < rp.sampler_domain ? static_cast<float>(idx) / static_cast<float>(rp.sampler_domain) : 1.0f;   // Stratified
+        case 7: return __ldg(s.pixel_table + (idx < rp.pixel_stream_n ? idx : idx % rp.pixel_stream_n)); // caller's stream
+        default: return 0.5f;                                                                            // Constant(0.5)
+    }
 }
 
 MRT_D uint32_t hash_u32(uint32_t a, uint32_t b, uint32_t c) {

@@ -99,7 +99,7 @@ struct Trav8 {
 // The indexed arrays live outside Trav8 so that its scalar fields stay in registers (with the arrays inside, the whole
 // struct sat in local memory: 9 LDL per node step in the first ncu SASS view).
 struct TravMem {
-    uint2 stack[kStack8];      // node groups still to visit
+    uint2 stack[kStack8 + 1];  // node groups still to visit; entry kStack8 only ever receives the unconditional store of a full stack
     uint2 pend[kPend];         // parked leaf groups (x = triangle base, y = pending triangle bits); per-thread callers only
 #ifdef MRT_SMEM_STACK
     uint32_t sh = 0u;          // wavefront kernels: shared-window address of this thread's column of the CTA's short stack (entry stride kShStackStride)
@@ -189,7 +189,7 @@ MRT_D bool trav8_node_core(const SceneDev &s, Trav8 &t, TravMem &tm_, uint32_t &
     {   // the rest of the group goes to the stack: an unconditional store plus a conditional bump of sp (no divergent branch)
         const bool push = (t.ngroup.y & 0xff000000u) != 0u;
         if (push && t.sp >= kStack8) { *overflow = 1; return false; }
-        stack_put(tm_, t.sp < kStack8 ? t.sp : kStack8 - 1, t.ngroup);
+        stack_put(tm_, t.sp < kStack8 ? t.sp : kStack8, t.ngroup);   // sp == kStack8 without a push: a scratch slot, never popped
         t.sp += push ? 1 : 0;
     }
     const uint32_t one = s.prmt_one;

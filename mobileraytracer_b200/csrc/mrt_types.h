@@ -83,6 +83,10 @@ struct RenderParams {
     int32_t pixel_sampler;      // MRT_SAMPLER_* resolved
     v3 depth_max_point;
     uint32_t seed;
+    int32_t tile_begin, tile_stride;   // this handle renders tiles tile_begin, tile_begin + tile_stride, ... of the shuffled tile walk (multi-GPU tile partition)
+    int32_t n_tiles;                   // how many tiles that is (kNumberOfTiles without a partition)
+    uint32_t sampler_domain;           // Sampler::domainSize_ (Sampler.cpp:14-18) of the HaltonSeq / Stratified pixel samplers
+    uint32_t pixel_stream_n;           // MRT_SAMPLER_STREAM: draws in the caller's stream (>= 1)
 };
 
 // MRT_FLAG_REPLAY_SAMPLERS (mrt_shade.cuh DrawState, mrt_render.h ReplayArgs)

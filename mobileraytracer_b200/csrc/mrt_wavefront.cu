@@ -1,15 +1,19 @@
 // Wavefront path tracer: PathTracer::shade (Components/Shaders/PathTracer.cpp:22-142) driven by Shader::rayTrace
-// (MobileRT/Shader.cpp:86-123), re-expressed as generate / extend / shade / shadow / finalize kernels over compacted
-// ray queues in HBM. Built with -fmad=false (see mrt_math.cuh).
+// (MobileRT/Shader.cpp:86-123), re-expressed as generate / extend / shade / shadow / fold / finalize / resolve kernels
+// over compacted ray queues in HBM. Built with -fmad=false (see mrt_math.cuh).
 //
 // The reference's recursion has one non-local rule: at a vertex with direct light (Ld > 0) the WHOLE indirect diffuse
 // term is dropped when the diffuse chain below it ends on an emitter (PathTracer.cpp:99-110, the bool returned up the
-// recursion). A "chain" is therefore the unit of bookkeeping: a maximal sequence of diffuse bounces. Every chain owns a
-// record with one radiance sum per depth, a bit mask of depths that saw direct light and an "ended on an emitter" flag;
-// specular / transmission rays start child chains that are folded into the parent's sum of the spawning depth.
-// After the last level the chains are finalised deepest-first, which reproduces the recursion's result exactly:
-//   not ended on emitter : total = sum over all depths
-//   ended on emitter     : total = sum over depths <= first depth with direct light (+ the emitter term if there is none)
+// recursion). A "chain" is therefore the unit of bookkeeping: a maximal sequence of diffuse bounces; specular /
+// transmission rays start child chains that are folded into the parent at the depth of the spawning vertex.
+// With j* = the first depth of the chain whose direct light was > 0, the recursion's result is
+//   not ended on an emitter : sum of the contributions of all depths
+//   ended on an emitter     : sum of the contributions of the depths <= j* (+ the emitter term when there is no j*)
+// Levels are processed in depth order, so a 32-byte accumulator per chain is enough: `pre` collects what counts in both
+// cases (depths <= j*, everything while j* is still unknown, the emitter term), `post` what only counts when the chain
+// does not end on an emitter; total = pre + (ended ? 0 : post). The first version kept one sum per depth in a 128-byte
+// record per chain: 4.2 GB of records per 16-sample pass, written by generate, updated by atomics from the shadow
+// kernel (5x its algorithmic DRAM bytes, profiles/r1_traffic_s40.csv) and read back by resolve.
 #include "mrt_wavefront.h"
 #include "mrt_shade.cuh"
 #include <cstdlib>
@@ -26,25 +30,29 @@ constexpr int kWfThreads = 128;
 #define MRT_SHADE_MIN_BLOCKS 8
 #endif
 
-struct __align__(16) Chain {
-    float sum[kLevels][3];   // [depth-1]: throughput-weighted Ld and folded child chains of that vertex
-    float emit[3];           // throughput-weighted Le when the chain ends on an emitter
-    uint32_t ldmask;         // bit (depth-1): direct light at that vertex was > 0
-    uint32_t ended_on_light;
-    int32_t parent;          // parent chain, -1 for a camera path
-    int32_t parent_depth;    // depth of the vertex that spawned this chain; root: pixel index
-    uint32_t pad[7];
+// One sector per chain. info: bits 0..2 = j* (0: no vertex had direct light yet), bit 3 = ended on an emitter,
+// bits 4..6 = depth of the parent's vertex that spawned this chain. parent: parent chain, or -1 - pixel for a camera path.
+struct __align__(16) PathAcc {
+    float pre[3];
+    uint32_t info;
+    float post[3];
+    int32_t parent;
 };
-static_assert(sizeof(Chain) == 128, "Chain must be 128 bytes");
+static_assert(sizeof(PathAcc) == 32, "PathAcc must be one 32-byte sector");
+constexpr uint32_t kAccFirstMask = 7u, kAccEnded = 8u;
+
+struct BatchInts { int32_t v[kWfMaxBatch]; };   // per sample of a pass: sample index, or sample number of the running average
 
 struct Queues {
     // ray queue (SoA of float4): r0 = o.xyz d.x | r1 = d.y d.z skip depth | r2 = T.xyz chain | r3 = q branch - -
+    // level 0 (camera rays) only has r0 and r1 = d.y d.z q pixel: T = 1, chain = slot, depth = 1, nothing to skip
     float4 *r0[2], *r1[2], *r2[2], *r3[2];
     float4 *hit;                 // t u v (kind << 28 | idx)
-    float4 *s0, *s1, *s2;        // shadow queue: o.xyz d.x | d.y d.z dist skip | c.xyz (chain | depth << 28)
-    Chain *chains;
+    float4 *s0, *s1, *s2;        // shadow queue: o.xyz d.x | d.y d.z dist skip | c.xyz (chain | depth-1 << 28 | Ld > 0 << 31)
+    uint8_t *vis;                // per shadow ray: 1 = reached the light (written by the shadow kernel, consumed by k_wf_fold)
+    PathAcc *acc;                // per chain; the root chain of camera path `slot` is chain `slot`
     uint32_t *counts;            // [0..7] ray count per level, [8] shadow count, [9] chain pool size, [10..17] chain pool size after each level,
-                                 // [20],[21] work counters, [24..32] root-chain range boundaries of the samples of a batch
+                                 // [20],[21] work counters
     uint32_t cap_rays, cap_shadow, cap_chains;
 };
 
@@ -52,33 +60,24 @@ struct WfMark { cudaEvent_t ev; int cls; };
 
 struct Wavefront {
     Queues q {};
-    int width = 0, height = 0;
+    size_t paths_per_sample = 0;      // camera paths of one sample (the pixels of the tiles this handle renders)
     int sm_count = 148;
     int batch = 1;
+    int spl = 1;
+    int factor = 2;                   // ray-queue capacity in camera paths of a full pass (wf_alloc_queues)
+    size_t bytes = 0;
     std::vector<void *> allocs;
     std::vector<WfMark> marks;        // one event after every launch; the class says what ran before it
     std::vector<cudaEvent_t> pool;
     size_t used = 0;
-    // shadow(level) and extend(level + 1) only share the scene; with MRT_B200_OVERLAP=1 they run on two streams so that
-    // each persistent kernel's CTAs move into the SM slots the other's finished CTAs leave. Measured on the bench frame:
-    // 249.4 -> 248.2 ms (the dynamic work counter already keeps the tails short), so it is off by default, which keeps
-    // the per-kernel event times free of sharing.
-    cudaStream_t side = nullptr;
-    cudaEvent_t shaded = nullptr, shadowed = nullptr;
-    bool overlap = false;
 };
 
-// A fresh chain record, written as eight full 16-byte stores: all four 32-byte sectors of the line are completely
-// overwritten, so the L2 never has to read-modify-write a partial sector (the first version left 28 pad bytes and a
-// 4-byte field in the last sector: 66 MB of DRAM reads per generate launch and half the write bandwidth, ncu).
-MRT_D void chain_init(Chain *c, int32_t parent, int32_t parent_depth) {
-    float4 *cz = reinterpret_cast<float4 *>(c);
-    const float4 z = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-#pragma unroll
-    for (int k = 0; k < 5; ++k) { cz[k] = z; }
-    cz[5] = make_float4(0.0f, 0.0f, 0.0f, __int_as_float(parent));          // emit[2], ldmask, ended_on_light, parent
-    cz[6] = make_float4(__int_as_float(parent_depth), 0.0f, 0.0f, 0.0f);    // parent_depth, pad
-    cz[7] = z;
+// A fresh accumulator, written as two full 16-byte stores: the whole sector is overwritten, so the L2 never has to
+// read-modify-write it (a record with pad bytes left unwritten cost 66 MB of DRAM reads per generate launch, ncu).
+MRT_D void acc_init(PathAcc *a, v3 pre, uint32_t info, int32_t parent) {
+    float4 *p = reinterpret_cast<float4 *>(a);
+    p[0] = make_float4(pre.x, pre.y, pre.z, __uint_as_float(info));
+    p[1] = make_float4(0.0f, 0.0f, 0.0f, __int_as_float(parent));
 }
 
 MRT_D uint32_t pack_skip(int kind, int idx) { return kind == HIT_NONE ? 0u : (static_cast<uint32_t>(kind) << 28) | (static_cast<uint32_t>(idx) & 0x0fffffffu); }
@@ -96,9 +95,11 @@ MRT_D uint32_t queue_push(uint32_t *counter) {
 }
 
 // ---- generate: Renderer::renderScene's jitter + Camera::generateRay (Renderer.cpp:130-141) ---------------------------
-__global__ void __launch_bounds__(kWfThreads) k_wf_generate(Queues Q, CameraRec cam, RenderParams rp, const float *__restrict__ pixel_table,
+__global__ void __launch_bounds__(kWfThreads) k_wf_generate(Queues Q, SceneDev s, CameraRec cam, RenderParams rp,
                                                             const int2 *__restrict__ tile_origin, const uint32_t *__restrict__ tile_base,
-                                                            uint32_t slot_base, int sample, DeviceCounters *dc) {
+                                                            uint32_t roots_per_sample, BatchInts samples, DeviceCounters *dc) {
+    const int sample = samples.v[blockIdx.y];                       // blockIdx.y: position of the sample in the pass
+    const uint32_t slot_base = blockIdx.y * roots_per_sample;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int patch = blockIdx.x * (kWfThreads / 32) + warp;
     uint32_t q = 0;
@@ -109,29 +110,23 @@ __global__ void __launch_bounds__(kWfThreads) k_wf_generate(Queues Q, CameraRec 
         const float invImgWidth = 1.0f / static_cast<float>(rp.width), invImgHeight = 1.0f / static_cast<float>(rp.height);
         const float pixelWidth = 0.5f / static_cast<float>(rp.width), pixelHeight = 0.5f / static_cast<float>(rp.height);
         const float u = static_cast<float>(x) * invImgWidth, v = static_cast<float>(y) * invImgHeight;
-        float r1 = 0.5f, r2 = 0.5f;
-        if (pixel_table != nullptr) { r1 = __ldg(pixel_table + ((2u * q) & kArrayMask)); r2 = __ldg(pixel_table + ((2u * q + 1u) & kArrayMask)); }
+        const float r1 = pixel_draw(s, rp, 2u * q), r2 = pixel_draw(s, rp, 2u * q + 1u);
         v3 o, d;
         generate_ray(cam, u, v, (r1 - 0.5f) * 2.0f * pixelWidth, (r2 - 0.5f) * 2.0f * pixelHeight, o, d);
         // deterministic slot: no atomics (64 k same-address atomics per sample made this kernel latency bound, profiles/)
         const uint32_t slot = slot_base + __ldg(tile_base + tile) + static_cast<uint32_t>(rank);
-        // the root chain of camera path `slot` is chain `slot`
-        chain_init(Q.chains + slot, -1, pix);
+        // 32 bytes per camera ray; its accumulator (chain `slot`) is initialised by the shade kernel of level 0
         Q.r0[0][slot] = make_float4(o.x, o.y, o.z, d.x);
-        Q.r1[0][slot] = make_float4(d.y, d.z, __uint_as_float(0u), __int_as_float(1));
-        Q.r2[0][slot] = make_float4(1.0f, 1.0f, 1.0f, __uint_as_float(slot));
-        Q.r3[0][slot] = make_float4(__uint_as_float(q), __uint_as_float(1u), 0.0f, 0.0f);
+        Q.r1[0][slot] = make_float4(d.y, d.z, __uint_as_float(q), __int_as_float(pix));
         rc.primary = 1u;
     }
     const uint32_t p = __reduce_add_sync(0xffffffffu, rc.primary);
     if (lane == 0 && p) { atomicAdd(&dc->rays_primary, static_cast<unsigned long long>(p)); }
 }
 
-// the chain pool starts right after the root chains
-// camera paths of batch sample i occupy root chains [counts[24 + i], counts[24 + i + 1]) = i * roots_per_sample ...
+// the chain pool starts right after the root chains: camera paths of batch sample i are chains [i, i + 1) * roots_per_sample
 __global__ void k_wf_begin_levels(Queues Q, uint32_t n_samples, uint32_t roots_per_sample) {
     Q.counts[0] = n_samples * roots_per_sample; Q.counts[9] = n_samples * roots_per_sample;
-    for (uint32_t i = 0; i <= n_samples; ++i) { Q.counts[24 + i] = i * roots_per_sample; }
 }
 
 // ---- extend / shadow: persistent traversal kernels --------------------------------------------------------------
@@ -176,16 +171,6 @@ struct __align__(16) WarpShared {
 };
 
 MRT_D uint32_t pack_hit(const HitRec &h) { return (static_cast<uint32_t>(h.kind) << 28) | (static_cast<uint32_t>(h.idx) & 0x0fffffffu); }
-
-// an unoccluded shadow sample adds its share of Ld to the chain (PathTracer.cpp:72-80)
-MRT_D void shadow_unoccluded(const Queues &Q, uint32_t i) {
-    const float4 cc = Q.s2[i];
-    const uint32_t tag = __float_as_uint(cc.w);
-    Chain *ch = Q.chains + (tag & 0x0fffffffu);
-    const uint32_t dz = (tag >> 28) & 7u;
-    atomicAdd(&ch->sum[dz][0], cc.x); atomicAdd(&ch->sum[dz][1], cc.y); atomicAdd(&ch->sum[dz][2], cc.z);
-    if (tag & 0x80000000u) { atomicOr(&ch->ldmask, 1u << dz); }
-}
 
 // The warp tests the triangles of the node items nitems[first, first + n), n <= 32. Must be called by all 32 lanes.
 // Every lane expands one node item (hit leaf slots + meta bytes) into the bit mask of its triangles within the node's
@@ -333,7 +318,7 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
                 const unsigned long long k = w.key[lane], key0 = w.key0[lane];
                 const uint32_t cur = w.cur[lane];
                 if (ANY) {
-                    if (k == key0) { shadow_unoccluded(Q, cur); }
+                    Q.vis[cur] = k == key0 ? 1 : 0;      // one byte per shadow ray; k_wf_fold adds the light (PathTracer.cpp:72-80)
                 } else {
                     HitRec h;
                     const uint32_t pre = w.pre[lane];
@@ -375,7 +360,7 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
 #endif
                     const v3 o = mk3(a.x, a.y, a.z), d = mk3(a.w, c.x, c.y);
                     int sk, si;
-                    unpack_skip(__float_as_uint(ANY ? c.w : c.z), sk, si);
+                    unpack_skip(ANY ? __float_as_uint(c.w) : (level == 0 ? 0u : __float_as_uint(c.z)), sk, si);
                     h.t = ANY ? c.z : kRayLengthMax; h.kind = HIT_NONE; h.idx = -1; h.u = 0.0f; h.v = 0.0f;
                     bool occluded = false;
                     if (ANY) {
@@ -384,6 +369,7 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
                         trace_ref_bvh<0>(s, o, d, false, sk, si, h, &overflow);
                         trace_ref_bvh<1>(s, o, d, false, sk, si, h, &overflow);
                     }
+                    if (ANY && occluded) { Q.vis[cur] = 0; }
                     if (!occluded) {
                         if (s.n_bvh_prims > 0 && triangles_root_hit(s, o, d)) {
                             trav8_init(t, o, d, sk == HIT_TRIANGLE ? si : -1, h.t);
@@ -394,7 +380,7 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
                             w.cur[lane] = cur; w.pre[lane] = pack_hit(h);
                             got = true; node_work = true;
                         } else if (ANY) {
-                            shadow_unoccluded(Q, cur);
+                            Q.vis[cur] = 1;
                         } else {
                             if (s.n_bvh_prims > s.n_triangles) { trace_lights_linear(s, o, d, h); }
                             Q.hit[cur] = make_float4(h.t, h.u, h.v, __uint_as_float(pack_hit(h)));
@@ -460,7 +446,7 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
     }
 #undef MRT_FLUSH_ITEMS
 #undef MRT_REFRESH_BEST
-    if (overflow) { dc->overflow = 1; }
+    if (overflow) { atomicOr(&dc->overflow, 2); }   // traversal stack
 }
 
 __global__ void __launch_bounds__(kWfThreads, MRT_TRAV_MIN_BLOCKS) k_wf_extend(SceneDev s, Queues Q, int level, DeviceCounters *dc) { wf_traverse<false>(s, Q, level, dc); }
@@ -479,39 +465,86 @@ MRT_D v3 cosine_sample_hemisphere(v3 normal, float uniformRandom1, float uniform
 }
 
 // ---- shade: PathTracer::shade for every hit of the level; emits shadow rays and the next level's rays --------------
+// Where a draw of the reference's tables comes from (Shader.cpp:188-233, Sampler.hpp:58-63, PathTracer.cpp:91): the
+// reference hands out table[counter++] in execution order, which no parallel schedule can replay for a path tracer
+// (SURVEY H2), so every (pixel-sample q, vertex `branch`, ordinal, stream) reads its own decorrelated slot of the SAME
+// tables. The ordinals are fixed per vertex, independent of control flow, so that all table loads of a vertex can be
+// issued before the hit record has arrived (the shade kernel is latency bound: profiles/r1_shade_s40).
+MRT_D uint32_t pt_slot(uint32_t q, uint32_t e, uint32_t stream, uint32_t seed) { return hash_u32(q, e, stream ^ seed) & kArrayMask; }
+
+template <bool L0>
 __global__ void __launch_bounds__(kWfThreads, MRT_SHADE_MIN_BLOCKS) k_wf_shade(SceneDev s, RenderParams rp, Queues Q, int level, DeviceCounters *dc) {
     const int b = level & 1, nb = b ^ 1;
     const uint32_t n = min(Q.counts[level], Q.cap_rays);
+    const uint32_t stride = gridDim.x * blockDim.x;
     RayCounters rc = {0u, 0u, 0u};
     int overflow = 0;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        // hit and ray records are independent loads: issue all five before the first use (most rays hit something)
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+        // the records of this thread's next iteration start their trip from HBM to L2 now
+        if (i + stride < n) {
+            asm volatile("prefetch.global.L2 [%0];" :: "l"(Q.hit + i + stride));
+            asm volatile("prefetch.global.L2 [%0];" :: "l"(Q.r0[b] + i + stride));
+            asm volatile("prefetch.global.L2 [%0];" :: "l"(Q.r1[b] + i + stride));
+            if (!L0) {
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(Q.r2[b] + i + stride));
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(Q.r3[b] + i + stride));
+            }
+        }
+        // hit and ray records are independent loads: issue all of them before the first use
         const float4 hq = Q.hit[i];
-        const float4 a = Q.r0[b][i], c1 = Q.r1[b][i], c2 = Q.r2[b][i], c3 = Q.r3[b][i];
+        const float4 a = Q.r0[b][i], c1 = Q.r1[b][i];
+        float4 c2 = make_float4(1.0f, 1.0f, 1.0f, 0.0f), c3 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        if (!L0) { c2 = Q.r2[b][i]; c3 = Q.r3[b][i]; }
+        const uint32_t q = __float_as_uint(L0 ? c1.z : c3.x), branch = L0 ? 1u : __float_as_uint(c3.y);
+        const int depth = L0 ? 1 : __float_as_int(c1.w);
+        const uint32_t chain = L0 ? i : __float_as_uint(c2.w);
+        // the vertex's draws: light sample 0 (index, two position coordinates), russian roulette, hemisphere
+        const uint32_t eb = branch << 6;
+        const float r_li = __ldg(s.shader_table + pt_slot(q, eb, DS_LIGHT_INDEX, rp.seed));
+        const float r_p0 = __ldg(s.static_halton + pt_slot(q, eb, DS_LIGHT_POS, rp.seed));
+        const float r_p1 = __ldg(s.static_halton + pt_slot(q, eb + 1u, DS_LIGHT_POS, rp.seed));
+        const float r_rr = __ldg(s.static_halton + pt_slot(q, eb, DS_RR, rp.seed));
+        const float r_h0 = __ldg(s.shader_table + pt_slot(q, eb, DS_HEMI, rp.seed));
+        const float r_h1 = __ldg(s.shader_table + pt_slot(q, eb + 1u, DS_HEMI, rp.seed));
         const uint32_t packed = __float_as_uint(hq.w);
         HitRec h;
         h.t = hq.x; h.u = hq.y; h.v = hq.z; h.kind = static_cast<int>(packed >> 28); h.idx = static_cast<int>(packed & 0x0fffffffu);
-        if (h.kind == HIT_NONE) { continue; }                      // Shader.cpp:122: no intersection, rgb stays 0
-        const v3 o = mk3(a.x, a.y, a.z), d = mk3(a.w, c1.x, c1.y), T = mk3(c2.x, c2.y, c2.z);
-        const int depth = __float_as_int(c1.w);
-        const uint32_t chain = __float_as_uint(c2.w);
-        const uint32_t q = __float_as_uint(c3.x), branch = __float_as_uint(c3.y);
-        Surface sf;
-        resolve_surface(s, o, d, h, sf);
-        Chain *ch = Q.chains + chain;
-        if (has_positive(sf.Le)) {                                  // PathTracer.cpp:28-33: stop on a light source
-            const v3 e = T * sf.Le;
-            ch->emit[0] = e.x; ch->emit[1] = e.y; ch->emit[2] = e.z;
-            ch->ended_on_light = 1u;
+        const int32_t root_parent = L0 ? -1 - __float_as_int(c1.w) : 0;   // camera path: -1 - pixel
+        if (h.kind == HIT_NONE) {                                   // Shader.cpp:122: no intersection, rgb stays 0
+            if (L0) { acc_init(Q.acc + i, mk3(0.0f, 0.0f, 0.0f), 0u, root_parent); }
             continue;
         }
-        DrawState ds = {q, branch * 16u, rp.seed};
+        const v3 o = mk3(a.x, a.y, a.z), d = mk3(a.w, c1.x, c1.y), T = mk3(c2.x, c2.y, c2.z);
+        Surface sf;
+        resolve_surface(s, o, d, h, sf);
+        PathAcc *ch = Q.acc + chain;
+        if (has_positive(sf.Le)) {                                  // PathTracer.cpp:28-33: stop on a light source
+            const v3 e = T * sf.Le;
+            if (L0) { acc_init(ch, e, kAccEnded, root_parent); }
+            else {
+                // the emitter term only counts while no vertex of the chain had direct light (PathTracer.cpp:107-110)
+                const uint32_t info = ch->info;
+                if ((info & kAccFirstMask) == 0u) { ch->pre[0] += e.x; ch->pre[1] += e.y; ch->pre[2] += e.z; }
+                ch->info = info | kAccEnded;
+            }
+            continue;
+        }
+        if (L0) { acc_init(ch, mk3(0.0f, 0.0f, 0.0f), 0u, root_parent); }
         const bool diffuse = has_positive(sf.Kd);
         if (diffuse && s.n_lights > 0) {                            // PathTracer.cpp:55-87: direct light, one shadow ray per light sample
             for (int k = 0; k < rp.spl; ++k) {
-                const uint32_t chosen = light_index(s, ds);
+                const uint32_t ku = static_cast<uint32_t>(k);
+                // Shader::getLightIndex (Shader.cpp:223-233)
+                const float rl = k == 0 ? r_li : __ldg(s.shader_table + pt_slot(q, eb + ku, DS_LIGHT_INDEX, rp.seed));
+                const uint32_t chosen = static_cast<uint32_t>(floorf(rl * static_cast<float>(static_cast<uint32_t>(s.n_lights)) * 0.99999f));
                 const LightRec &l = s.lights[chosen];
-                const v3 lightPosition = light_position(s, l, ds, chosen);
+                v3 lightPosition = mk3(l.A[0], l.A[1], l.A[2]);        // PointLight::getPosition (PointLight.cpp:16-18)
+                if (l.kind != 0) {                                  // AreaLight::getPosition (AreaLight.cpp:17-26)
+                    float r = k == 0 ? r_p0 : __ldg(s.static_halton + pt_slot(q, eb + 2u * ku, DS_LIGHT_POS, rp.seed));
+                    float g = k == 0 ? r_p1 : __ldg(s.static_halton + pt_slot(q, eb + 2u * ku + 1u, DS_LIGHT_POS, rp.seed));
+                    if (r + g >= 1.0f) { r = 1.0f - r; g = 1.0f - g; }
+                    lightPosition = (lightPosition + r * mk3(l.AB[0], l.AB[1], l.AB[2])) + g * mk3(l.AC[0], l.AC[1], l.AC[2]);
+                }
                 v3 vectorToLight = lightPosition - sf.point;
                 const float distanceToLight = length(vectorToLight);
                 vectorToLight = normalize(vectorToLight);
@@ -533,11 +566,9 @@ __global__ void __launch_bounds__(kWfThreads, MRT_SHADE_MIN_BLOCKS) k_wf_shade(S
         }
         const bool traceable = depth + 1 <= kRayDepthMax;           // deeper rays are constructed (counted) but add nothing
         if (diffuse) {                                              // PathTracer.cpp:89-111: indirect diffuse with russian roulette
-            bool go = depth <= kRayDepthMin;
-            if (!go) { go = draw(s.static_halton, ds, DS_RR) > 0.5f; }
+            const bool go = depth <= kRayDepthMin || r_rr > 0.5f;
             if (go) {
-                const float r1 = draw(s.shader_table, ds, DS_HEMI), r2 = draw(s.shader_table, ds, DS_HEMI);
-                const v3 nd = cosine_sample_hemisphere(sf.normal, r1, r2);
+                const v3 nd = cosine_sample_hemisphere(sf.normal, r_h0, r_h1);
                 ++rc.secondary;
                 if (traceable) {
                     v3 Tn = T * sf.Kd;
@@ -561,8 +592,9 @@ __global__ void __launch_bounds__(kWfThreads, MRT_SHADE_MIN_BLOCKS) k_wf_shade(S
             const v3 nd = kind == 0 ? reflect(d, sf.normal) : refract(d, sf.normal, 1.0f / sf.ior);
             const uint32_t cslot = queue_push(&Q.counts[9]);
             const uint32_t slot = queue_push(&Q.counts[level + 1]);
+            // the accumulator is initialised whenever the pool slot exists, so that finalize never reads a stale record
+            if (cslot < Q.cap_chains) { acc_init(Q.acc + cslot, mk3(0.0f, 0.0f, 0.0f), static_cast<uint32_t>(depth) << 4, static_cast<int32_t>(chain)); }
             if (cslot < Q.cap_chains && slot < Q.cap_rays) {
-                chain_init(Q.chains + cslot, static_cast<int32_t>(chain), depth);
                 const v3 Tn = T * K;
                 Q.r0[nb][slot] = make_float4(sf.point.x, sf.point.y, sf.point.z, nd.x);
                 Q.r1[nb][slot] = make_float4(nd.y, nd.z, __uint_as_float(pack_skip(sf.skipKind, sf.skipIdx)), __int_as_float(depth + 1));
@@ -576,76 +608,113 @@ __global__ void __launch_bounds__(kWfThreads, MRT_SHADE_MIN_BLOCKS) k_wf_shade(S
         if (sh) { atomicAdd(&dc->rays_shadow, static_cast<unsigned long long>(sh)); }
         if (se) { atomicAdd(&dc->rays_secondary, static_cast<unsigned long long>(se)); }
     }
-    if (overflow) { dc->overflow = 1; }
+    if (overflow) { atomicOr(&dc->overflow, 1); }   // a queue was full: the frame driver repeats the pass with fewer samples
 }
 
-// bookkeeping after shade(level) (main stream) and after shadow(level) (side stream); the two touch disjoint words
+// bookkeeping after shade(level) and after shadow(level)
 __global__ void k_wf_after_shade(Queues Q, int level, DeviceCounters *dc) {
     dc->extend_traced += min(Q.counts[level], Q.cap_rays);
     Q.counts[kCounterExtend] = 0u;            // work counter of the persistent extend kernel
     Q.counts[10 + level] = min(Q.counts[9], Q.cap_chains);   // chain pool size after this level
 }
-__global__ void k_wf_after_shadow(Queues Q, DeviceCounters *dc) {
+
+// ---- fold: the light of every unoccluded shadow ray goes into its chain (PathTracer.cpp:72-82) ---------------------
+// A streaming pass over the shadow queue in queue order (the shade kernel filled it in roughly chain order, so the
+// accumulator sectors are touched nearly sequentially). The shadow kernel used to do this itself with three float atomics
+// and an atomicOr per unoccluded ray at the moment the ray retired, i.e. in random order. All rays of one chain in one
+// level belong to the same depth, so "no j* yet, or j* == this depth" decides pre / post without ordering between them.
+__global__ void k_wf_fold(Queues Q) {
+    const uint32_t n = min(Q.counts[8], Q.cap_shadow);
+    for (uint32_t j = blockIdx.x * blockDim.x + threadIdx.x; j < n; j += gridDim.x * blockDim.x) {
+        if (Q.vis[j] == 0) { continue; }
+        const float4 cc = Q.s2[j];
+        const uint32_t tag = __float_as_uint(cc.w);
+        PathAcc *a = Q.acc + (tag & 0x0fffffffu);
+        const uint32_t depth = ((tag >> 28) & 7u) + 1u;
+        const uint32_t first = a->info & kAccFirstMask;
+        float *dst = (first == 0u || first == depth) ? a->pre : a->post;
+        if (cc.x != 0.0f) { atomicAdd(dst + 0, cc.x); }
+        if (cc.y != 0.0f) { atomicAdd(dst + 1, cc.y); }
+        if (cc.z != 0.0f) { atomicAdd(dst + 2, cc.z); }
+        if ((tag & 0x80000000u) && first == 0u) { atomicOr(&a->info, depth); }
+    }
+}
+__global__ void k_wf_after_fold(Queues Q, DeviceCounters *dc) {
     dc->shadow_traced += min(Q.counts[8], Q.cap_shadow);
     Q.counts[kCounterShadow] = 0u;
     Q.counts[8] = 0u;                         // shadow queue consumed
 }
 
-// The whole 128-byte record comes in as eight independent 16-byte loads (one dependent scalar load after the other made
-// the resolve / finalize kernels latency bound, profiles/r1_resolve_s28_*), then the reference's rule is applied.
-struct ChainRegs { float4 v[8]; };
-MRT_D ChainRegs chain_load(const Chain *ch) {
-    ChainRegs r;
-    const float4 *p = reinterpret_cast<const float4 *>(ch);
-#pragma unroll
-    for (int k = 0; k < 8; ++k) { r.v[k] = p[k]; }
-    return r;
-}
-MRT_D v3 chain_total(const ChainRegs &r, int32_t &parent, int32_t &parent_depth) {
-    // layout of Chain: floats 0..17 sum[6][3], 18..20 emit, 21 ldmask, 22 ended_on_light, 23 parent, 24 parent_depth
-    const float f[28] = {r.v[0].x, r.v[0].y, r.v[0].z, r.v[0].w, r.v[1].x, r.v[1].y, r.v[1].z, r.v[1].w, r.v[2].x, r.v[2].y, r.v[2].z, r.v[2].w,
-                         r.v[3].x, r.v[3].y, r.v[3].z, r.v[3].w, r.v[4].x, r.v[4].y, r.v[4].z, r.v[4].w, r.v[5].x, r.v[5].y, r.v[5].z, r.v[5].w,
-                         r.v[6].x, r.v[6].y, r.v[6].z, r.v[6].w};
-    const uint32_t ldmask = __float_as_uint(f[21]), ended = __float_as_uint(f[22]);
-    parent = __float_as_int(f[23]); parent_depth = __float_as_int(f[24]);
-    int last = kLevels - 1;
-    bool with_emit = true;
-    if (ended && ldmask) { last = __ffs(ldmask) - 1; with_emit = false; }
-    v3 t = mk3(0.0f, 0.0f, 0.0f);
-#pragma unroll
-    for (int k = 0; k < kLevels; ++k) {
-        if (k <= last) { t = t + mk3(f[3 * k], f[3 * k + 1], f[3 * k + 2]); }
-    }
-    if (with_emit) { t = t + mk3(f[18], f[19], f[20]); }
+MRT_D v3 acc_total(const float4 p0, const float4 p1) {
+    v3 t = mk3(p0.x, p0.y, p0.z);
+    if (!(__float_as_uint(p0.w) & kAccEnded)) { t = t + mk3(p1.x, p1.y, p1.z); }
     return t;
 }
 
-// child chains created while shading `level` (pool range [counts[10+level-1], counts[10+level])) fold into their parents
+// child chains created while shading `level` (pool range [counts[10+level-1], counts[10+level])) fold into their parents:
+// a child spawned at depth pd counts like the parent's own light of that depth (see the header comment)
 __global__ void k_wf_finalize_level(Queues Q, int level) {
-    const uint32_t begin = level == 0 ? Q.counts[0] : Q.counts[10 + level - 1], end = Q.counts[10 + level];
+    const uint32_t begin = min(level == 0 ? Q.counts[0] : Q.counts[10 + level - 1], Q.cap_chains), end = min(Q.counts[10 + level], Q.cap_chains);
     for (uint32_t i = begin + blockIdx.x * blockDim.x + threadIdx.x; i < end; i += gridDim.x * blockDim.x) {
-        int32_t parent, parent_depth;
-        const v3 t = chain_total(chain_load(Q.chains + i), parent, parent_depth);
-        Chain *p = Q.chains + parent;
-        const int dz = parent_depth - 1;
-        if (t.x != 0.0f) { atomicAdd(&p->sum[dz][0], t.x); }
-        if (t.y != 0.0f) { atomicAdd(&p->sum[dz][1], t.y); }
-        if (t.z != 0.0f) { atomicAdd(&p->sum[dz][2], t.z); }
+        const float4 *cp = reinterpret_cast<const float4 *>(Q.acc + i);
+        const float4 p0 = cp[0], p1 = cp[1];
+        const v3 t = acc_total(p0, p1);
+        const int32_t parent = __float_as_int(p1.w);
+        const uint32_t pd = (__float_as_uint(p0.w) >> 4) & 7u;
+        if (parent < 0 || static_cast<uint32_t>(parent) >= Q.cap_chains || pd == 0u) { continue; }
+        PathAcc *p = Q.acc + parent;
+        const uint32_t first = p->info & kAccFirstMask;
+        float *dst = (first == 0u || pd <= first) ? p->pre : p->post;
+        if (t.x != 0.0f) { atomicAdd(dst + 0, t.x); }
+        if (t.y != 0.0f) { atomicAdd(dst + 1, t.y); }
+        if (t.z != 0.0f) { atomicAdd(dst + 2, t.z); }
     }
 }
 
-// camera paths -> pixels (Renderer.cpp:149-157)
-__global__ void k_wf_resolve_roots(Queues Q, int batch_index, int avg_n, FrameTargets tg) {
-    const uint32_t begin = min(Q.counts[24 + batch_index], Q.cap_rays), end = min(Q.counts[24 + batch_index + 1], Q.cap_rays);
-    for (uint32_t i = begin + blockIdx.x * blockDim.x + threadIdx.x; i < end; i += gridDim.x * blockDim.x) {
-        int32_t parent, pix;
-        const v3 rgb = chain_total(chain_load(Q.chains + i), parent, pix);
-        if (tg.bitmap != nullptr) { tg.bitmap[pix] = incremental_avg(rgb, tg.bitmap[pix], avg_n); }
-        if (tg.accum != nullptr) {
-            float4 a = tg.accum[pix];
-            a.x += static_cast<float>(f2u_x86(rgb.x * 255.0f)); a.y += static_cast<float>(f2u_x86(rgb.y * 255.0f));
-            a.z += static_cast<float>(f2u_x86(rgb.z * 255.0f)); a.w += 1.0f;
-            tg.accum[pix] = a;
+// camera paths -> pixels (Renderer.cpp:149-157). One thread owns one path slot of the tile walk and applies the batch's
+// samples in order, so the 8-bit running average stays exact while the pixel is read and written once per pass.
+// Requires that no two slots of a sample map to the same pixel (tiles_disjoint, mrt_api.cu).
+__global__ void k_wf_resolve(Queues Q, uint32_t roots_per_sample, int n_samples, BatchInts avg_n, FrameTargets tg) {
+    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= roots_per_sample) { return; }
+    const int32_t pix = -1 - Q.acc[r].parent;
+    int32_t bm = tg.bitmap != nullptr ? tg.bitmap[pix] : 0;
+    float4 ac = tg.accum != nullptr ? tg.accum[pix] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+#pragma unroll 4
+    for (int b = 0; b < n_samples; ++b) {
+        const float4 *cp = reinterpret_cast<const float4 *>(Q.acc + static_cast<size_t>(b) * roots_per_sample + r);
+        const v3 rgb = acc_total(cp[0], cp[1]);
+        bm = incremental_avg(rgb, bm, avg_n.v[b]);
+        ac.x += static_cast<float>(f2u_x86(rgb.x * 255.0f)); ac.y += static_cast<float>(f2u_x86(rgb.y * 255.0f));
+        ac.z += static_cast<float>(f2u_x86(rgb.z * 255.0f)); ac.w += 1.0f;
+    }
+    if (tg.bitmap != nullptr) { tg.bitmap[pix] = bm; }
+    if (tg.accum != nullptr) { tg.accum[pix] = ac; }
+}
+
+// Image sizes that are not multiples of 16 make the reference's tiles wrap and overlap (Renderer.cpp:125-133), so several
+// path slots of one sample can hit the same pixel; the reference applies them one after the other in tile order. One CTA
+// walks the samples and tiles in that order (slots of one tile never share a pixel). Slow, and only used for such sizes;
+// both front-ends round the size to a multiple of 16 first.
+__global__ void __launch_bounds__(1024) k_wf_resolve_serial(Queues Q, const uint32_t *__restrict__ tile_base, int n_tiles, uint32_t roots_per_sample,
+                                                            int n_samples, BatchInts avg_n, FrameTargets tg) {
+    for (int b = 0; b < n_samples; ++b) {
+        for (int k = 0; k < n_tiles; ++k) {
+            const uint32_t lo = tile_base[k], hi = tile_base[k + 1];
+            for (uint32_t r = lo + threadIdx.x; r < hi; r += blockDim.x) {
+                const float4 *cp = reinterpret_cast<const float4 *>(Q.acc + static_cast<size_t>(b) * roots_per_sample + r);
+                const float4 p0 = cp[0], p1 = cp[1];
+                const v3 rgb = acc_total(p0, p1);
+                const int32_t pix = -1 - __float_as_int(p1.w);
+                if (tg.bitmap != nullptr) { tg.bitmap[pix] = incremental_avg(rgb, tg.bitmap[pix], avg_n.v[b]); }
+                if (tg.accum != nullptr) {
+                    float4 ac = tg.accum[pix];
+                    ac.x += static_cast<float>(f2u_x86(rgb.x * 255.0f)); ac.y += static_cast<float>(f2u_x86(rgb.y * 255.0f));
+                    ac.z += static_cast<float>(f2u_x86(rgb.z * 255.0f)); ac.w += 1.0f;
+                    tg.accum[pix] = ac;
+                }
+            }
+            __syncthreads();
         }
     }
 }
@@ -661,56 +730,73 @@ template <typename T> cudaError_t wf_alloc(Wavefront *w, T **p, size_t count) {
 enum WfClass { WF_OTHER = 0, WF_EXTEND = 1, WF_SHADE = 2, WF_SHADOW = 3 };
 }  // namespace
 
-typedef Wavefront WavefrontHost;
-static WavefrontHost *host_of(Wavefront *w) { return w; }
-
 #define WF_TRY(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { return e_; } } while (0)
 
 int wavefront_batch(const Wavefront *w) { return w->batch; }
 uint64_t wavefront_capacity(const Wavefront *w) { return w->q.cap_rays < w->q.cap_shadow ? w->q.cap_rays : w->q.cap_shadow; }
+size_t wavefront_bytes(const Wavefront *w) { return w->bytes; }
 
-cudaError_t wavefront_create(int width, int height, int batch, Wavefront **out) {
-    Wavefront *w = new Wavefront;
-    *out = w;
-    w->width = width; w->height = height;
-    w->batch = batch < 1 ? 1 : (batch > kWfMaxBatch ? kWfMaxBatch : batch);
-    WavefrontHost *hst = w;
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&hst->sm_count, cudaDevAttrMultiProcessorCount, dev);
-    const size_t P = static_cast<size_t>(width) * height * static_cast<size_t>(w->batch);
+// Queue capacities for `paths` camera paths per pass. A hit can emit three continuation rays (diffuse, specular,
+// transmission) and samples_light shadow rays, so no fixed factor is safe for every material set: the frame driver
+// (mrt_api.cu) retries a pass that overflowed with half the samples and, for a single sample, with grown queues.
+static cudaError_t wf_alloc_queues(Wavefront *w, size_t paths, int factor) {
     Queues &q = w->q;
-    q.cap_rays = static_cast<uint32_t>(std::min<size_t>(2 * P + 1024, 0x0ffffff0u));
-    q.cap_shadow = q.cap_rays;
-    q.cap_chains = static_cast<uint32_t>(std::min<size_t>(3 * P + 1024, 0x0ffffff0u));
+    const size_t lim = 0x0ffffff0u;
+    const size_t spl = static_cast<size_t>(w->spl < 1 ? 1 : w->spl);
+    q.cap_rays = static_cast<uint32_t>(std::min<size_t>(static_cast<size_t>(factor) * paths + 1024, lim));
+    q.cap_shadow = static_cast<uint32_t>(std::min<size_t>(static_cast<size_t>(q.cap_rays) * spl, lim));
+    q.cap_chains = static_cast<uint32_t>(std::min<size_t>((static_cast<size_t>(factor) + 1) * paths + 1024, lim));
+    w->bytes = 0;
     for (int b = 0; b < 2; ++b) {
         WF_TRY(wf_alloc(w, &q.r0[b], q.cap_rays)); WF_TRY(wf_alloc(w, &q.r1[b], q.cap_rays));
         WF_TRY(wf_alloc(w, &q.r2[b], q.cap_rays)); WF_TRY(wf_alloc(w, &q.r3[b], q.cap_rays));
     }
     WF_TRY(wf_alloc(w, &q.hit, q.cap_rays));
     WF_TRY(wf_alloc(w, &q.s0, q.cap_shadow)); WF_TRY(wf_alloc(w, &q.s1, q.cap_shadow)); WF_TRY(wf_alloc(w, &q.s2, q.cap_shadow));
-    WF_TRY(wf_alloc(w, &q.chains, q.cap_chains));
+    WF_TRY(wf_alloc(w, &q.vis, static_cast<size_t>(q.cap_shadow) + 64));
+    WF_TRY(wf_alloc(w, &q.acc, q.cap_chains));
     WF_TRY(wf_alloc(w, &q.counts, kWfCounts));
-    const char *ov = std::getenv("MRT_B200_OVERLAP");
-    w->overlap = ov && std::atoi(ov) != 0;
-    WF_TRY(cudaStreamCreateWithFlags(&w->side, cudaStreamNonBlocking));
-    WF_TRY(cudaEventCreateWithFlags(&w->shaded, cudaEventDisableTiming));
-    WF_TRY(cudaEventCreateWithFlags(&w->shadowed, cudaEventDisableTiming));
+    w->bytes = static_cast<size_t>(q.cap_rays) * (8 * 16 + 16) + static_cast<size_t>(q.cap_shadow) * (3 * 16 + 1) + static_cast<size_t>(q.cap_chains) * sizeof(PathAcc);
+    w->factor = factor;
     return cudaSuccess;
+}
+static void wf_free_queues(Wavefront *w) {
+    for (void *p : w->allocs) { cudaFree(p); }
+    w->allocs.clear();
+}
+
+cudaError_t wavefront_create(size_t paths_per_sample, int batch, int spl, Wavefront **out) {
+    Wavefront *w = new Wavefront;
+    *out = w;
+    w->paths_per_sample = paths_per_sample; w->spl = spl;
+    w->batch = batch < 1 ? 1 : (batch > kWfMaxBatch ? kWfMaxBatch : batch);
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&w->sm_count, cudaDevAttrMultiProcessorCount, dev);
+    return wf_alloc_queues(w, paths_per_sample * static_cast<size_t>(w->batch), 2);
+}
+
+// doubles the queues (after a single-sample pass overflowed); false when the limit is reached
+cudaError_t wavefront_grow(Wavefront *w, bool *grown) {
+    *grown = false;
+    const size_t paths = w->paths_per_sample * static_cast<size_t>(w->batch);
+    const int factor = w->factor * 2;
+    const double need = static_cast<double>(w->bytes) * 2.0;
+    if (w->q.cap_rays >= 0x0ffffff0u || need > 64.0e9) { return cudaSuccess; }
+    wf_free_queues(w);
+    cudaError_t e = wf_alloc_queues(w, paths, factor);
+    if (e == cudaSuccess) { *grown = true; }
+    return e;
 }
 
 void wavefront_destroy(Wavefront *w) {
     if (!w) { return; }
-    WavefrontHost *hst = host_of(w);
-    for (cudaEvent_t e : hst->pool) { cudaEventDestroy(e); }
-    if (w->shaded) { cudaEventDestroy(w->shaded); }
-    if (w->shadowed) { cudaEventDestroy(w->shadowed); }
-    if (w->side) { cudaStreamDestroy(w->side); }
-    for (void *p : w->allocs) { cudaFree(p); }
+    for (cudaEvent_t e : w->pool) { cudaEventDestroy(e); }
+    wf_free_queues(w);
     delete w;
 }
 
-static cudaError_t wf_mark(WavefrontHost *hst, int cls, cudaStream_t st) {
+static cudaError_t wf_mark(Wavefront *hst, int cls, cudaStream_t st) {
     if (hst->used == hst->pool.size()) {
         if (hst->pool.size() >= 16384) { return cudaSuccess; }   // stop timing very long frames, keep rendering
         cudaEvent_t e;
@@ -724,31 +810,28 @@ static cudaError_t wf_mark(WavefrontHost *hst, int cls, cudaStream_t st) {
 
 // to be called after the stream has been synchronised: adds the device time of every launch since the last call
 cudaError_t wavefront_collect_times(Wavefront *w, WavefrontTimes *t) {
-    WavefrontHost *hst = host_of(w);
-    for (size_t i = 1; i < hst->marks.size(); ++i) {
-        if (hst->marks[i].cls < 0) { continue; }   // a "begin" mark: nothing ran between it and its predecessor
+    for (size_t i = 1; i < w->marks.size(); ++i) {
+        if (w->marks[i].cls < 0) { continue; }   // a "begin" mark: nothing ran between it and its predecessor
         float ms = 0.0f;
-        WF_TRY(cudaEventElapsedTime(&ms, hst->marks[i - 1].ev, hst->marks[i].ev));
-        switch (hst->marks[i].cls) {
+        WF_TRY(cudaEventElapsedTime(&ms, w->marks[i - 1].ev, w->marks[i].ev));
+        switch (w->marks[i].cls) {
             case WF_EXTEND: t->extend_ms += ms; t->extend_launches += 1; break;
             case WF_SHADE: t->shade_ms += ms; break;
             case WF_SHADOW: t->shadow_ms += ms; break;
             default: t->other_ms += ms; break;
         }
     }
-    hst->marks.clear();
-    hst->used = 0;
+    w->marks.clear();
+    w->used = 0;
     return cudaSuccess;
 }
 
-cudaError_t wavefront_render_batch(Wavefront *w, const SceneDev &s, const CameraRec &cam, const RenderParams &rp, const int2 *d_tile_origin,
-                                   const uint32_t *d_tile_base, uint32_t roots_per_sample, int n_samples, const int *samples, const int *avg_n, FrameTargets tg, DeviceCounters *dc,
-                                   WavefrontTimes *times, uint64_t *launches, cudaStream_t st) {
-    (void)times;
-    WavefrontHost *hst = host_of(w);
+cudaError_t wavefront_trace_batch(Wavefront *w, const SceneDev &s, const CameraRec &cam, const RenderParams &rp, const int2 *d_tile_origin,
+                                  const uint32_t *d_tile_base, uint32_t roots_per_sample, int n_samples, const int *samples, DeviceCounters *dc,
+                                  uint64_t *launches, cudaStream_t st) {
     Queues &Q = w->q;
-    if (n_samples < 1 || n_samples > hst->batch) { return cudaErrorInvalidValue; }
-    const int grid = hst->sm_count * MRT_TRAV_MIN_BLOCKS;
+    if (n_samples < 1 || n_samples > w->batch) { return cudaErrorInvalidValue; }
+    const int grid = w->sm_count * MRT_TRAV_MIN_BLOCKS;
 #if defined(MRT_SMEM_STACK) && MRT_SMEM_STACK > 3
     {   // above 3 entries the short stack needs a larger shared-memory carve-out than the default build's 164 KB to hold MRT_TRAV_MIN_BLOCKS CTAs per SM
         static bool carved = false;
@@ -759,46 +842,51 @@ cudaError_t wavefront_render_batch(Wavefront *w, const SceneDev &s, const Camera
         }
     }
 #endif
-    WF_TRY(wf_mark(hst, -1, st));
+    WF_TRY(wf_mark(w, -1, st));
     WF_TRY(cudaMemsetAsync(Q.counts, 0, kWfCounts * sizeof(uint32_t), st));
-    const int patches = kNumberOfTiles * ((rp.bsx + 7) / 8) * ((rp.bsy + 3) / 4);
+    const int patches = rp.n_tiles * ((rp.bsx + 7) / 8) * ((rp.bsy + 3) / 4);
     if (patches == 0) { return cudaSuccess; }
     if (static_cast<unsigned long long>(roots_per_sample) * static_cast<unsigned long long>(n_samples) > Q.cap_rays) { return cudaErrorInvalidValue; }
-    for (int i = 0; i < n_samples; ++i) {
-        k_wf_generate<<<(patches + kWfThreads / 32 - 1) / (kWfThreads / 32), kWfThreads, 0, st>>>(Q, cam, rp, s.pixel_table, d_tile_origin, d_tile_base,
-                                                                                              static_cast<uint32_t>(i) * roots_per_sample, samples[i], dc);
-        *launches += 1;
-    }
+    BatchInts sl {};
+    for (int i = 0; i < n_samples; ++i) { sl.v[i] = samples[i]; }
+    const dim3 ggrid(static_cast<unsigned>((patches + kWfThreads / 32 - 1) / (kWfThreads / 32)), static_cast<unsigned>(n_samples));
+    k_wf_generate<<<ggrid, kWfThreads, 0, st>>>(Q, s, cam, rp, d_tile_origin, d_tile_base, roots_per_sample, sl, dc);
     k_wf_begin_levels<<<1, 1, 0, st>>>(Q, static_cast<uint32_t>(n_samples), roots_per_sample);
-    WF_TRY(wf_mark(hst, WF_OTHER, st));
-    *launches += 1;
-    // per level: extend -> shade on the main stream; shadow(level) on the side stream, concurrent with extend(level + 1);
-    // shade(level + 1) pushes into the shadow queue, so it waits for shadow(level)
-    cudaStream_t sb = hst->overlap ? hst->side : st;
+    WF_TRY(wf_mark(w, WF_OTHER, st));
+    *launches += 2;
+    const int sgrid = w->sm_count * MRT_SHADE_MIN_BLOCKS;
     for (int level = 0; level < kLevels; ++level) {
         k_wf_extend<<<grid, kWfThreads, 0, st>>>(s, Q, level, dc);
-        WF_TRY(wf_mark(hst, WF_EXTEND, st));
-        if (hst->overlap && level > 0) { WF_TRY(cudaStreamWaitEvent(st, hst->shadowed, 0)); WF_TRY(wf_mark(hst, -1, st)); }
-        k_wf_shade<<<hst->sm_count * MRT_SHADE_MIN_BLOCKS, kWfThreads, 0, st>>>(s, rp, Q, level, dc);
-        WF_TRY(wf_mark(hst, WF_SHADE, st));
+        WF_TRY(wf_mark(w, WF_EXTEND, st));
+        if (level == 0) { k_wf_shade<true><<<sgrid, kWfThreads, 0, st>>>(s, rp, Q, level, dc); }
+        else { k_wf_shade<false><<<sgrid, kWfThreads, 0, st>>>(s, rp, Q, level, dc); }
+        WF_TRY(wf_mark(w, WF_SHADE, st));
         k_wf_after_shade<<<1, 1, 0, st>>>(Q, level, dc);
-        if (hst->overlap) { WF_TRY(cudaEventRecord(hst->shaded, st)); WF_TRY(cudaStreamWaitEvent(sb, hst->shaded, 0)); WF_TRY(wf_mark(hst, -1, sb)); }
-        k_wf_shadow<<<grid, kWfThreads, 0, sb>>>(s, Q, dc);
-        WF_TRY(wf_mark(hst, WF_SHADOW, sb));
-        k_wf_after_shadow<<<1, 1, 0, sb>>>(Q, dc);
-        if (hst->overlap) { WF_TRY(cudaEventRecord(hst->shadowed, sb)); WF_TRY(wf_mark(hst, -1, st)); }
-        *launches += 5;
+        k_wf_shadow<<<grid, kWfThreads, 0, st>>>(s, Q, dc);
+        WF_TRY(wf_mark(w, WF_SHADOW, st));
+        k_wf_fold<<<sgrid, 256, 0, st>>>(Q);
+        k_wf_after_fold<<<1, 1, 0, st>>>(Q, dc);
+        WF_TRY(wf_mark(w, WF_OTHER, st));
+        *launches += 6;
     }
-    if (hst->overlap) { WF_TRY(cudaStreamWaitEvent(st, hst->shadowed, 0)); WF_TRY(wf_mark(hst, -1, st)); }
-    for (int level = kLevels - 1; level >= 0; --level) {
-        k_wf_finalize_level<<<grid, kWfThreads, 0, st>>>(Q, level);
+    for (int level = kLevels - 2; level >= 0; --level) {   // no chain is created while shading the last level
+        k_wf_finalize_level<<<w->sm_count * 2, 256, 0, st>>>(Q, level);
         *launches += 1;
     }
-    for (int i = 0; i < n_samples; ++i) {
-        k_wf_resolve_roots<<<grid, kWfThreads, 0, st>>>(Q, i, avg_n[i], tg);
-        *launches += 1;
-    }
-    WF_TRY(wf_mark(hst, WF_OTHER, st));
+    WF_TRY(wf_mark(w, WF_OTHER, st));
+    return cudaGetLastError();
+}
+
+cudaError_t wavefront_resolve_batch(Wavefront *w, const uint32_t *d_tile_base, int n_tiles, uint32_t roots_per_sample, bool tiles_disjoint, int n_samples,
+                                    const int *avg_n, FrameTargets tg, uint64_t *launches, cudaStream_t st) {
+    if (n_samples < 1 || n_samples > w->batch || roots_per_sample == 0) { return n_samples < 1 || n_samples > w->batch ? cudaErrorInvalidValue : cudaSuccess; }
+    BatchInts an {};
+    for (int i = 0; i < n_samples; ++i) { an.v[i] = avg_n[i]; }
+    WF_TRY(wf_mark(w, -1, st));
+    if (tiles_disjoint) { k_wf_resolve<<<(roots_per_sample + 255) / 256, 256, 0, st>>>(w->q, roots_per_sample, n_samples, an, tg); }
+    else { k_wf_resolve_serial<<<1, 1024, 0, st>>>(w->q, d_tile_base, n_tiles, roots_per_sample, n_samples, an, tg); }
+    *launches += 1;
+    WF_TRY(wf_mark(w, WF_OTHER, st));
     return cudaGetLastError();
 }
 
@@ -816,8 +904,11 @@ extern "C" int mrt_debug_traversal_stats(unsigned long long out[3], int reset) {
 
 // ---- per-ray ground truth through the wavefront kernels (mrt_trace_rays on a PathTracer handle) ------------------------
 // The parity tests compare these results with the reference ray by ray, so that the persistent extend / shadow kernels
-// themselves (not only the per-thread traversal of the megakernel) are pinned bit for bit.
+// themselves (not only the per-thread traversal of the megakernel) are pinned bit for bit. The closest-hit rays go in as
+// level 2 of the ray queue (same buffer as level 0, but with the skip primitive where a camera ray carries its q).
 namespace mrt {
+
+constexpr int kTestLevel = 2;
 
 __global__ void k_wf_test_fill(Queues Q, int64_t n, const float *__restrict__ o, const float *__restrict__ d, const int32_t *__restrict__ okind,
                                const int32_t *__restrict__ oidx, const float *__restrict__ sdist) {
@@ -827,12 +918,11 @@ __global__ void k_wf_test_fill(Queues Q, int64_t n, const float *__restrict__ o,
     const uint32_t skip = pack_skip(sk, si);
     if (sdist != nullptr && sdist[i] >= 0.0f) {
         const uint32_t slot = atomicAdd(&Q.counts[8], 1u);
-        chain_init(Q.chains + slot, -1, static_cast<int32_t>(i));
         Q.s0[slot] = make_float4(o[3 * i], o[3 * i + 1], o[3 * i + 2], d[3 * i]);
         Q.s1[slot] = make_float4(d[3 * i + 1], d[3 * i + 2], sdist[i], __uint_as_float(skip));
-        Q.s2[slot] = make_float4(1.0f, 0.0f, 0.0f, __uint_as_float(slot));     // an unoccluded ray leaves 1 in sum[0][0] of its chain
+        Q.s2[slot] = make_float4(0.0f, 0.0f, 0.0f, __uint_as_float(static_cast<uint32_t>(i)));   // where the answer goes
     } else {
-        const uint32_t slot = atomicAdd(&Q.counts[0], 1u);
+        const uint32_t slot = atomicAdd(&Q.counts[kTestLevel], 1u);
         Q.r0[0][slot] = make_float4(o[3 * i], o[3 * i + 1], o[3 * i + 2], d[3 * i]);
         Q.r1[0][slot] = make_float4(d[3 * i + 1], d[3 * i + 2], __uint_as_float(skip), __int_as_float(1));
         Q.r3[0][slot] = make_float4(__uint_as_float(static_cast<uint32_t>(i)), 0.0f, 0.0f, 0.0f);
@@ -841,7 +931,7 @@ __global__ void k_wf_test_fill(Queues Q, int64_t n, const float *__restrict__ o,
 
 __global__ void k_wf_test_gather(SceneDev s, Queues Q, float *out_t, int32_t *out_kind, int32_t *out_idx, int32_t *out_mat, float *out_normal) {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < Q.counts[0]) {
+    if (i < Q.counts[kTestLevel]) {
         const float4 a = Q.r0[0][i], c1 = Q.r1[0][i], hq = Q.hit[i];
         const uint32_t dst = __float_as_uint(Q.r3[0][i].x), packed = __float_as_uint(hq.w);
         const v3 ro = mk3(a.x, a.y, a.z), rd = mk3(a.w, c1.x, c1.y);
@@ -860,16 +950,13 @@ __global__ void k_wf_test_gather(SceneDev s, Queues Q, float *out_t, int32_t *ou
         out_t[dst] = h.t; out_kind[dst] = h.kind; out_idx[dst] = idx; out_mat[dst] = mat;
         if (out_normal) { out_normal[3 * dst] = nrm.x; out_normal[3 * dst + 1] = nrm.y; out_normal[3 * dst + 2] = nrm.z; }
     }
-    if (i < Q.counts[9]) {   // counts[9]: shadow rays of this test (saved before the shadow queue counter is consumed)
-        const Chain *ch = Q.chains + i;
-        const uint32_t dst = static_cast<uint32_t>(ch->parent_depth);
-        const bool occluded = !(ch->sum[0][0] > 0.0f);
+    if (i < Q.counts[8]) {   // the shadow rays of this test: the visibility byte the shadow kernel wrote
+        const uint32_t dst = __float_as_uint(Q.s2[i].w);
+        const bool occluded = Q.vis[i] == 0;
         out_t[dst] = occluded ? 0.0f : Q.s1[i].z;
         out_kind[dst] = occluded ? 1 : 0; out_idx[dst] = -1; out_mat[dst] = -1;
     }
 }
-
-__global__ void k_wf_test_save_counts(Queues Q) { Q.counts[9] = Q.counts[8]; }
 
 cudaError_t wavefront_trace_rays(Wavefront *w, const SceneDev &s, int64_t n, const float *d_o, const float *d_d, const int32_t *d_okind,
                                  const int32_t *d_oidx, const float *d_sdist, float *d_t, int32_t *d_kind, int32_t *d_idx, int32_t *d_mat,
@@ -880,8 +967,7 @@ cudaError_t wavefront_trace_rays(Wavefront *w, const SceneDev &s, int64_t n, con
     WF_TRY(cudaMemsetAsync(Q.counts, 0, kWfCounts * sizeof(uint32_t), st));
     const int blocks = static_cast<int>((n + 255) / 256), grid = w->sm_count * MRT_TRAV_MIN_BLOCKS;
     k_wf_test_fill<<<blocks, 256, 0, st>>>(Q, n, d_o, d_d, d_okind, d_oidx, d_sdist);
-    k_wf_test_save_counts<<<1, 1, 0, st>>>(Q);
-    k_wf_extend<<<grid, kWfThreads, 0, st>>>(s, Q, 0, dc);
+    k_wf_extend<<<grid, kWfThreads, 0, st>>>(s, Q, kTestLevel, dc);
     k_wf_shadow<<<grid, kWfThreads, 0, st>>>(s, Q, dc);
     k_wf_test_gather<<<blocks, 256, 0, st>>>(s, Q, d_t, d_kind, d_idx, d_mat, d_normal);
     return cudaGetLastError();

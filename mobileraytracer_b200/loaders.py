@@ -252,3 +252,24 @@ def load_camera(cam_path, aspect_ratio):
     if kind.startswith("o"):
         return Camera(capi.CAMERA_ORTHOGRAPHIC, pos, look, up, f32(fov[0]) * f32(aspect_ratio), fov[1])
     return Camera(capi.CAMERA_PERSPECTIVE, pos, look, up, f32(fov[0]) * f32(aspect_ratio), fov[1])
+
+
+def replicate_scene(arrays, nx=6, nz=5, pitch_x=4200.0, pitch_z=5200.0):
+    """BASELINE config 5's synthetic scene: the scene's triangles and lights copied nx x nz times on a grid (flattened, the
+    reference has no instancing, SURVEY 8c); the copy at grid position (nx // 3, nz // 2) stays where it is, under the camera."""
+    tri, lights = arrays["triangles"], arrays["lights"]
+    tris, ls = [], []
+    for ix in range(nx):
+        for iz in range(nz):
+            off = np.array([(ix - nx // 3) * pitch_x, 0.0, (iz - nz // 2) * pitch_z], np.float32)
+            t = tri.copy()
+            t["A"] += off
+            tris.append(t)
+            lg = lights.copy()
+            lg["triangle"]["A"] += off
+            lg["position"] += off
+            ls.append(lg)
+    out = dict(arrays)
+    out["triangles"] = np.ascontiguousarray(np.concatenate(tris))
+    out["lights"] = np.ascontiguousarray(np.concatenate(ls))
+    return out

@@ -44,7 +44,7 @@ class Renderer:
 
     def __init__(self, scene, camera, width, height, samplesPixel, samplesLight=1, shader=capi.SHADER_WHITTED,
                  accelerator=capi.ACC_B200, depth_max_point=(1, 1, 1), pixel_sampler=capi.SAMPLER_AUTO, seed=1, flags=0,
-                 tables=None, device=-1, light_sampler=capi.SAMPLER_AUTO):
+                 tables=None, device=-1, light_sampler=capi.SAMPLER_AUTO, tile_begin=0, tile_stride=1):
         L = capi.lib()
         arr = scene.arrays() if isinstance(scene, S.Scene) else scene
         self._keep = arr
@@ -67,6 +67,7 @@ class Renderer:
         rd.width, rd.height, rd.samples_pixel, rd.samples_light = width, height, samplesPixel, samplesLight
         rd.shader, rd.accelerator, rd.pixel_sampler, rd.seed, rd.flags, rd.device = shader, accelerator, pixel_sampler, seed, flags, device
         rd.light_sampler = light_sampler
+        rd.tile_begin, rd.tile_stride = tile_begin, tile_stride
         for k in range(3):
             rd.depth_max_point[k] = float(depth_max_point[k])
         tb = None
@@ -141,8 +142,20 @@ class Renderer:
         capi.check(capi.lib().mrt_set_camera(self._h, C.byref(cd)), self._h)
 
     def setStream(self, cuda_stream):
-        """Run this renderer's kernels on the caller's CUDA stream (an integer cudaStream_t, e.g. torch's `cuda_stream`)."""
-        capi.check(capi.lib().mrt_set_stream(self._h, C.c_void_p(cuda_stream)), self._h)
+        """Run this renderer's kernels on the caller's CUDA stream (an integer cudaStream_t, e.g. torch's `cuda_stream`).
+        torch's default stream has the handle 0, which mrt_set_stream reads as "back to the handle's own stream": it is
+        passed as cudaStreamLegacy (0x1), the same stream under the name the C-ABI can tell apart. None restores the own stream."""
+        if cuda_stream is None:
+            handle = None
+        else:
+            handle = C.c_void_p(int(cuda_stream) if int(cuda_stream) != 0 else 1)
+        capi.check(capi.lib().mrt_set_stream(self._h, handle), self._h)
+
+    def setPixelStream(self, draws):
+        """SAMPLER_STREAM: the pixel sampler's draws of the next frame(s), taken by the host from the sampler object itself
+        (MersenneTwister / PCG keep hidden generator state), in the order Renderer::renderScene makes them."""
+        d = np.ascontiguousarray(draws, np.float32)
+        capi.check(capi.lib().mrt_set_pixel_stream(self._h, capi.ptr(d), len(d)), self._h)
 
     def stats(self):
         st = capi.Stats()

@@ -16,6 +16,11 @@
 #include "Components/Samplers/Constant.hpp"
 #include "Components/Samplers/StaticHaltonSeq.hpp"
 #include "Components/Samplers/StaticPCG.hpp"
+#include "Components/Samplers/StaticMersenneTwister.hpp"
+#include "Components/Samplers/HaltonSeq.hpp"
+#include "Components/Samplers/Stratified.hpp"
+#include "Components/Samplers/MersenneTwister.hpp"
+#include "Components/Samplers/PCG.hpp"
 #include "Components/Shaders/DepthMap.hpp"
 #include "Components/Shaders/DiffuseMaterial.hpp"
 #include "Components/Shaders/NoShadows.hpp"
@@ -38,6 +43,8 @@ struct RefConfig {
     int width, height, threads, shader, scene, spp, spl, accelerator;
     const char *obj, *mtl, *cam;
     int samplers;   // 0: the Linux front-end's choice (StaticHaltonSeq, C_wrapper.cpp:144-148,176); 1: Android's (StaticPCG, JNI_layer.cpp:601,616-618,636)
+    int copies_x, copies_z;   // OBJ scenes: the loaded triangles are copied on a copies_x x copies_z grid (BASELINE config 5's synthetic scene,
+                              // same offsets and order as mobileraytracer_b200.loaders.replicate_scene); 0 / 1 = as loaded. Lights are not copied.
 };
 
 struct RefHandle {
@@ -121,6 +128,18 @@ void *ref_create(const RefConfig *c) {
                             if (pcg) { return ::MobileRT::std::make_unique<::Components::StaticPCG>(); }
                             return ::MobileRT::std::make_unique<::Components::StaticHaltonSeq>(); },
                         c->obj, texturesCache)) { delete h; return nullptr; }
+                if (c->copies_x > 1 || c->copies_z > 1) {
+                    const int nx {c->copies_x > 1 ? c->copies_x : 1}, nz {c->copies_z > 1 ? c->copies_z : 1};
+                    const ::std::vector<Triangle> base {scene.triangles_};
+                    scene.triangles_.clear();
+                    scene.triangles_.reserve(base.size() * static_cast<size_t>(nx * nz));
+                    for (int ix {0}; ix < nx; ++ix) {
+                        for (int iz {0}; iz < nz; ++iz) {
+                            const ::glm::vec3 off {static_cast<float>(ix - nx / 3) * 4200.0F, 0.0F, static_cast<float>(iz - nz / 2) * 5200.0F};
+                            for (Triangle t : base) { t.pointA_ += off; scene.triangles_.push_back(t); }
+                        }
+                    }
+                }
                 const double t2 = now();
                 h->secsLoad = t1 - t0; h->secsFill = t2 - t1;
                 ::Components::CameraFactory cameraFactory {};
@@ -134,6 +153,16 @@ void *ref_create(const RefConfig *c) {
         if (dynamic_cast<::Components::Orthographic *>(camera.get()) != nullptr) { h->cameraKind = 1; }
         if (c->spp > 1 && c->samplers == 1) {
             samplerPixel = ::MobileRT::std::make_unique<::Components::StaticPCG>();
+        } else if (c->spp > 1 && c->samplers == 2) {   // pixel jitter from StaticMersenneTwister (StaticMersenneTwister.cpp:6-16); lights / RR as the Linux front-end
+            samplerPixel = ::MobileRT::std::make_unique<::Components::StaticMersenneTwister>();
+        } else if (c->spp > 1 && c->samplers == 3) {   // HaltonSeq (HaltonSeq.cpp:10-19): returns 1.0 once its domain is exhausted
+            samplerPixel = ::MobileRT::std::make_unique<::Components::HaltonSeq>(static_cast<::std::uint32_t>(c->width), static_cast<::std::uint32_t>(c->height), static_cast<::std::uint32_t>(c->spp));
+        } else if (c->spp > 1 && c->samplers == 4) {   // Stratified (Stratified.cpp:10-19)
+            samplerPixel = ::MobileRT::std::make_unique<::Components::Stratified>(static_cast<::std::uint32_t>(c->width), static_cast<::std::uint32_t>(c->height), static_cast<::std::uint32_t>(c->spp));
+        } else if (c->spp > 1 && c->samplers == 5) {   // MersenneTwister (MersenneTwister.cpp:5-11): thread_local generator, never reset
+            samplerPixel = ::MobileRT::std::make_unique<::Components::MersenneTwister>();
+        } else if (c->spp > 1 && c->samplers == 6) {   // PCG (PCG.cpp:6-13)
+            samplerPixel = ::MobileRT::std::make_unique<::Components::PCG>();
         } else if (c->spp > 1) {
             samplerPixel = ::MobileRT::std::make_unique<::Components::StaticHaltonSeq>();
         } else {
@@ -166,6 +195,23 @@ void *ref_create(const RefConfig *c) {
 }
 
 void ref_destroy(void *p) { delete static_cast<RefHandle *>(p); }
+
+// The next n draws of the renderer's pixel sampler (Renderer.cpp:137-138 calls getSample() twice per pixel-sample), for
+// the stateful samplers whose sequence only the sampler object itself can produce (MersenneTwister, PCG).
+void ref_pixel_sampler_draws(void *p, int n, float *out) {
+    auto *h = static_cast<RefHandle *>(p);
+    for (int i = 0; i < n; ++i) { out[i] = h->renderer->samplerPixel_->getSample(); }
+    errno = 0;
+}
+// The seeded std::random_device stand-in counts its draws; setting the counter back makes the next generators and table
+// shuffles repeat (used to give two threads' thread_local MersenneTwister / PCG generators the same seed).
+unsigned ref_random_device_counter(int set, unsigned value) {
+    unsigned &c = ::std::mrt_seeded_random_device::counter();
+    const unsigned old = c;
+    if (set) { c = value; }
+    return old;
+}
+void ref_pixel_sampler_reset(void *p) { static_cast<RefHandle *>(p)->renderer->samplerPixel_->resetSampling(); errno = 0; }
 
 // renderFrame (app/MobileRT/Renderer.cpp:53) x repeats; returns wall seconds of the loop.
 double ref_render(void *p, int32_t *bitmap, int threads, int repeats) {

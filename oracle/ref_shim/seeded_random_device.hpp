@@ -19,12 +19,13 @@ namespace std {
         static constexpr result_type min() { return 0u; }
         static constexpr result_type max() { return 0xFFFFFFFFu; }
         double entropy() const noexcept { return 0.0; }
+        // draws made so far by every instance (the shim can rewind it: ref_random_device_counter in ref_api.cpp)
+        static unsigned int &counter() { static unsigned int c = 0u; return c; }
         result_type operator()() {
             // Every draw returns seed + draw-counter, seed from MRT_ORACLE_SEED (default 1).
-            static unsigned int counter = 0u;
             const char *s = ::getenv("MRT_ORACLE_SEED");
             const unsigned int seed = s ? static_cast<unsigned int>(::strtoul(s, nullptr, 10)) : 1u;
-            return seed + 7919u * (counter++);
+            return seed + 7919u * (counter()++);
         }
     };
 }

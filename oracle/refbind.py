@@ -22,7 +22,8 @@ assert TRI_DTYPE.itemsize == 100 and SPH_DTYPE.itemsize == 20 and PLA_DTYPE.item
 class RefConfig(C.Structure):
     _fields_ = [("width", C.c_int), ("height", C.c_int), ("threads", C.c_int), ("shader", C.c_int),
                 ("scene", C.c_int), ("spp", C.c_int), ("spl", C.c_int), ("accelerator", C.c_int),
-                ("obj", C.c_char_p), ("mtl", C.c_char_p), ("cam", C.c_char_p), ("samplers", C.c_int)]
+                ("obj", C.c_char_p), ("mtl", C.c_char_p), ("cam", C.c_char_p), ("samplers", C.c_int),
+                ("copies_x", C.c_int), ("copies_z", C.c_int)]
 
 
 def available():
@@ -45,6 +46,10 @@ def lib():
         L.ref_render.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int]
         L.ref_raytrace.restype = C.c_double
         L.ref_raytrace.argtypes = [C.POINTER(RefConfig), C.c_void_p, C.c_int, C.c_int]
+        L.ref_pixel_sampler_draws.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        L.ref_pixel_sampler_reset.argtypes = [C.c_void_p]
+        L.ref_random_device_counter.restype = C.c_uint
+        L.ref_random_device_counter.argtypes = [C.c_int, C.c_uint]
         L.ref_casted_rays.restype = C.c_uint64
         L.ref_casted_rays.argtypes = [C.c_void_p]
         for name in ("ref_times", "ref_counts", "ref_triangles", "ref_spheres", "ref_planes", "ref_materials",
@@ -104,15 +109,22 @@ def light_index_counter():
     return int(lib().mrt_ref_light_index_counter())
 
 
+def random_device_counter(value=None):
+    """Draws the seeded std::random_device stand-in has handed out; with a value, rewinds / sets it (returns the old count)."""
+    return int(lib().ref_random_device_counter(0 if value is None else 1, 0 if value is None else int(value)))
+
+
 class RefRenderer:
     """Scene -> Shader -> Renderer assembled like C_wrapper.cpp's work_thread and kept alive."""
 
     def __init__(self, width, height, shader, scene, spp=1, spl=1, accelerator=3, threads=1,
-                 obj=None, mtl=None, cam=None, samplers=0):
-        """samplers: 0 = the Linux front-end's (StaticHaltonSeq), 1 = Android's (StaticPCG) for pixel jitter, OBJ lights, RR."""
+                 obj=None, mtl=None, cam=None, samplers=0, copies=(1, 1)):
+        """samplers: 0 = the Linux front-end's (StaticHaltonSeq), 1 = Android's (StaticPCG) for pixel jitter, OBJ lights, RR;
+        2..6 = pixel jitter from StaticMersenneTwister / HaltonSeq / Stratified / MersenneTwister / PCG (lights, RR as 0).
+        copies: OBJ scenes only, the loaded triangles copied on a (nx, nz) grid (config 5's synthetic scene)."""
         self.cfg = RefConfig(width, height, threads, shader, scene, spp, spl, accelerator,
                              obj.encode() if obj else None, mtl.encode() if mtl else None,
-                             cam.encode() if cam else None, samplers)
+                             cam.encode() if cam else None, samplers, int(copies[0]), int(copies[1]))
         self.width, self.height, self.spp, self.spl = width, height, spp, spl
         self.h = lib().ref_create(C.byref(self.cfg))
         if not self.h:
@@ -145,6 +157,15 @@ class RefRenderer:
 
     def casted_rays(self):
         return int(lib().ref_casted_rays(self.h))
+
+    def pixel_sampler_draws(self, n):
+        """The next n draws of the renderer's own pixel sampler object (advances it, like rendering would)."""
+        out = np.zeros(n, np.float32)
+        lib().ref_pixel_sampler_draws(self.h, n, _p(out))
+        return out
+
+    def pixel_sampler_reset(self):
+        lib().ref_pixel_sampler_reset(self.h)
 
     def times(self):
         t = np.zeros(3, np.float64)

@@ -41,7 +41,7 @@ def test_no_cpu_fallback_and_argument_checks():
 def test_record_layouts_match_the_reference():
     from mobileraytracer_b200 import capi
     assert capi.TRIANGLE.itemsize == 100 and capi.SPHERE.itemsize == 20 and capi.PLANE.itemsize == 28   # static_asserts of ref_api.cpp
-    assert C.sizeof(capi.Stats) == 7 * 8 + 13 * 8
+    assert C.sizeof(capi.Stats) == 7 * 8 + 15 * 8   # mrt_stats (include/mobilert_b200.h)
 
 
 def test_round_down_to_multiple_of():
@@ -173,3 +173,16 @@ def test_cpp_adapter_compiles_against_reference(tmp_path):
         cmd += ["-isystem", d]
     r = subprocess.run(cmd + [str(src)], capture_output=True, text=True)
     assert r.returncode == 0, r.stderr[-2000:]
+
+
+def test_tile_and_sample_partition_covers_every_tile_sample_once():
+    """plan_partition (multigpu.py): tile_groups x sample_groups ranks; every (tile, sample) pair belongs to exactly one rank."""
+    from mobileraytracer_b200.multigpu import plan_partition
+    for world, tg in ((1, 1), (2, 1), (2, 2), (4, 4), (8, 4), (8, 1), (8, 8)):
+        seen = np.zeros((256, 16), np.int32)
+        for rank in range(world):
+            tb, ts, sb, ss = plan_partition(rank, world, tg)
+            seen[tb::ts, sb::ss] += 1
+        assert (seen == 1).all(), (world, tg)
+    with pytest.raises(ValueError):
+        plan_partition(0, 8, 3)

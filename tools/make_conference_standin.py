@@ -3,7 +3,8 @@
 reference's own loader (tinyobjloader) and mobileraytracer_b200.loaders read:
 
   a closed room with panelled walls, a long table, rows of chairs, table-top objects and 4 emissive ceiling panels
-  (material `light`, Ke 0.9 like conference.mtl:360-361), 328 120 triangles at the default detail, 36 diffuse materials,
+  (material `light`, Ke 0.9 like conference.mtl:360-361), 328 120 triangles at the default detail, conference.mtl's own
+  materials (Kd by file position, the three specular ones included),
   camera = WavefrontOBJs/conference/conference.cam (p -460 500 -1000, l 0 400 0, f 45 45).
 
 Everything is generated from a fixed seed; the same arguments always give the same bytes. Numbers measured on this scene
@@ -243,12 +244,27 @@ def generate(detail=DEFAULT_DETAIL, seed=7):
     return mesh.arrays()
 
 
+# Kd of the 35 surface materials of the reference's WavefrontOBJs/conference/conference.mtl, in file order (mesh0_SG ...
+# mesh27_SG); the three with a specular term (Ks 0.1 0.1 0.1: mesh11_SG "green boards", mesh12_SG, mesh13_SG, conference.mtl:104-138)
+# are file positions 10, 11, 12. A constant table of the reference's data file: the mesh is a stand-in, the materials are not.
+CONFERENCE_KD = [
+    (0.639216, 0.6, 0.607843), (0.639216, 0.4, 0.129412), (0.737255, 0.4, 0.156863), (0.176471, 0.058824, 0.058824),
+    (0.898039, 0.898039, 0.898039), (0.066667, 0.066667, 0.066667), (0.698039, 0.698039, 0.698039), (0.686275, 0.427451, 0.168627),
+    (0.709804, 0.709804, 0.709804), (0.6, 0.6, 0.6), (0.117647, 0.258824, 0.14902), (0.427451, 0.427451, 0.427451),
+    (0.517647, 0.447059, 0.337255), (0.447059, 0.447059, 0.447059), (1.0, 1.0, 1.0), (0.498039, 0.498039, 0.498039),
+    (0.4, 0.4, 0.4), (0.878431, 0.717647, 0.576471), (0.827451, 0.698039, 0.427451), (0.286275, 0.14902, 0.129412),
+    (0.078431, 0.078431, 0.078431), (0.819608, 0.086275, 0.066667), (0.698039, 0.698039, 0.698039), (0.6, 0.6, 0.6),
+    (0.639216, 0.439216, 0.317647), (1.0, 1.0, 1.0), (0.058824, 0.058824, 0.058824), (0.976471, 0.176471, 0.168627),
+    (0.6, 0.6, 0.6), (0.478431, 0.239216, 0.117647), (0.047059, 0.047059, 0.047059), (0.6, 0.6, 0.6),
+    (0.098039, 0.098039, 0.098039), (0.047059, 0.047059, 0.047059), (0.466667, 0.447059, 0.427451)]
+CONFERENCE_KS = {10: (0.1, 0.1, 0.1), 11: (0.1, 0.1, 0.1), 12: (0.1, 0.1, 0.1)}
+
+
 def material_table(seed=7):
-    rng = np.random.default_rng(seed + 1000)
-    kd = rng.uniform(0.15, 0.8, (N_MATERIALS, 3))
-    kd[0] = (0.55, 0.5, 0.45)
-    kd[1] = (0.75, 0.75, 0.75)
-    return np.round(kd, 6)
+    """(Kd, Ks) of the stand-in's 36 material ids: conference.mtl's own values by file position (id 35 wraps to 0)."""
+    kd = np.array([CONFERENCE_KD[i % len(CONFERENCE_KD)] for i in range(N_MATERIALS)])
+    ks = np.array([CONFERENCE_KS.get(i % len(CONFERENCE_KD), (0.0, 0.0, 0.0)) for i in range(N_MATERIALS)])
+    return kd, ks
 
 
 def write(out_dir, detail=DEFAULT_DETAIL, seed=7, name="conference_standin"):
@@ -256,10 +272,11 @@ def write(out_dir, detail=DEFAULT_DETAIL, seed=7, name="conference_standin"):
     os.makedirs(out_dir, exist_ok=True)
     v, f, m = generate(detail, seed)
     obj, mtl, cam = (os.path.join(out_dir, name + ext) for ext in (".obj", ".mtl", ".cam"))
-    kd = material_table(seed)
+    kd, ks = material_table(seed)
     with open(mtl, "w") as fh:
         for i in range(N_MATERIALS):
-            fh.write("newmtl mesh%d_SG\n  Ns 40.0\n  Ni 1.5\n  d 1.0\n  Tf 1.0 1.0 1.0\n  illum 2\n  Ka 0.0 0.0 0.0\n  Kd %.6f %.6f %.6f\n  Ke 0.0 0.0 0.0\n\n" % (i, *kd[i]))
+            spec = "  Ks %.6f %.6f %.6f\n" % tuple(ks[i]) if ks[i].any() else ""
+            fh.write("newmtl mesh%d_SG\n  Ns 40.0\n  Ni 1.5\n  d 1.0\n  Tf 1.0 1.0 1.0\n  illum 2\n  Ka 0.0 0.0 0.0\n  Kd %.6f %.6f %.6f\n%s  Ke 0.0 0.0 0.0\n\n" % (i, *kd[i], spec))
         fh.write("newmtl light\n  Ke 0.9 0.9 0.9\n")
     with open(obj, "w") as fh:
         fh.write("# procedural stand-in for the missing conference.obj (see tools/make_conference_standin.py)\nmtllib %s.mtl\n" % name)

@@ -14,17 +14,7 @@ import mobileraytracer_b200 as mrt  # noqa: E402
 from mobileraytracer_b200 import capi, loaders  # noqa: E402
 
 
-def replicate(scene, nx=6, nz=5, pitch_x=4200.0, pitch_z=5200.0):
-    tri, lights = scene["triangles"], scene["lights"]
-    tris, ls = [], []
-    for ix in range(nx):
-        for iz in range(nz):
-            off = np.array([(ix - nx // 3) * pitch_x, 0.0, (iz - nz // 2) * pitch_z], np.float32)   # one copy stays at the origin, under the camera
-            t = tri.copy(); t["A"] += off; tris.append(t)
-            l = lights.copy(); l["triangle"]["A"] += off; l["position"] += off; ls.append(l)
-    out = dict(scene)
-    out["triangles"] = np.ascontiguousarray(np.concatenate(tris)); out["lights"] = np.ascontiguousarray(np.concatenate(ls))
-    return out
+replicate = loaders.replicate_scene
 
 
 if __name__ == "__main__":
