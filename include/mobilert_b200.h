@@ -68,13 +68,20 @@ typedef struct mrt_scene_desc {
     const int32_t *material_texture;
 } mrt_scene_desc;
 
-enum { MRT_CAMERA_PERSPECTIVE = 0, MRT_CAMERA_ORTHOGRAPHIC = 1 };
+enum { MRT_CAMERA_PERSPECTIVE = 0, MRT_CAMERA_ORTHOGRAPHIC = 1,
+       /* the state of an already constructed camera object instead of its constructor arguments (what a front-end holds:
+        * C_wrapper.cpp:76-141 / JNI_layer.cpp:164 keep a Camera, not its lookAt): position = Camera::position_, look_at =
+        * Camera::direction_, up = Camera::up_, right = Camera::right_ (MobileRT/Camera.hpp:26-41), a / b = Perspective::hFov_ /
+        * vFov_ in radians (Perspective.hpp:16-17) or Orthographic::sizeH_ / sizeV_ (already halved, Orthographic.hpp:19-20).
+        * Nothing is recomputed, so the rays are bit-identical to that object's generateRay. */
+       MRT_CAMERA_PERSPECTIVE_STATE = 2, MRT_CAMERA_ORTHOGRAPHIC_STATE = 3 };
 /* Arguments of Perspective(position, lookAt, up, hFovDeg, vFovDeg) (Components/Cameras/Perspective.cpp:8-14)
  * or Orthographic(position, lookAt, up, sizeH, sizeV) (Components/Cameras/Orthographic.cpp:7-13). */
 typedef struct mrt_camera_desc {
     int32_t kind;
     float position[3], look_at[3], up[3];
     float a, b;
+    float right[3];   /* only read for the *_STATE kinds */
 } mrt_camera_desc;
 
 /* Shader ids of MobileRT::Config::shader (MobileRT/Config.hpp, C_wrapper.cpp:154-194) */
@@ -227,17 +234,6 @@ int mrt_trace_rays(mrt_handle *h, int64_t n, const float *origins, const float *
 int mrt_generate_rays(mrt_handle *h, int64_t n, const float *uvdd, float *out_origins, float *out_directions);
 /* Shader::rayTrace (Shader.cpp:86) on arbitrary rays of the given depth -> rgb (deterministic shaders). HOST arrays. */
 int mrt_shade_rays(mrt_handle *h, int64_t n, const float *origins, const float *directions, int32_t depth, float *out_rgb);
-
-/* Primitive-level device functions exposed for the reference's known-answer tests (Unit_Testing/TestTriangle.cpp,
- * TestAABB.cpp, TestPlane.cpp). Each runs the device function in a one-thread kernel. */
-int mrt_test_triangle_intersect(const mrt_triangle *tri, const float *o, const float *d, float t_max, int32_t self_skip,
-                                float *out_t, float *out_normal_uv_point8);
-int mrt_test_sphere_intersect(const mrt_sphere *s, const float *o, const float *d, float t_max, float *out_t, float *out_normal);
-int mrt_test_plane_intersect(const mrt_plane *p, const float *o, const float *d, float t_max, float *out_t);
-int mrt_test_aabb_intersect(const float *box_min, const float *box_max, const float *o, const float *d, int32_t *out_hit);
-int mrt_test_incremental_avg(const float *rgb, int32_t avg, int32_t num_sample, int32_t *out);
-/* MobileRT::haltonSequence (MobileRT/Utils/Utils.cpp:43-53) evaluated on the device for indices [first, first+n). */
-int mrt_test_halton(uint32_t first, int64_t n, uint32_t base, float *out);
 
 /* Library / device info: returns the number of CUDA devices visible, 0 when none (never falls back to the CPU). */
 int mrt_device_count(void);

@@ -42,16 +42,16 @@ class B200Renderer final {
         return r;
     }
 
-    static mrt_camera_desc flatten(const Camera &camera, const ::glm::vec3 &lookAt, const ::glm::vec3 &up) {
+    /* The camera object as the front-end holds it (C_wrapper.cpp:76-141 keeps the Camera, not its lookAt): its members go
+     * over unchanged (MRT_CAMERA_*_STATE), so the device's generateRay sees the very numbers Camera::generateRay sees. */
+    static mrt_camera_desc flatten(const Camera &camera) {
         mrt_camera_desc c;
         ::std::memset(&c, 0, sizeof(c));
-        put3(c.position, camera.position_); put3(c.look_at, lookAt); put3(c.up, up);
+        put3(c.position, camera.position_); put3(c.look_at, camera.direction_); put3(c.up, camera.up_); put3(c.right, camera.right_);
         if (const auto *p = dynamic_cast<const ::Components::Perspective *>(&camera)) {
-            c.kind = MRT_CAMERA_PERSPECTIVE;
-            // Perspective stores radians (Perspective.cpp:8-14); the C-ABI takes the constructor's degrees
-            c.a = p->getHFov() * 180.0F / 3.14159265358979323846F; c.b = p->getVFov() * 180.0F / 3.14159265358979323846F;
+            c.kind = MRT_CAMERA_PERSPECTIVE_STATE; c.a = p->hFov_; c.b = p->vFov_;   // the stored radians (getHFov() converts back to degrees)
         } else if (const auto *o = dynamic_cast<const ::Components::Orthographic *>(&camera)) {
-            c.kind = MRT_CAMERA_ORTHOGRAPHIC; c.a = o->getSizeH() * 2.0F; c.b = o->getSizeV() * 2.0F;
+            c.kind = MRT_CAMERA_ORTHOGRAPHIC_STATE; c.a = o->sizeH_; c.b = o->sizeV_;
         } else {
             throw ::std::runtime_error("B200Renderer: unknown camera type");
         }
@@ -60,14 +60,16 @@ class B200Renderer final {
 
 public:
     /* Same inputs the front-ends hold right before they build Shader + Renderer (C_wrapper.cpp:76-203): the Scene
-     * (before it is moved into the Shader), the camera with its lookAt / up, the Config fields. */
-    B200Renderer(const Scene &scene, const Camera &camera, const ::glm::vec3 &lookAt, const ::glm::vec3 &up,
+     * (before it is moved into the Shader), the camera, the Config fields. */
+    B200Renderer(const Scene &scene, const Camera &camera,
                  ::std::int32_t width, ::std::int32_t height, ::std::int32_t samplesPixel, ::std::int32_t samplesLight,
                  ::std::int32_t shader,
                  // which static table the front-end's own samplers read: MRT_SAMPLER_AUTO = StaticHaltonSeq as in
                  // C_wrapper.cpp:109,145,176; the Android layer passes MRT_SAMPLER_STATIC_PCG (JNI_layer.cpp:601,616-618,636)
                  ::std::int32_t frontEndSampler = MRT_SAMPLER_AUTO,
-                 ::std::uint32_t flags = 0u /* MRT_FLAG_*, e.g. MRT_FLAG_PROGRESSIVE for a UI that shows the bitmap while it renders */) {
+                 ::std::uint32_t flags = 0u /* MRT_FLAG_*, e.g. MRT_FLAG_PROGRESSIVE for a UI that shows the bitmap while it renders */,
+                 const ::glm::vec3 &depthMaxPoint = ::glm::vec3 {1.0F, 1.0F, 1.0F} /* DepthMap's maxPoint (C_wrapper.cpp:80-138) */,
+                 ::std::int32_t accelerator = MRT_ACC_B200 /* or MRT_ACC_NAIVE for Naive's visibility rules */) {
         ::std::vector<mrt_triangle> tris; tris.reserve(scene.triangles_.size());
         for (const Triangle &t : scene.triangles_) { tris.push_back(flatten(t)); }
         ::std::vector<mrt_sphere> spheres;
@@ -116,12 +118,12 @@ public:
         sd.planes = planes.data(); sd.n_planes = static_cast<int64_t>(planes.size());
         sd.materials = mats.data(); sd.n_materials = static_cast<int64_t>(mats.size());
         sd.lights = lights.data(); sd.n_lights = static_cast<int64_t>(lights.size());
-        const mrt_camera_desc cd = flatten(camera, lookAt, up);
+        const mrt_camera_desc cd = flatten(camera);
         mrt_render_desc rd;
         ::std::memset(&rd, 0, sizeof(rd));
         rd.width = width; rd.height = height; rd.samples_pixel = samplesPixel; rd.samples_light = samplesLight;
-        rd.shader = shader; rd.accelerator = MRT_ACC_B200; rd.pixel_sampler = MRT_SAMPLER_AUTO; rd.seed = 1u;
-        rd.depth_max_point[0] = rd.depth_max_point[1] = rd.depth_max_point[2] = 1.0F;   // C_wrapper.cpp:138
+        rd.shader = shader; rd.accelerator = accelerator; rd.pixel_sampler = MRT_SAMPLER_AUTO; rd.seed = 1u;
+        put3(rd.depth_max_point, depthMaxPoint);
         rd.device = -1; rd.flags = flags;
         if (frontEndSampler == MRT_SAMPLER_STATIC_PCG) {
             rd.light_sampler = MRT_SAMPLER_STATIC_PCG;

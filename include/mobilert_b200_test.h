@@ -1,0 +1,32 @@
+/*
+ * mobilert_b200_test.h — C-ABI of libmobilert_b200_test.so: the primitive-level device functions of the hot path, one call
+ * at a time, so that the reference's own known-answer vectors can be run against the device code. A separate library on
+ * purpose: nothing of this is in libmobilert_b200.so, which a front-end links.
+ */
+#ifndef MOBILERT_B200_TEST_H
+#define MOBILERT_B200_TEST_H
+
+#include "mobilert_b200.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Primitive-level device functions exposed for the reference's known-answer tests (Unit_Testing/TestTriangle.cpp,
+ * TestAABB.cpp, TestPlane.cpp). Each runs the device function in a one-thread kernel. */
+int mrt_test_triangle_intersect(const mrt_triangle *tri, const float *o, const float *d, float t_max, int32_t self_skip,
+                                float *out_t, float *out_normal_uv_point8);
+int mrt_test_sphere_intersect(const mrt_sphere *s, const float *o, const float *d, float t_max, float *out_t, float *out_normal);
+int mrt_test_plane_intersect(const mrt_plane *p, const float *o, const float *d, float t_max, float *out_t);
+int mrt_test_aabb_intersect(const float *box_min, const float *box_max, const float *o, const float *d, int32_t *out_hit);
+int mrt_test_incremental_avg(const float *rgb, int32_t avg, int32_t num_sample, int32_t *out);
+/* MobileRT::haltonSequence (MobileRT/Utils/Utils.cpp:43-53) evaluated on the device for indices [first, first+n). */
+int mrt_test_halton(uint32_t first, int64_t n, uint32_t base, float *out);
+
+/* Description of the last failure of an entry point of this library on the calling thread. */
+const char *mrt_test_last_error(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MOBILERT_B200_TEST_H */

@@ -40,7 +40,7 @@ class Texture(C.Structure):
 
 class CameraDesc(C.Structure):
     _fields_ = [("kind", C.c_int32), ("position", C.c_float * 3), ("look_at", C.c_float * 3), ("up", C.c_float * 3),
-                ("a", C.c_float), ("b", C.c_float)]
+                ("a", C.c_float), ("b", C.c_float), ("right", C.c_float * 3)]
 
 
 class RenderDesc(C.Structure):
@@ -70,9 +70,10 @@ class Stats(C.Structure):
 # every symbol include/mobilert_b200.h declares
 SYMBOLS = ["mrt_create", "mrt_destroy", "mrt_render_frame", "mrt_render_frame_device", "mrt_render_accumulate_device",
            "mrt_resolve_device", "mrt_set_camera", "mrt_set_pixel_stream", "mrt_set_stream", "mrt_stop", "mrt_set_replay_counter", "mrt_get_replay_counter", "mrt_get_sample", "mrt_get_total_rays", "mrt_get_stats",
-           "mrt_last_error", "mrt_trace_rays", "mrt_generate_rays", "mrt_shade_rays", "mrt_test_triangle_intersect",
-           "mrt_test_sphere_intersect", "mrt_test_plane_intersect", "mrt_test_aabb_intersect", "mrt_test_incremental_avg",
-           "mrt_test_halton", "mrt_device_count", "mrt_version"]
+           "mrt_last_error", "mrt_trace_rays", "mrt_generate_rays", "mrt_shade_rays", "mrt_device_count", "mrt_version"]
+# every symbol include/mobilert_b200_test.h declares (libmobilert_b200_test.so: the device functions one call at a time)
+TEST_SYMBOLS = ["mrt_test_triangle_intersect", "mrt_test_sphere_intersect", "mrt_test_plane_intersect", "mrt_test_aabb_intersect",
+                "mrt_test_incremental_avg", "mrt_test_halton", "mrt_test_last_error"]
 
 _lib = None
 
@@ -101,7 +102,8 @@ def lib():
         L.mrt_resolve_device.argtypes = [vp, vp, vp]
         L.mrt_set_camera.argtypes = [vp, C.POINTER(CameraDesc)]
         L.mrt_set_stream.argtypes = [vp, vp]
-        L.mrt_set_pixel_stream.argtypes = [vp, vp, i64]
+        if hasattr(L, "mrt_set_pixel_stream"):   # absent from older diagnostic builds loaded through MRT_B200_LIB
+            L.mrt_set_pixel_stream.argtypes = [vp, vp, i64]
         L.mrt_stop.argtypes = [vp]
         L.mrt_set_replay_counter.argtypes = [vp, C.c_uint32]
         L.mrt_get_replay_counter.argtypes = [vp, C.POINTER(C.c_uint32)]
@@ -113,16 +115,40 @@ def lib():
         L.mrt_trace_rays.argtypes = [vp, i64] + [vp] * 10
         L.mrt_generate_rays.argtypes = [vp, i64, vp, vp, vp]
         L.mrt_shade_rays.argtypes = [vp, i64, vp, vp, i32, vp]
+        L.mrt_device_count.restype = C.c_int
+        L.mrt_version.restype = C.c_char_p
+        _lib = L
+    return _lib
+
+
+_test_lib = None
+TEST_LIB_PATH = os.path.join(_HERE, "libmobilert_b200_test.so")
+
+
+def test_lib():
+    """libmobilert_b200_test.so (include/mobilert_b200_test.h): raises when it has not been built."""
+    global _test_lib
+    if _test_lib is None:
+        if not os.path.exists(TEST_LIB_PATH):
+            raise ImportError("libmobilert_b200_test.so is missing: run `python -c 'import __graft_entry__ as g; g.build()'`")
+        L = C.CDLL(TEST_LIB_PATH)
+        vp, i32, i64, f32 = C.c_void_p, C.c_int32, C.c_int64, C.c_float
         L.mrt_test_triangle_intersect.argtypes = [vp, vp, vp, f32, i32, vp, vp]
         L.mrt_test_sphere_intersect.argtypes = [vp, vp, vp, f32, vp, vp]
         L.mrt_test_plane_intersect.argtypes = [vp, vp, vp, f32, vp]
         L.mrt_test_aabb_intersect.argtypes = [vp, vp, vp, vp, vp]
         L.mrt_test_incremental_avg.argtypes = [vp, i32, i32, vp]
         L.mrt_test_halton.argtypes = [C.c_uint32, i64, C.c_uint32, vp]
-        L.mrt_device_count.restype = C.c_int
-        L.mrt_version.restype = C.c_char_p
-        _lib = L
-    return _lib
+        L.mrt_test_last_error.restype = C.c_char_p
+        _test_lib = L
+    return _test_lib
+
+
+def check_test(rc):
+    if rc != MRT_OK:
+        msg = test_lib().mrt_test_last_error()
+        raise MrtError(rc, msg.decode() if msg else "?")
+    return rc
 
 
 def ptr(a):

@@ -90,6 +90,15 @@ int cuda_fail(mrt_handle *h, cudaError_t e, const char *what) {
 // + Orthographic ctor (Orthographic.cpp:7-13)
 CameraRec make_camera(const mrt_camera_desc &c) {
     CameraRec r {};
+    if (c.kind == MRT_CAMERA_PERSPECTIVE_STATE || c.kind == MRT_CAMERA_ORTHOGRAPHIC_STATE) {   // a constructed camera's members, taken as they are
+        r.kind = c.kind == MRT_CAMERA_PERSPECTIVE_STATE ? MRT_CAMERA_PERSPECTIVE : MRT_CAMERA_ORTHOGRAPHIC;
+        r.position = mk3(c.position[0], c.position[1], c.position[2]);
+        r.direction = mk3(c.look_at[0], c.look_at[1], c.look_at[2]);
+        r.up = mk3(c.up[0], c.up[1], c.up[2]);
+        r.right = mk3(c.right[0], c.right[1], c.right[2]);
+        r.a = c.a; r.b = c.b;
+        return r;
+    }
     r.kind = c.kind;
     const v3 pos = mk3(c.position[0], c.position[1], c.position[2]);
     const v3 look = mk3(c.look_at[0], c.look_at[1], c.look_at[2]);
@@ -306,6 +315,20 @@ int upload_scene(mrt_handle *h, const mrt_scene_desc &sc) {
     return MRT_OK;
 }
 
+// true when the 2^20 values are exactly the set {k / 2^20 : 0 <= k < 2^20}, each once: the radical inverses in base 2 of
+// 0 .. 2^20 - 1 (Utils.cpp:43-53) in any order, i.e. any shuffle of fillArrayWithHaltonSeq's table
+bool is_permutation_of_dyadic_grid(const float *t) {
+    std::vector<bool> seen(kArraySize, false);
+    for (uint32_t i = 0; i < kArraySize; ++i) {
+        const float v = t[i] * static_cast<float>(kArraySize);
+        if (!(v >= 0.0f) || v >= static_cast<float>(kArraySize)) { return false; }
+        const uint32_t k = static_cast<uint32_t>(v);
+        if (static_cast<float>(k) != v || seen[k]) { return false; }
+        seen[k] = true;
+    }
+    return true;
+}
+
 int upload_tables(mrt_handle *h, const mrt_render_desc &rd, const mrt_sampler_tables *tb) {
     cudaStream_t st = h->stream;
     std::vector<float> tile, shader, sh, smt, spcg;
@@ -378,7 +401,10 @@ int upload_tables(mrt_handle *h, const mrt_render_desc &rd, const mrt_sampler_ta
                   : ps == MRT_SAMPLER_STATIC_MT ? h->d_static_mt.as<float>()
                   : ps == MRT_SAMPLER_STATIC_PCG ? h->d_static_pcg.as<float>() : nullptr;
     // from here on `static_halton` is the table of the area lights' and the russian roulette's samplers
-    if (rd.light_sampler == MRT_SAMPLER_STATIC_PCG) { s.static_halton = h->d_static_pcg.as<float>(); }
+    s.shader_table_is_perm = is_permutation_of_dyadic_grid(p_shader) ? 1 : 0;
+    s.static_halton_is_perm = is_permutation_of_dyadic_grid(p_sh) ? 1 : 0;
+    if (std::getenv("MRT_B200_TABLE_GATHER")) { s.shader_table_is_perm = 0; s.static_halton_is_perm = 0; }   // A/B: always read the tables
+    if (rd.light_sampler == MRT_SAMPLER_STATIC_PCG) { s.static_halton = h->d_static_pcg.as<float>(); s.static_halton_is_perm = 0; }
     return MRT_OK;
 }
 
@@ -791,7 +817,6 @@ struct TmpDev {
         return e;
     }
 };
-#define TEST_CUDA(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { return cuda_fail(nullptr, e_, #x); } } while (0)
 }  // namespace
 
 extern "C" {
@@ -873,78 +898,6 @@ int mrt_shade_rays(mrt_handle *h, int64_t n, const float *origins, const float *
     API_CUDA(h, launch_shade_rays(h->scene, h->rp, n, d_o, d_d, depth, d_rgb, h->d_counters.as<DeviceCounters>(), st));
     API_CUDA(h, cudaMemcpyAsync(out_rgb, d_rgb, 3 * N * 4, cudaMemcpyDeviceToHost, st));
     API_CUDA(h, cudaStreamSynchronize(st));
-    errno = 0;
-    return MRT_OK;
-}
-
-int mrt_test_triangle_intersect(const mrt_triangle *tri, const float *o, const float *d, float t_max, int32_t self_skip,
-                                float *out_t, float *out8) {
-    if (!tri || !o || !d || !out_t) { return fail(nullptr, MRT_ERR_INVALID, "null argument"); }
-    TmpDev tmp;
-    float *d_tri, *d_o, *d_d, *d_out;
-    TEST_CUDA(tmp.put(&d_tri, reinterpret_cast<const float *>(tri), 25, nullptr));
-    TEST_CUDA(tmp.put(&d_o, o, 3, nullptr)); TEST_CUDA(tmp.put(&d_d, d, 3, nullptr)); TEST_CUDA(tmp.get(&d_out, 9));
-    TEST_CUDA(launch_test_triangle(d_tri, d_o, d_d, t_max, self_skip, d_out, nullptr));
-    float out[9];
-    TEST_CUDA(cudaMemcpy(out, d_out, sizeof(out), cudaMemcpyDeviceToHost));
-    *out_t = out[0];
-    if (out8) { std::memcpy(out8, out + 1, 8 * sizeof(float)); }
-    errno = 0;
-    return MRT_OK;
-}
-int mrt_test_sphere_intersect(const mrt_sphere *s, const float *o, const float *d, float t_max, float *out_t, float *out_normal) {
-    if (!s || !o || !d || !out_t) { return fail(nullptr, MRT_ERR_INVALID, "null argument"); }
-    TmpDev tmp;
-    float *d_s, *d_o, *d_d, *d_out;
-    const float s4[4] = {s->center[0], s->center[1], s->center[2], s->sq_radius};
-    TEST_CUDA(tmp.put(&d_s, s4, 4, nullptr)); TEST_CUDA(tmp.put(&d_o, o, 3, nullptr)); TEST_CUDA(tmp.put(&d_d, d, 3, nullptr)); TEST_CUDA(tmp.get(&d_out, 4));
-    TEST_CUDA(launch_test_sphere(d_s, d_o, d_d, t_max, d_out, nullptr));
-    float out[4];
-    TEST_CUDA(cudaMemcpy(out, d_out, sizeof(out), cudaMemcpyDeviceToHost));
-    *out_t = out[0];
-    if (out_normal) { std::memcpy(out_normal, out + 1, 3 * sizeof(float)); }
-    errno = 0;
-    return MRT_OK;
-}
-int mrt_test_plane_intersect(const mrt_plane *p, const float *o, const float *d, float t_max, float *out_t) {
-    if (!p || !o || !d || !out_t) { return fail(nullptr, MRT_ERR_INVALID, "null argument"); }
-    TmpDev tmp;
-    float *d_p, *d_o, *d_d, *d_out;
-    const float p6[6] = {p->normal[0], p->normal[1], p->normal[2], p->point[0], p->point[1], p->point[2]};
-    TEST_CUDA(tmp.put(&d_p, p6, 6, nullptr)); TEST_CUDA(tmp.put(&d_o, o, 3, nullptr)); TEST_CUDA(tmp.put(&d_d, d, 3, nullptr)); TEST_CUDA(tmp.get(&d_out, 1));
-    TEST_CUDA(launch_test_plane(d_p, d_o, d_d, t_max, d_out, nullptr));
-    TEST_CUDA(cudaMemcpy(out_t, d_out, sizeof(float), cudaMemcpyDeviceToHost));
-    errno = 0;
-    return MRT_OK;
-}
-int mrt_test_aabb_intersect(const float *box_min, const float *box_max, const float *o, const float *d, int32_t *out_hit) {
-    if (!box_min || !box_max || !o || !d || !out_hit) { return fail(nullptr, MRT_ERR_INVALID, "null argument"); }
-    TmpDev tmp;
-    float *d_b, *d_o, *d_d; int32_t *d_out;
-    const float b6[6] = {box_min[0], box_min[1], box_min[2], box_max[0], box_max[1], box_max[2]};
-    TEST_CUDA(tmp.put(&d_b, b6, 6, nullptr)); TEST_CUDA(tmp.put(&d_o, o, 3, nullptr)); TEST_CUDA(tmp.put(&d_d, d, 3, nullptr)); TEST_CUDA(tmp.get(&d_out, 1));
-    TEST_CUDA(launch_test_aabb(d_b, d_o, d_d, d_out, nullptr));
-    TEST_CUDA(cudaMemcpy(out_hit, d_out, sizeof(int32_t), cudaMemcpyDeviceToHost));
-    errno = 0;
-    return MRT_OK;
-}
-int mrt_test_incremental_avg(const float *rgb, int32_t avg, int32_t num_sample, int32_t *out) {
-    if (!rgb || !out || num_sample <= 0) { return fail(nullptr, MRT_ERR_INVALID, "bad argument"); }
-    TmpDev tmp;
-    float *d_rgb; int32_t *d_out;
-    TEST_CUDA(tmp.put(&d_rgb, rgb, 3, nullptr)); TEST_CUDA(tmp.get(&d_out, 1));
-    TEST_CUDA(launch_test_incavg(d_rgb, avg, num_sample, d_out, nullptr));
-    TEST_CUDA(cudaMemcpy(out, d_out, sizeof(int32_t), cudaMemcpyDeviceToHost));
-    errno = 0;
-    return MRT_OK;
-}
-int mrt_test_halton(uint32_t first, int64_t n, uint32_t base, float *out) {
-    if (!out || n < 0 || base < 2) { return fail(nullptr, MRT_ERR_INVALID, "bad argument"); }
-    TmpDev tmp;
-    float *d_out;
-    TEST_CUDA(tmp.get(&d_out, static_cast<size_t>(n)));
-    TEST_CUDA(launch_test_halton(first, n, base, d_out, nullptr));
-    TEST_CUDA(cudaMemcpy(out, d_out, static_cast<size_t>(n) * sizeof(float), cudaMemcpyDeviceToHost));
     errno = 0;
     return MRT_OK;
 }

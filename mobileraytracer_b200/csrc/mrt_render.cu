@@ -137,48 +137,6 @@ __global__ void __launch_bounds__(128) k_shade_rays(SceneDev s, RenderParams rp,
     if (overflow) { dc->overflow = 1; }
 }
 
-// ---- one-thread test kernels ----------------------------------------------------------------------------------
-__global__ void k_test_triangle(const float *t, const float *o, const float *d, float tmax, int self_skip, float *out) {
-    // t = the reference's 100-byte record: AC, AB, A, nA, nB, nC, tA, tB, tC, mat
-    const v3 AC = mk3(t[0], t[1], t[2]), AB = mk3(t[3], t[4], t[5]), A = mk3(t[6], t[7], t[8]);
-    const v3 ro = mk3(o[0], o[1], o[2]), rd = mk3(d[0], d[1], d[2]);
-    float tt, u, v;
-    out[0] = tmax;
-    out[1] = 0.0f; out[2] = 1.0f; out[3] = 0.0f; out[4] = -1.0f; out[5] = -1.0f; out[6] = 0.0f; out[7] = 0.0f; out[8] = 0.0f;
-    if (self_skip) { return; }
-    if (triangle_intersect(A, AB, AC, ro, rd, tt, u, v) && tt < tmax) {
-        const float w = 1.0f - u - v;
-        const v3 nA = mk3(t[9], t[10], t[11]), nB = mk3(t[12], t[13], t[14]), nC = mk3(t[15], t[16], t[17]);
-        const v3 nrm = normalize((nA * w + nB * u) + nC * v);
-        const v3 p = ro + rd * tt;
-        out[0] = tt; out[1] = nrm.x; out[2] = nrm.y; out[3] = nrm.z;
-        out[4] = (t[18] * w + t[20] * u) + t[22] * v; out[5] = (t[19] * w + t[21] * u) + t[23] * v;
-        out[6] = p.x; out[7] = p.y; out[8] = p.z;
-    }
-}
-__global__ void k_test_sphere(const float *s4, const float *o, const float *d, float tmax, float *out) {
-    const v3 ro = mk3(o[0], o[1], o[2]), rd = mk3(d[0], d[1], d[2]), c = mk3(s4[0], s4[1], s4[2]);
-    float t;
-    out[0] = tmax; out[1] = 0.0f; out[2] = 1.0f; out[3] = 0.0f;
-    if (sphere_intersect(c, s4[3], ro, rd, t) && t < tmax) {
-        const v3 n = normalize((ro + rd * t) - c);
-        out[0] = t; out[1] = n.x; out[2] = n.y; out[3] = n.z;
-    }
-}
-__global__ void k_test_plane(const float *p6, const float *o, const float *d, float tmax, float *out) {
-    float t;
-    out[0] = tmax;
-    if (plane_intersect(mk3(p6[0], p6[1], p6[2]), mk3(p6[3], p6[4], p6[5]), mk3(o[0], o[1], o[2]), mk3(d[0], d[1], d[2]), t) && t < tmax) { out[0] = t; }
-}
-__global__ void k_test_aabb(const float *b, const float *o, const float *d, int32_t *out) {
-    out[0] = aabb_intersect_exact(mk3(b[0], b[1], b[2]), mk3(b[3], b[4], b[5]), mk3(o[0], o[1], o[2]), mk3(d[0], d[1], d[2])) ? 1 : 0;
-}
-__global__ void k_test_incavg(const float *rgb, int32_t avg, int32_t n, int32_t *out) { out[0] = incremental_avg(mk3(rgb[0], rgb[1], rgb[2]), avg, n); }
-__global__ void k_test_halton(uint32_t first, int64_t n, uint32_t base, float *out) {
-    const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
-    if (i < n) { out[i] = halton_sequence(first + static_cast<uint32_t>(i), base); }
-}
-
 // ---- launchers ------------------------------------------------------------------------------------------------
 cudaError_t launch_render_sample(const SceneDev &s, const CameraRec &cam, const RenderParams &rp, const int2 *d_tile_origin,
                                  int sample, int avg_n, FrameTargets tg, DeviceCounters *dc, cudaStream_t st, ReplayArgs rep) {
@@ -221,24 +179,4 @@ cudaError_t launch_shade_rays(const SceneDev &s, const RenderParams &rp, int64_t
     }
     return cudaGetLastError();
 }
-cudaError_t launch_test_triangle(const float *tri25, const float *o, const float *d, float tmax, int self_skip, float *out9, cudaStream_t st) {
-    k_test_triangle<<<1, 1, 0, st>>>(tri25, o, d, tmax, self_skip, out9); return cudaGetLastError();
-}
-cudaError_t launch_test_sphere(const float *sph4, const float *o, const float *d, float tmax, float *out4, cudaStream_t st) {
-    k_test_sphere<<<1, 1, 0, st>>>(sph4, o, d, tmax, out4); return cudaGetLastError();
-}
-cudaError_t launch_test_plane(const float *pl6, const float *o, const float *d, float tmax, float *out1, cudaStream_t st) {
-    k_test_plane<<<1, 1, 0, st>>>(pl6, o, d, tmax, out1); return cudaGetLastError();
-}
-cudaError_t launch_test_aabb(const float *box6, const float *o, const float *d, int32_t *out, cudaStream_t st) {
-    k_test_aabb<<<1, 1, 0, st>>>(box6, o, d, out); return cudaGetLastError();
-}
-cudaError_t launch_test_incavg(const float *rgb, int32_t avg, int32_t n, int32_t *out, cudaStream_t st) {
-    k_test_incavg<<<1, 1, 0, st>>>(rgb, avg, n, out); return cudaGetLastError();
-}
-cudaError_t launch_test_halton(uint32_t first, int64_t n, uint32_t base, float *out, cudaStream_t st) {
-    if (n == 0) { return cudaSuccess; }
-    k_test_halton<<<static_cast<unsigned>((n + 255) / 256), 256, 0, st>>>(first, n, base, out); return cudaGetLastError();
-}
-
 }  // namespace mrt

@@ -38,12 +38,4 @@ cudaError_t launch_generate_rays(const CameraRec &cam, int64_t n, const float *u
 cudaError_t launch_shade_rays(const SceneDev &s, const RenderParams &rp, int64_t n, const float *o, const float *d, int depth,
                               float *rgb, DeviceCounters *d_counters, cudaStream_t st);
 
-// one-thread kernels behind the mrt_test_* entry points; all pointers are device pointers
-cudaError_t launch_test_triangle(const float *tri25, const float *o, const float *d, float tmax, int self_skip, float *out9, cudaStream_t st);
-cudaError_t launch_test_sphere(const float *sph4, const float *o, const float *d, float tmax, float *out4, cudaStream_t st);
-cudaError_t launch_test_plane(const float *pl6, const float *o, const float *d, float tmax, float *out1, cudaStream_t st);
-cudaError_t launch_test_aabb(const float *box6, const float *o, const float *d, int32_t *out, cudaStream_t st);
-cudaError_t launch_test_incavg(const float *rgb, int32_t avg, int32_t n, int32_t *out, cudaStream_t st);
-cudaError_t launch_test_halton(uint32_t first, int64_t n, uint32_t base, float *out, cudaStream_t st);
-
 }  // namespace mrt

@@ -101,9 +101,10 @@ struct Surface {
     int32_t skipKind, skipIdx;   // the primitive a ray leaving this surface must skip (Ray::primitive_)
 };
 
-MRT_D void load_material(const SceneDev &s, int m, Surface &sf) {
-    const float4 *mp = reinterpret_cast<const float4 *>(s.materials + m);
-    const float4 a = __ldg(mp), b = __ldg(mp + 1), c = __ldg(mp + 2), d = __ldg(mp + 3);
+// matp: the material records as float4 quadruples, in global or (wavefront shade kernel) shared memory
+MRT_D void load_material(const float4 *matp, int m, Surface &sf) {
+    const float4 *mp = matp + 4 * m;
+    const float4 a = mp[0], b = mp[1], c = mp[2], d = mp[3];
     sf.Le = mk3(a.x, a.y, a.z); sf.Kd = mk3(a.w, b.x, b.y); sf.Ks = mk3(b.z, b.w, c.x); sf.Kt = mk3(c.y, c.z, c.w); sf.ior = d.x;
     sf.texture = __float_as_int(d.y);
 }
@@ -123,7 +124,9 @@ MRT_D v3 texture_load_color(const SceneDev &s, int tex, float tu, float tv) {
 
 // What the primitive's intersect() stores in the Intersection (Triangle.cpp:100-108, Sphere.cpp:69-78, Plane.cpp:64-70)
 // plus Shader::rayTrace's material lookup (Shader.cpp:112-121; AreaLight.cpp:32-41 for lights).
-MRT_D void resolve_surface(const SceneDev &s, v3 o, v3 d, const HitRec &h, Surface &sf) {
+MRT_D void resolve_surface(const SceneDev &s, v3 o, v3 d, const HitRec &h, Surface &sf, const float4 *matp = nullptr, const float4 *lightp = nullptr) {
+    if (matp == nullptr) { matp = reinterpret_cast<const float4 *>(s.materials); }
+    if (lightp == nullptr) { lightp = reinterpret_cast<const float4 *>(s.lights); }
     sf.point = o + d * h.t;
     sf.skipKind = HIT_NONE; sf.skipIdx = -1;
     if (h.kind == HIT_TRIANGLE) {
@@ -132,7 +135,7 @@ MRT_D void resolve_surface(const SceneDev &s, v3 o, v3 d, const HitRec &h, Surfa
         const float w = 1.0f - h.u - h.v;
         const v3 nA = mk3(s0.x, s0.y, s0.z), nB = mk3(s0.w, s1.x, s1.y), nC = mk3(s1.z, s1.w, s2.x);
         sf.normal = normalize((nA * w + nB * h.u) + nC * h.v);
-        load_material(s, __float_as_int(s3.w), sf);
+        load_material(matp, __float_as_int(s3.w), sf);
         if (sf.texture >= 0) {
             // Triangle.cpp:98 texCoords = tA * w + tB * u + tC * v; Shader.cpp:116-120: both >= 0 -> Kd comes from the texture
             const float tu = (s2.y * w + s2.w * h.u) + s3.y * h.v, tv = (s2.z * w + s3.x * h.u) + s3.z * h.v;
@@ -142,17 +145,18 @@ MRT_D void resolve_surface(const SceneDev &s, v3 o, v3 d, const HitRec &h, Surfa
     } else if (h.kind == HIT_SPHERE) {
         const SphereRec sp = s.spheres[h.idx];
         sf.normal = normalize(sf.point - mk3(sp.cx, sp.cy, sp.cz));
-        load_material(s, sp.material, sf);
+        load_material(matp, sp.material, sf);
     } else if (h.kind == HIT_PLANE) {
         const PlaneRec p = s.planes[h.idx];
         sf.normal = mk3(p.nx, p.ny, p.nz);
-        load_material(s, p.material, sf);
+        load_material(matp, p.material, sf);
         sf.skipKind = HIT_PLANE; sf.skipIdx = h.idx;
     } else {  // HIT_LIGHT: material = the light's radiance_ (Le only)
-        const LightRec &l = s.lights[h.idx];
+        // LightRec as four float4: kind A.xyz | AB.xyz AC.x | AC.yz Le.xy | Le.z - - -
+        const float4 l1 = lightp[4 * h.idx + 1], l2 = lightp[4 * h.idx + 2], l3 = lightp[4 * h.idx + 3];
         // the light triangle's face normal (Triangle::Builder, Triangle.cpp:328-340); no shader reads it: Le > 0 ends the path
-        sf.normal = normalize(normalize(cross(mk3(l.AC[0], l.AC[1], l.AC[2]), mk3(l.AB[0], l.AB[1], l.AB[2]))));
-        sf.Le = mk3(l.Le[0], l.Le[1], l.Le[2]);
+        sf.normal = normalize(normalize(cross(mk3(l1.w, l2.x, l2.y), mk3(l1.x, l1.y, l1.z))));
+        sf.Le = mk3(l2.z, l2.w, l3.x);
         sf.Kd = sf.Ks = sf.Kt = mk3(0.0f, 0.0f, 0.0f);
         sf.ior = 1.0f;
     }

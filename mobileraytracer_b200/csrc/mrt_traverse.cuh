@@ -169,6 +169,21 @@ MRT_D bool child_hit(uint32_t nx, uint32_t ny, uint32_t nz, uint32_t fx, uint32_
     return tmin <= tmax;
 }
 
+#ifdef MRT_SIGN_PACK
+// The same test as a number: tmax - tmin, whose sign bit is clear exactly when the child is hit (x - x is +0; all operands are
+// finite, see rcp_robust). The caller shifts the eight sign bits into one word with one funnel shift each, which replaces
+// FSETP + a predicated add per child (both on the ALU pipe that bounds the traversal kernels) by FADD (FMA pipe) + SHF.
+template <int B>
+MRT_D uint32_t child_gap(uint32_t nx, uint32_t ny, uint32_t nz, uint32_t fx, uint32_t fy, uint32_t fz, float ax, float ay, float az,
+                         float ox0, float oy0, float oz0, float ox1, float oy1, float oz1, float tbest, uint32_t one) {
+    const float t0x = __fmaf_rn(u8_to_unit<B>(nx, one), ax, ox0), t0y = __fmaf_rn(u8_to_unit<B>(ny, one), ay, oy0), t0z = __fmaf_rn(u8_to_unit<B>(nz, one), az, oz0);
+    const float t1x = __fmaf_rn(u8_to_unit<B>(fx, one), ax, ox1), t1y = __fmaf_rn(u8_to_unit<B>(fy, one), ay, oy1), t1z = __fmaf_rn(u8_to_unit<B>(fz, one), az, oz1);
+    const float tmin = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, 0.0f));
+    const float tmax = fminf(fminf(t1x, t1y), fminf(t1z, tbest));
+    return __float_as_uint(tmax - tmin);
+}
+#endif
+
 // Visits the next pending inner node of t.ngroup: afterwards t.ngroup holds that node's hit children and
 // `tnew` the hit leaf triangles (the previous group, if it still has pending nodes, goes to the stack).
 //
@@ -216,6 +231,17 @@ MRT_D bool trav8_node_core(const SceneDev &s, Trav8 &t, TravMem &tm_, uint32_t &
     const uint32_t ny0 = fy_ ? qhy0 : qly0, ny1 = fy_ ? qhy1 : qly1, fy0 = fy_ ? qly0 : qhy0, fy1 = fy_ ? qly1 : qhy1;
     const uint32_t nz0 = fz_ ? qhz0 : qlz0, nz1 = fz_ ? qhz1 : qlz1, fz0 = fz_ ? qlz0 : qhz0, fz1 = fz_ ? qlz1 : qhz1;
     const uint32_t imask = e >> 24;
+#ifdef MRT_SIGN_PACK
+    uint32_t miss = 0u;   // child 7 first, so that child k ends up in bit k
+#define MRT_CHILD(B, NX, NY, NZ, FX, FY, FZ) \
+    miss = __funnelshift_l(child_gap<B>(NX, NY, NZ, FX, FY, FZ, ax, ay, az, ox0, oy0, oz0, ox1, oy1, oz1, t.tbest, one), miss, 1);
+    MRT_CHILD(3, nx1, ny1, nz1, fx1, fy1, fz1) MRT_CHILD(2, nx1, ny1, nz1, fx1, fy1, fz1)
+    MRT_CHILD(1, nx1, ny1, nz1, fx1, fy1, fz1) MRT_CHILD(0, nx1, ny1, nz1, fx1, fy1, fz1)
+    MRT_CHILD(3, nx0, ny0, nz0, fx0, fy0, fz0) MRT_CHILD(2, nx0, ny0, nz0, fx0, fy0, fz0)
+    MRT_CHILD(1, nx0, ny0, nz0, fx0, fy0, fz0) MRT_CHILD(0, nx0, ny0, nz0, fx0, fy0, fz0)
+#undef MRT_CHILD
+    const uint32_t hits = ~miss & 0xffu;   // bit k: child slot k is hit
+#else
     uint32_t hits = 0u;   // bit k: child slot k is hit
 #define MRT_CHILD(B, NX, NY, NZ, FX, FY, FZ, K) \
     if (child_hit<B>(NX, NY, NZ, FX, FY, FZ, ax, ay, az, ox0, oy0, oz0, ox1, oy1, oz1, t.tbest, one)) { hits |= 1u << (K); }
@@ -224,6 +250,7 @@ MRT_D bool trav8_node_core(const SceneDev &s, Trav8 &t, TravMem &tm_, uint32_t &
     MRT_CHILD(0, nx1, ny1, nz1, fx1, fy1, fz1, 4) MRT_CHILD(1, nx1, ny1, nz1, fx1, fy1, fz1, 5)
     MRT_CHILD(2, nx1, ny1, nz1, fx1, fy1, fz1, 6) MRT_CHILD(3, nx1, ny1, nz1, fx1, fy1, fz1, 7)
 #undef MRT_CHILD
+#endif
     // inner children: bit (slot ^ octinv), so that the highest pending bit is always the nearest child along the ray
     // (slot s of a node holds the child lying towards +axis k for every set bit k of s, see k_collapse8)
     uint32_t in = hits & imask;

@@ -75,6 +75,9 @@ struct SceneDev {
     int32_t naive;               // 1: Naive accelerator semantics (no triangle root-box test; planes / spheres behind an unbounded box)
     uint32_t prmt_one;           // 0x3F800000, deliberately a run-time value (mrt_traverse.cuh, u8_to_unit)
     const float *pixel_table;    // table the pixel sampler reads (static_halton or static_mt), or null for Constant
+    // 1: the table is a permutation of {k / 2^20} (what fillArrayWithHaltonSeq + std::shuffle produce, Utils.hpp:209-218), so the
+    // value of a uniformly chosen slot can be computed instead of gathered (wavefront path tracer, mrt_wavefront.cu pt_draw)
+    int32_t shader_table_is_perm, static_halton_is_perm;
 };
 
 struct RenderParams {

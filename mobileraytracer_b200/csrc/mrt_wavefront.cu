@@ -27,7 +27,7 @@ constexpr int kWfThreads = 128;
 #define MRT_TRAV_MIN_BLOCKS 8     // CTAs per SM of the persistent traversal kernels (64 registers per thread)
 #endif
 #ifndef MRT_SHADE_MIN_BLOCKS
-#define MRT_SHADE_MIN_BLOCKS 8
+#define MRT_SHADE_MIN_BLOCKS 3    // CTAs of 256 threads per SM of the shade kernel: 80 registers per thread (4 CTAs = 64 registers spilled: +37 %; 2 CTAs: +24 %; 1: 2.2x, profiles/r2_ab_shade.txt)
 #endif
 
 // One sector per chain. info: bits 0..2 = j* (0: no vertex had direct light yet), bit 3 = ended on an emitter,
@@ -82,17 +82,6 @@ MRT_D void acc_init(PathAcc *a, v3 pre, uint32_t info, int32_t parent) {
 
 MRT_D uint32_t pack_skip(int kind, int idx) { return kind == HIT_NONE ? 0u : (static_cast<uint32_t>(kind) << 28) | (static_cast<uint32_t>(idx) & 0x0fffffffu); }
 MRT_D void unpack_skip(uint32_t s, int &kind, int &idx) { kind = static_cast<int>(s >> 28); idx = kind == HIT_NONE ? -1 : static_cast<int>(s & 0x0fffffffu); }
-
-// warp-aggregated slot allocation: one atomic per warp per push site
-MRT_D uint32_t queue_push(uint32_t *counter) {
-    const uint32_t mask = __activemask();
-    const int lane = threadIdx.x & 31;
-    const int leader = __ffs(mask) - 1;
-    uint32_t base = 0;
-    if (lane == leader) { base = atomicAdd(counter, static_cast<uint32_t>(__popc(mask))); }
-    base = __shfl_sync(mask, base, leader);
-    return base + __popc(mask & ((1u << lane) - 1u));
-}
 
 // ---- generate: Renderer::renderScene's jitter + Camera::generateRay (Renderer.cpp:130-141) ---------------------------
 __global__ void __launch_bounds__(kWfThreads) k_wf_generate(Queues Q, SceneDev s, CameraRec cam, RenderParams rp,
@@ -337,7 +326,9 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
             }
             hasmask &= ~done;
         }
-        // refill the idle lanes
+        // refill the idle lanes (one warp-aggregated atomicAdd on the level's work counter per refill; handing every warp chunks
+        // of 32-128 rays per atomicAdd instead was measured slower, shadow +5 %, extend +1 %: a chunk that runs out in the middle
+        // of a refill leaves lanes idle until the next one)
         if (refill_now) {
             const uint32_t idle = ~hasmask;
             uint32_t base = 0;
@@ -468,139 +459,220 @@ MRT_D v3 cosine_sample_hemisphere(v3 normal, float uniformRandom1, float uniform
 // Where a draw of the reference's tables comes from (Shader.cpp:188-233, Sampler.hpp:58-63, PathTracer.cpp:91): the
 // reference hands out table[counter++] in execution order, which no parallel schedule can replay for a path tracer
 // (SURVEY H2), so every (pixel-sample q, vertex `branch`, ordinal, stream) reads its own decorrelated slot of the SAME
-// tables. The ordinals are fixed per vertex, independent of control flow, so that all table loads of a vertex can be
-// issued before the hit record has arrived (the shade kernel is latency bound: profiles/r1_shade_s40).
-MRT_D uint32_t pt_slot(uint32_t q, uint32_t e, uint32_t stream, uint32_t seed) { return hash_u32(q, e, stream ^ seed) & kArrayMask; }
+// tables. The ordinals are fixed per vertex, independent of control flow.
+// The tables are shuffles of the radical inverses of 0 .. 2^20 - 1, i.e. permutations of {k / 2^20}; the value found in a
+// uniformly chosen slot is therefore k / 2^20 for a uniformly chosen k, and is computed instead of gathered when the host
+// has verified that property (SceneDev::*_is_perm). Six 4-byte gathers per hit cost six 32-byte sectors of L2 -> L1
+// traffic, 40 % of what the shade kernel moved while it ran at 73 % of the measured L2 gather peak (profiles/).
+MRT_D float pt_draw(const float *__restrict__ table, int is_perm, uint32_t q, uint32_t e, uint32_t stream, uint32_t seed) {
+    const uint32_t i = hash_u32(q, e, stream ^ seed) & kArrayMask;
+    // k / 2^20 without an integer-to-float conversion (I2F runs on the quarter-rate XU pipe): 1.mantissa - 1
+    return is_perm ? __uint_as_float(0x3F800000u | (i << 3)) - 1.0f : __ldg(table + i);
+}
 
+constexpr int kShadeThreads = 256;
+constexpr int kShadeMatCap = 64, kShadeLightCap = 256;   // records staged in shared memory (64 bytes each); larger scenes read them from global memory
+
+// One light sample of a vertex (PathTracer.cpp:60-82): Shader::getLightIndex (Shader.cpp:223-233), then
+// PointLight::getPosition (PointLight.cpp:16-18) or AreaLight::getPosition (AreaLight.cpp:17-26). True when the light point
+// lies in front of the surface, i.e. when the reference casts the shadow ray.
+struct LightSample { v3 dir; float dist; v3 ld; };
+MRT_D bool pt_light_sample(const SceneDev &s, const RenderParams &rp, const float4 *lightp, const Surface &sf, uint32_t q, uint32_t eb, uint32_t k,
+                           LightSample &ls) {
+    const float rl = pt_draw(s.shader_table, s.shader_table_is_perm, q, eb + k, DS_LIGHT_INDEX, rp.seed);
+    const uint32_t chosen = static_cast<uint32_t>(floorf(rl * static_cast<float>(static_cast<uint32_t>(s.n_lights)) * 0.99999f));
+    // LightRec as four float4: kind A.xyz | AB.xyz AC.x | AC.yz Le.xy | Le.z - - -
+    const float4 l0 = lightp[4u * chosen], l1 = lightp[4u * chosen + 1u], l2 = lightp[4u * chosen + 2u], l3 = lightp[4u * chosen + 3u];
+    v3 lightPosition = mk3(l0.y, l0.z, l0.w);
+    if (__float_as_int(l0.x) != 0) {
+        float r = pt_draw(s.static_halton, s.static_halton_is_perm, q, eb + 2u * k, DS_LIGHT_POS, rp.seed);
+        float g = pt_draw(s.static_halton, s.static_halton_is_perm, q, eb + 2u * k + 1u, DS_LIGHT_POS, rp.seed);
+        if (r + g >= 1.0f) { r = 1.0f - r; g = 1.0f - g; }
+        lightPosition = (lightPosition + r * mk3(l1.x, l1.y, l1.z)) + g * mk3(l1.w, l2.x, l2.y);
+    }
+    v3 vectorToLight = lightPosition - sf.point;
+    ls.dist = length(vectorToLight);
+    ls.dir = normalize(vectorToLight);
+    const float cosNormalLight = dot(sf.normal, ls.dir);
+    // Ld's share of this light sample: (Le * cos) * kD / samplesLight
+    ls.ld = ((mk3(l2.z, l2.w, l3.x) * cosNormalLight) * sf.Kd) / static_cast<float>(rp.spl);
+    return cosNormalLight > 0.0f;
+}
+
+// Queue slots are handed out per CTA: every thread first decides what its hit emits (phase 1), a block-wide prefix sum turns
+// the counts into offsets and ONE thread per queue bumps the global counter for all 256 hits, then the records are written
+// (phase 2). With one warp-aggregated atomicAdd per push site the kernel spent 48 % of its stall samples waiting for the two
+// same-address atomics of the shadow and ray queues (2 M per 33 M-hit launch, about 0.7 ns each at the L2;
+// profiles/r2_shade_before_ncu_summary.txt). Consecutive hits now also get consecutive slots.
 template <bool L0>
-__global__ void __launch_bounds__(kWfThreads, MRT_SHADE_MIN_BLOCKS) k_wf_shade(SceneDev s, RenderParams rp, Queues Q, int level, DeviceCounters *dc) {
+__global__ void __launch_bounds__(kShadeThreads, MRT_SHADE_MIN_BLOCKS) k_wf_shade(SceneDev s, RenderParams rp, Queues Q, int level, DeviceCounters *dc) {
+    // materials and lights: a few KB that every hit needs; out of shared memory instead of 2 x 64 bytes of L2 -> L1 traffic per hit
+    __shared__ float4 sm_mat[kShadeMatCap * 4];
+    __shared__ float4 sm_light[kShadeLightCap * 4];
+    __shared__ unsigned long long sm_warp[kShadeThreads / 32];   // per warp: shadow rays | rays << 24 | chains << 44 of this iteration
+    __shared__ uint32_t sm_base[3];
+    const bool mat_sh = s.n_materials <= kShadeMatCap, light_sh = s.n_lights <= kShadeLightCap;
+    if (mat_sh) { for (int k = threadIdx.x; k < s.n_materials * 4; k += kShadeThreads) { sm_mat[k] = __ldg(reinterpret_cast<const float4 *>(s.materials) + k); } }
+    if (light_sh) { for (int k = threadIdx.x; k < s.n_lights * 4; k += kShadeThreads) { sm_light[k] = __ldg(reinterpret_cast<const float4 *>(s.lights) + k); } }
+    __syncthreads();
+    const float4 *matp = mat_sh ? sm_mat : reinterpret_cast<const float4 *>(s.materials);
+    const float4 *lightp = light_sh ? sm_light : reinterpret_cast<const float4 *>(s.lights);
     const int b = level & 1, nb = b ^ 1;
     const uint32_t n = min(Q.counts[level], Q.cap_rays);
     const uint32_t stride = gridDim.x * blockDim.x;
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
     RayCounters rc = {0u, 0u, 0u};
     int overflow = 0;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        // the records of this thread's next iteration start their trip from HBM to L2 now
-        if (i + stride < n) {
-            asm volatile("prefetch.global.L2 [%0];" :: "l"(Q.hit + i + stride));
-            asm volatile("prefetch.global.L2 [%0];" :: "l"(Q.r0[b] + i + stride));
-            asm volatile("prefetch.global.L2 [%0];" :: "l"(Q.r1[b] + i + stride));
-            if (!L0) {
-                asm volatile("prefetch.global.L2 [%0];" :: "l"(Q.r2[b] + i + stride));
-                asm volatile("prefetch.global.L2 [%0];" :: "l"(Q.r3[b] + i + stride));
-            }
-        }
-        // hit and ray records are independent loads: issue all of them before the first use
-        const float4 hq = Q.hit[i];
-        const float4 a = Q.r0[b][i], c1 = Q.r1[b][i];
-        float4 c2 = make_float4(1.0f, 1.0f, 1.0f, 0.0f), c3 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-        if (!L0) { c2 = Q.r2[b][i]; c3 = Q.r3[b][i]; }
-        const uint32_t q = __float_as_uint(L0 ? c1.z : c3.x), branch = L0 ? 1u : __float_as_uint(c3.y);
-        const int depth = L0 ? 1 : __float_as_int(c1.w);
-        const uint32_t chain = L0 ? i : __float_as_uint(c2.w);
-        // the vertex's draws: light sample 0 (index, two position coordinates), russian roulette, hemisphere
-        const uint32_t eb = branch << 6;
-        const float r_li = __ldg(s.shader_table + pt_slot(q, eb, DS_LIGHT_INDEX, rp.seed));
-        const float r_p0 = __ldg(s.static_halton + pt_slot(q, eb, DS_LIGHT_POS, rp.seed));
-        const float r_p1 = __ldg(s.static_halton + pt_slot(q, eb + 1u, DS_LIGHT_POS, rp.seed));
-        const float r_rr = __ldg(s.static_halton + pt_slot(q, eb, DS_RR, rp.seed));
-        const float r_h0 = __ldg(s.shader_table + pt_slot(q, eb, DS_HEMI, rp.seed));
-        const float r_h1 = __ldg(s.shader_table + pt_slot(q, eb + 1u, DS_HEMI, rp.seed));
-        const uint32_t packed = __float_as_uint(hq.w);
-        HitRec h;
-        h.t = hq.x; h.u = hq.y; h.v = hq.z; h.kind = static_cast<int>(packed >> 28); h.idx = static_cast<int>(packed & 0x0fffffffu);
-        const int32_t root_parent = L0 ? -1 - __float_as_int(c1.w) : 0;   // camera path: -1 - pixel
-        if (h.kind == HIT_NONE) {                                   // Shader.cpp:122: no intersection, rgb stays 0
-            if (L0) { acc_init(Q.acc + i, mk3(0.0f, 0.0f, 0.0f), 0u, root_parent); }
-            continue;
-        }
-        const v3 o = mk3(a.x, a.y, a.z), d = mk3(a.w, c1.x, c1.y), T = mk3(c2.x, c2.y, c2.z);
+    for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += stride) {   // the same trip count for every thread of the CTA
+        const uint32_t i = base + threadIdx.x;
+        // ---- phase 1: the surface, and how many shadow rays / rays / chains this hit emits
+        uint32_t ns = 0u, nr = 0u, nc = 0u;
+        bool shading = false, first_lit = false, go = false, spec = false, trans = false;
         Surface sf;
-        resolve_surface(s, o, d, h, sf);
-        PathAcc *ch = Q.acc + chain;
-        if (has_positive(sf.Le)) {                                  // PathTracer.cpp:28-33: stop on a light source
-            const v3 e = T * sf.Le;
-            if (L0) { acc_init(ch, e, kAccEnded, root_parent); }
-            else {
-                // the emitter term only counts while no vertex of the chain had direct light (PathTracer.cpp:107-110)
-                const uint32_t info = ch->info;
-                if ((info & kAccFirstMask) == 0u) { ch->pre[0] += e.x; ch->pre[1] += e.y; ch->pre[2] += e.z; }
-                ch->info = info | kAccEnded;
+        LightSample ls0;
+        v3 d = mk3(0.0f, 0.0f, 0.0f), T = mk3(1.0f, 1.0f, 1.0f);
+        uint32_t q = 0u, branch = 1u, chain = i, eb = 0u;
+        int depth = 1;
+        float r_h0 = 0.0f, r_h1 = 0.0f;
+        if (i < n) {
+            // the records of this thread's next iteration start their trip from HBM to L2 now
+            if (i + stride < n) {
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(Q.hit + i + stride));
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(Q.r0[b] + i + stride));
+                asm volatile("prefetch.global.L2 [%0];" :: "l"(Q.r1[b] + i + stride));
+                if (!L0) {
+                    asm volatile("prefetch.global.L2 [%0];" :: "l"(Q.r2[b] + i + stride));
+                    asm volatile("prefetch.global.L2 [%0];" :: "l"(Q.r3[b] + i + stride));
+                }
             }
-            continue;
+            // hit and ray records are independent loads: issue all of them before the first use
+            const float4 hq = Q.hit[i];
+            const float4 a = Q.r0[b][i], c1 = Q.r1[b][i];
+            float4 c2 = make_float4(1.0f, 1.0f, 1.0f, 0.0f), c3 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            if (!L0) { c2 = Q.r2[b][i]; c3 = Q.r3[b][i]; }
+            q = __float_as_uint(L0 ? c1.z : c3.x); branch = L0 ? 1u : __float_as_uint(c3.y);
+            depth = L0 ? 1 : __float_as_int(c1.w);
+            chain = L0 ? i : __float_as_uint(c2.w);
+            eb = branch << 6;
+            // the vertex's russian-roulette and hemisphere draws (table gathers, when they are gathers, go out before the hit is looked at)
+            const float r_rr = pt_draw(s.static_halton, s.static_halton_is_perm, q, eb, DS_RR, rp.seed);
+            r_h0 = pt_draw(s.shader_table, s.shader_table_is_perm, q, eb, DS_HEMI, rp.seed);
+            r_h1 = pt_draw(s.shader_table, s.shader_table_is_perm, q, eb + 1u, DS_HEMI, rp.seed);
+            const uint32_t packed = __float_as_uint(hq.w);
+            HitRec h;
+            h.t = hq.x; h.u = hq.y; h.v = hq.z; h.kind = static_cast<int>(packed >> 28); h.idx = static_cast<int>(packed & 0x0fffffffu);
+            const int32_t root_parent = L0 ? -1 - __float_as_int(c1.w) : 0;   // camera path: -1 - pixel
+            PathAcc *ch = Q.acc + chain;
+            if (h.kind == HIT_NONE) {                                   // Shader.cpp:122: no intersection, rgb stays 0
+                if (L0) { acc_init(ch, mk3(0.0f, 0.0f, 0.0f), 0u, root_parent); }
+            } else {
+                const v3 o = mk3(a.x, a.y, a.z);
+                d = mk3(a.w, c1.x, c1.y); T = mk3(c2.x, c2.y, c2.z);
+                resolve_surface(s, o, d, h, sf, matp, lightp);
+                if (has_positive(sf.Le)) {                              // PathTracer.cpp:28-33: stop on a light source
+                    const v3 e = T * sf.Le;
+                    if (L0) { acc_init(ch, e, kAccEnded, root_parent); }
+                    else {
+                        // the emitter term only counts while no vertex of the chain had direct light (PathTracer.cpp:107-110)
+                        const uint32_t info = ch->info;
+                        if ((info & kAccFirstMask) == 0u) { ch->pre[0] += e.x; ch->pre[1] += e.y; ch->pre[2] += e.z; }
+                        ch->info = info | kAccEnded;
+                    }
+                } else {
+                    if (L0) { acc_init(ch, mk3(0.0f, 0.0f, 0.0f), 0u, root_parent); }
+                    shading = true;
+                    const bool diffuse = has_positive(sf.Kd);
+                    if (diffuse && s.n_lights > 0) {                    // PathTracer.cpp:55-87: direct light, one shadow ray per light sample
+                        first_lit = pt_light_sample(s, rp, lightp, sf, q, eb, 0u, ls0);
+                        ns = first_lit ? 1u : 0u;
+                        for (int k = 1; k < rp.spl; ++k) {
+                            LightSample ls;
+                            if (pt_light_sample(s, rp, lightp, sf, q, eb, static_cast<uint32_t>(k), ls)) { ++ns; }
+                        }
+                        rc.shadow += ns;
+                    }
+                    const bool traceable = depth + 1 <= kRayDepthMax;   // deeper rays are constructed (counted) but add nothing
+                    go = diffuse && (depth <= kRayDepthMin || r_rr > 0.5f);   // PathTracer.cpp:89-91: russian roulette
+                    spec = has_positive(sf.Ks); trans = has_positive(sf.Kt);   // PathTracer.cpp:113-134
+                    rc.secondary += (go ? 1u : 0u) + (spec ? 1u : 0u) + (trans ? 1u : 0u);
+                    if (traceable) { nc = (spec ? 1u : 0u) + (trans ? 1u : 0u); nr = nc + (go ? 1u : 0u); }
+                    else { go = false; spec = false; trans = false; }
+                }
+            }
         }
-        if (L0) { acc_init(ch, mk3(0.0f, 0.0f, 0.0f), 0u, root_parent); }
-        const bool diffuse = has_positive(sf.Kd);
-        if (diffuse && s.n_lights > 0) {                            // PathTracer.cpp:55-87: direct light, one shadow ray per light sample
+        // ---- slots: prefix sums over the CTA, one atomicAdd per queue
+        unsigned long long mine = static_cast<unsigned long long>(ns) | (static_cast<unsigned long long>(nr) << 24) | (static_cast<unsigned long long>(nc) << 44);
+        unsigned long long incl = mine;
+#pragma unroll
+        for (int k = 1; k < 32; k <<= 1) {
+            const unsigned long long v = __shfl_up_sync(0xffffffffu, incl, k);
+            if (lane >= static_cast<uint32_t>(k)) { incl += v; }
+        }
+        if (lane == 31u) { sm_warp[warp] = incl; }
+        __syncthreads();
+        unsigned long long before = 0ull, total = 0ull;
+#pragma unroll
+        for (uint32_t wq = 0; wq < kShadeThreads / 32; ++wq) {
+            const unsigned long long v = sm_warp[wq];
+            total += v;
+            if (wq < warp) { before += v; }
+        }
+        if (threadIdx.x < 3u) {
+            const uint32_t cnt = threadIdx.x == 0u ? static_cast<uint32_t>(total & 0xffffffu)
+                               : threadIdx.x == 1u ? static_cast<uint32_t>((total >> 24) & 0xfffffu) : static_cast<uint32_t>(total >> 44);
+            uint32_t *ctr = &Q.counts[threadIdx.x == 0u ? 8 : (threadIdx.x == 1u ? level + 1 : 9)];
+            sm_base[threadIdx.x] = cnt ? atomicAdd(ctr, cnt) : 0u;
+        }
+        __syncthreads();
+        const unsigned long long excl = before + incl - mine;
+        uint32_t sslot = sm_base[0] + static_cast<uint32_t>(excl & 0xffffffu);
+        uint32_t rslot = sm_base[1] + static_cast<uint32_t>((excl >> 24) & 0xfffffu);
+        uint32_t cslot = sm_base[2] + static_cast<uint32_t>(excl >> 44);
+        if (!shading) { continue; }
+        // ---- phase 2: write the records
+        const uint32_t skip = pack_skip(sf.skipKind, sf.skipIdx);
+        if (ns != 0u) {
             for (int k = 0; k < rp.spl; ++k) {
-                const uint32_t ku = static_cast<uint32_t>(k);
-                // Shader::getLightIndex (Shader.cpp:223-233)
-                const float rl = k == 0 ? r_li : __ldg(s.shader_table + pt_slot(q, eb + ku, DS_LIGHT_INDEX, rp.seed));
-                const uint32_t chosen = static_cast<uint32_t>(floorf(rl * static_cast<float>(static_cast<uint32_t>(s.n_lights)) * 0.99999f));
-                const LightRec &l = s.lights[chosen];
-                v3 lightPosition = mk3(l.A[0], l.A[1], l.A[2]);        // PointLight::getPosition (PointLight.cpp:16-18)
-                if (l.kind != 0) {                                  // AreaLight::getPosition (AreaLight.cpp:17-26)
-                    float r = k == 0 ? r_p0 : __ldg(s.static_halton + pt_slot(q, eb + 2u * ku, DS_LIGHT_POS, rp.seed));
-                    float g = k == 0 ? r_p1 : __ldg(s.static_halton + pt_slot(q, eb + 2u * ku + 1u, DS_LIGHT_POS, rp.seed));
-                    if (r + g >= 1.0f) { r = 1.0f - r; g = 1.0f - g; }
-                    lightPosition = (lightPosition + r * mk3(l.AB[0], l.AB[1], l.AB[2])) + g * mk3(l.AC[0], l.AC[1], l.AC[2]);
-                }
-                v3 vectorToLight = lightPosition - sf.point;
-                const float distanceToLight = length(vectorToLight);
-                vectorToLight = normalize(vectorToLight);
-                const float cosNormalLight = dot(sf.normal, vectorToLight);
-                if (cosNormalLight > 0.0f) {
-                    ++rc.shadow;
-                    // Ld's share of this light sample: (Le * cos) * kD / samplesLight, times the path throughput
-                    const v3 ld = ((mk3(l.Le[0], l.Le[1], l.Le[2]) * cosNormalLight) * sf.Kd) / static_cast<float>(rp.spl);
-                    const v3 cc = T * ld;
-                    const uint32_t slot = queue_push(&Q.counts[8]);
-                    if (slot < Q.cap_shadow) {
-                        Q.s0[slot] = make_float4(sf.point.x, sf.point.y, sf.point.z, vectorToLight.x);
-                        Q.s1[slot] = make_float4(vectorToLight.y, vectorToLight.z, distanceToLight, __uint_as_float(pack_skip(sf.skipKind, sf.skipIdx)));
-                        const uint32_t tag = chain | (static_cast<uint32_t>(depth - 1) << 28) | (has_positive(ld) ? 0x80000000u : 0u);
-                        Q.s2[slot] = make_float4(cc.x, cc.y, cc.z, __uint_as_float(tag));
-                    } else { overflow = 1; }
-                }
+                LightSample ls = ls0;
+                const bool lit = k == 0 ? first_lit : pt_light_sample(s, rp, lightp, sf, q, eb, static_cast<uint32_t>(k), ls);
+                if (!lit) { continue; }
+                const v3 cc = T * ls.ld;
+                if (sslot < Q.cap_shadow) {
+                    Q.s0[sslot] = make_float4(sf.point.x, sf.point.y, sf.point.z, ls.dir.x);
+                    Q.s1[sslot] = make_float4(ls.dir.y, ls.dir.z, ls.dist, __uint_as_float(skip));
+                    const uint32_t tag = chain | (static_cast<uint32_t>(depth - 1) << 28) | (has_positive(ls.ld) ? 0x80000000u : 0u);
+                    Q.s2[sslot] = make_float4(cc.x, cc.y, cc.z, __uint_as_float(tag));
+                } else { overflow = 1; }
+                ++sslot;
             }
         }
-        const bool traceable = depth + 1 <= kRayDepthMax;           // deeper rays are constructed (counted) but add nothing
-        if (diffuse) {                                              // PathTracer.cpp:89-111: indirect diffuse with russian roulette
-            const bool go = depth <= kRayDepthMin || r_rr > 0.5f;
-            if (go) {
-                const v3 nd = cosine_sample_hemisphere(sf.normal, r_h0, r_h1);
-                ++rc.secondary;
-                if (traceable) {
-                    v3 Tn = T * sf.Kd;
-                    if (depth > kRayDepthMin) { Tn = Tn / (0.5f * 0.5f); }
-                    const uint32_t slot = queue_push(&Q.counts[level + 1]);
-                    if (slot < Q.cap_rays) {
-                        Q.r0[nb][slot] = make_float4(sf.point.x, sf.point.y, sf.point.z, nd.x);
-                        Q.r1[nb][slot] = make_float4(nd.y, nd.z, __uint_as_float(pack_skip(sf.skipKind, sf.skipIdx)), __int_as_float(depth + 1));
-                        Q.r2[nb][slot] = make_float4(Tn.x, Tn.y, Tn.z, __uint_as_float(chain));
-                        Q.r3[nb][slot] = make_float4(__uint_as_float(q), __uint_as_float(branch * 4u + 1u), 0.0f, 0.0f);
-                    } else { overflow = 1; }
-                }
-            }
+        if (go) {                                                   // PathTracer.cpp:89-111: indirect diffuse
+            const v3 nd = cosine_sample_hemisphere(sf.normal, r_h0, r_h1);
+            v3 Tn = T * sf.Kd;
+            if (depth > kRayDepthMin) { Tn = Tn / (0.5f * 0.5f); }
+            if (rslot < Q.cap_rays) {
+                Q.r0[nb][rslot] = make_float4(sf.point.x, sf.point.y, sf.point.z, nd.x);
+                Q.r1[nb][rslot] = make_float4(nd.y, nd.z, __uint_as_float(skip), __int_as_float(depth + 1));
+                Q.r2[nb][rslot] = make_float4(Tn.x, Tn.y, Tn.z, __uint_as_float(chain));
+                Q.r3[nb][rslot] = make_float4(__uint_as_float(q), __uint_as_float(branch * 4u + 1u), 0.0f, 0.0f);
+            } else { overflow = 1; }
+            ++rslot;
         }
 #pragma unroll
         for (int kind = 0; kind < 2; ++kind) {                      // PathTracer.cpp:113-134: specular reflection, then transmission
+            if (!(kind == 0 ? spec : trans)) { continue; }
             const v3 K = kind == 0 ? sf.Ks : sf.Kt;
-            if (!has_positive(K)) { continue; }
-            ++rc.secondary;
-            if (!traceable) { continue; }
             const v3 nd = kind == 0 ? reflect(d, sf.normal) : refract(d, sf.normal, 1.0f / sf.ior);
-            const uint32_t cslot = queue_push(&Q.counts[9]);
-            const uint32_t slot = queue_push(&Q.counts[level + 1]);
             // the accumulator is initialised whenever the pool slot exists, so that finalize never reads a stale record
             if (cslot < Q.cap_chains) { acc_init(Q.acc + cslot, mk3(0.0f, 0.0f, 0.0f), static_cast<uint32_t>(depth) << 4, static_cast<int32_t>(chain)); }
-            if (cslot < Q.cap_chains && slot < Q.cap_rays) {
+            if (cslot < Q.cap_chains && rslot < Q.cap_rays) {
                 const v3 Tn = T * K;
-                Q.r0[nb][slot] = make_float4(sf.point.x, sf.point.y, sf.point.z, nd.x);
-                Q.r1[nb][slot] = make_float4(nd.y, nd.z, __uint_as_float(pack_skip(sf.skipKind, sf.skipIdx)), __int_as_float(depth + 1));
-                Q.r2[nb][slot] = make_float4(Tn.x, Tn.y, Tn.z, __uint_as_float(cslot));
-                Q.r3[nb][slot] = make_float4(__uint_as_float(q), __uint_as_float(branch * 4u + 2u + static_cast<uint32_t>(kind)), 0.0f, 0.0f);
+                Q.r0[nb][rslot] = make_float4(sf.point.x, sf.point.y, sf.point.z, nd.x);
+                Q.r1[nb][rslot] = make_float4(nd.y, nd.z, __uint_as_float(skip), __int_as_float(depth + 1));
+                Q.r2[nb][rslot] = make_float4(Tn.x, Tn.y, Tn.z, __uint_as_float(cslot));
+                Q.r3[nb][rslot] = make_float4(__uint_as_float(q), __uint_as_float(branch * 4u + 2u + static_cast<uint32_t>(kind)), 0.0f, 0.0f);
             } else { overflow = 1; }
+            ++cslot; ++rslot;
         }
     }
     const uint32_t sh = __reduce_add_sync(0xffffffffu, rc.shadow), se = __reduce_add_sync(0xffffffffu, rc.secondary);
@@ -858,13 +930,13 @@ cudaError_t wavefront_trace_batch(Wavefront *w, const SceneDev &s, const CameraR
     for (int level = 0; level < kLevels; ++level) {
         k_wf_extend<<<grid, kWfThreads, 0, st>>>(s, Q, level, dc);
         WF_TRY(wf_mark(w, WF_EXTEND, st));
-        if (level == 0) { k_wf_shade<true><<<sgrid, kWfThreads, 0, st>>>(s, rp, Q, level, dc); }
-        else { k_wf_shade<false><<<sgrid, kWfThreads, 0, st>>>(s, rp, Q, level, dc); }
+        if (level == 0) { k_wf_shade<true><<<sgrid, kShadeThreads, 0, st>>>(s, rp, Q, level, dc); }
+        else { k_wf_shade<false><<<sgrid, kShadeThreads, 0, st>>>(s, rp, Q, level, dc); }
         WF_TRY(wf_mark(w, WF_SHADE, st));
         k_wf_after_shade<<<1, 1, 0, st>>>(Q, level, dc);
         k_wf_shadow<<<grid, kWfThreads, 0, st>>>(s, Q, dc);
         WF_TRY(wf_mark(w, WF_SHADOW, st));
-        k_wf_fold<<<sgrid, 256, 0, st>>>(Q);
+        k_wf_fold<<<w->sm_count * 8, 256, 0, st>>>(Q);
         k_wf_after_fold<<<1, 1, 0, st>>>(Q, dc);
         WF_TRY(wf_mark(w, WF_OTHER, st));
         *launches += 6;

@@ -17,12 +17,20 @@ def test_library_exports_every_declared_symbol():
     from mobileraytracer_b200 import capi
     hdr = open(os.path.join(ROOT, "include", "mobilert_b200.h")).read()
     declared = set(re.findall(r"\b(mrt_[a-z0-9_]+)\s*\(", hdr))
-    assert len(declared) >= 24
+    assert len(declared) >= 20
     L = capi.lib()
     for sym in sorted(declared):
         assert getattr(L, sym) is not None, sym
     assert declared == set(capi.SYMBOLS), declared ^ set(capi.SYMBOLS)
     assert b"sm_100a" in L.mrt_version()
+    # the second library: the device functions one call at a time (include/mobilert_b200_test.h); none of them in the product
+    hdr_t = open(os.path.join(ROOT, "include", "mobilert_b200_test.h")).read()
+    declared_t = set(re.findall(r"\b(mrt_test_[a-z0-9_]+)\s*\(", hdr_t))
+    T = capi.test_lib()
+    for sym in sorted(declared_t):
+        assert getattr(T, sym) is not None, sym
+        assert not hasattr(L, sym), sym + " must not ship in the product library"
+    assert declared_t == set(capi.TEST_SYMBOLS), declared_t ^ set(capi.TEST_SYMBOLS)
 
 
 def test_no_cpu_fallback_and_argument_checks():

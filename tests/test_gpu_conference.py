@@ -34,11 +34,12 @@ def test_known_answer_vectors_on_device(mrt):
     from mobileraytracer_b200.scene import make_triangle
     capi = mrt.capi
     L = capi.lib()
+    T = capi.test_lib()
     ka = json.load(open(os.path.join(GOLD, "known_answers.json")))
     f3 = lambda x: np.ascontiguousarray(np.asarray(x, np.float32))
     for c in ka["aabb"]["ray"]:
         hit = C.c_int32(-1)
-        capi.check(L.mrt_test_aabb_intersect(capi.ptr(f3(c["min"])), capi.ptr(f3(c["max"])), capi.ptr(f3(c["o"])), capi.ptr(f3(c["d"])), C.byref(hit)))
+        capi.check_test(T.mrt_test_aabb_intersect(capi.ptr(f3(c["min"])), capi.ptr(f3(c["max"])), capi.ptr(f3(c["o"])), capi.ptr(f3(c["d"])), C.byref(hit)))
         assert bool(hit.value) == c["hit"], c["cite"]
     t = ka["triangle"]
     tri = np.asarray(make_triangle(t["A"], t["B"], t["C"], material=0)).reshape(1)
@@ -46,14 +47,14 @@ def test_known_answer_vectors_on_device(mrt):
         o = f3(c["o"])
         d = (f3(c["to"]) - o).astype(np.float32)
         dist = C.c_float(0)
-        capi.check(L.mrt_test_triangle_intersect(capi.ptr(tri), capi.ptr(o), capi.ptr(d), C.c_float(1e30), 1 if c.get("self") else 0, C.byref(dist), None))
+        capi.check_test(T.mrt_test_triangle_intersect(capi.ptr(tri), capi.ptr(o), capi.ptr(d), C.c_float(1e30), 1 if c.get("self") else 0, C.byref(dist), None))
         assert (dist.value < 1e30) == c["hit"], c["cite"]
     p = ka["plane"]
     pl = np.zeros(1, capi.PLANE)
     pl["normal"], pl["point"] = p["normal"], p["point"]
     for c in p["ray"]:
         dist = C.c_float(0)
-        capi.check(L.mrt_test_plane_intersect(capi.ptr(pl), capi.ptr(f3(c["o"])), capi.ptr(f3(c["d"])), C.c_float(1e30), C.byref(dist)))
+        capi.check_test(T.mrt_test_plane_intersect(capi.ptr(pl), capi.ptr(f3(c["o"])), capi.ptr(f3(c["d"])), C.c_float(1e30), C.byref(dist)))
         assert (dist.value < 1e30) == c["hit"], c["cite"]
 
 

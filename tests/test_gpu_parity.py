@@ -24,6 +24,7 @@ def test_device_primitives_match_reference(mrt, ref):
     import ctypes as C
     capi = mrt.capi
     L = capi.lib()
+    T = capi.test_lib()
     rng = np.random.default_rng(7)
     n_hit = 0
     for i in range(200):
@@ -38,7 +39,7 @@ def test_device_primitives_match_reference(mrt, ref):
         t_ref, out_ref = ref.triangle_intersect(tri, o, d)
         t = C.c_float(0)
         out = np.zeros(8, np.float32)
-        capi.check(L.mrt_test_triangle_intersect(capi.ptr(tri), capi.ptr(o), capi.ptr(d.astype(np.float32)), C.c_float(1e30), 0, C.byref(t), capi.ptr(out)))
+        capi.check_test(T.mrt_test_triangle_intersect(capi.ptr(tri), capi.ptr(o), capi.ptr(d.astype(np.float32)), C.c_float(1e30), 0, C.byref(t), capi.ptr(out)))
         assert np.float32(t.value) == np.float32(t_ref)
         if t_ref < 1e29:
             n_hit += 1
@@ -55,7 +56,7 @@ def test_device_primitives_match_reference(mrt, ref):
         s["center"], s["sq_radius"] = c, rad * rad
         t = C.c_float(0)
         nrm = np.zeros(3, np.float32)
-        capi.check(L.mrt_test_sphere_intersect(capi.ptr(s), capi.ptr(o), capi.ptr(d), C.c_float(1e30), C.byref(t), capi.ptr(nrm)))
+        capi.check_test(T.mrt_test_sphere_intersect(capi.ptr(s), capi.ptr(o), capi.ptr(d), C.c_float(1e30), C.byref(t), capi.ptr(nrm)))
         assert np.float32(t.value) == np.float32(t_ref)
         if t_ref < 1e29:
             assert np.array_equal(nrm, n_ref)
@@ -70,11 +71,11 @@ def test_device_primitives_match_reference(mrt, ref):
         pl = np.zeros(1, capi.PLANE)
         pl["normal"], pl["point"] = nrm, p
         t = C.c_float(0)
-        capi.check(L.mrt_test_plane_intersect(capi.ptr(pl), capi.ptr(o), capi.ptr(d), C.c_float(1e30), C.byref(t)))
+        capi.check_test(T.mrt_test_plane_intersect(capi.ptr(pl), capi.ptr(o), capi.ptr(d), C.c_float(1e30), C.byref(t)))
         assert np.float32(t.value) == np.float32(t_ref)
         mn, mx = np.minimum(p, o * 0.3), np.maximum(p, o * 0.3) + np.float32(0.1)
         hit = C.c_int32(0)
-        capi.check(L.mrt_test_aabb_intersect(capi.ptr(mn), capi.ptr(mx), capi.ptr(o), capi.ptr(d), C.byref(hit)))
+        capi.check_test(T.mrt_test_aabb_intersect(capi.ptr(mn), capi.ptr(mx), capi.ptr(o), capi.ptr(d), C.byref(hit)))
         assert bool(hit.value) == ref.aabb_intersect(mn, mx, o, d)
     for i in range(300):
         rgb = rng.uniform(-0.2, 3.0, 3).astype(np.float32)
@@ -82,10 +83,10 @@ def test_device_primitives_match_reference(mrt, ref):
         avg = int(np.int32(np.uint32(avg & 0xFFFFFFFF)))
         n = int(rng.integers(1, 200))
         out = C.c_int32(0)
-        capi.check(L.mrt_test_incremental_avg(capi.ptr(rgb), avg, n, C.byref(out)))
+        capi.check_test(T.mrt_test_incremental_avg(capi.ptr(rgb), avg, n, C.byref(out)))
         assert out.value == ref.incremental_avg(rgb, avg, n)
     h = np.zeros(4096, np.float32)
-    capi.check(L.mrt_test_halton(0, 4096, 2, capi.ptr(h)))
+    capi.check_test(T.mrt_test_halton(0, 4096, 2, capi.ptr(h)))
     assert np.array_equal(h, np.array([ref.halton(i, 2) for i in range(4096)], np.float32))
 
 
