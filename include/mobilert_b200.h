@@ -101,9 +101,11 @@ enum { MRT_SAMPLER_AUTO = 0, MRT_SAMPLER_CONSTANT = 1, MRT_SAMPLER_STATIC_HALTON
 enum {
     MRT_FLAG_FP32_ACCUMULATE = 1,  /* accumulate radiance in fp32 and quantise once (needed for multi-GPU partitions);
                                       default is the reference's 8-bit running average (MobileRT/Utils/Utils.cpp:66-90) */
-    MRT_FLAG_SORT_BY_MATERIAL = 2, /* accepted and ignored: every material runs the same shading routine (materials are data,
-                                      Material.hpp), so the shade kernel has no per-material divergence to sort away; it is
-                                      bound by gather latency (profiles/), which a sort of the 16-byte hit records would not help */
+    MRT_FLAG_SORT_BY_MATERIAL = 2, /* PathTracer: the hits of every depth level are binned by material (counting sort of hit indices)
+                                      before they are shaded. Same image. Off by default because it is slower on this design: every
+                                      material runs the same shading routine (materials are data, Material.hpp:18-43), so there is no
+                                      divergence to sort away, and the permuted order turns the streamed hit / ray records into
+                                      gathers (measured A/B: profiles/r2_ab_material_sort.txt) */
     MRT_FLAG_PROGRESSIVE = 8,      /* mrt_render_frame refreshes the caller's HOST bitmap after every sample (wavefront: every pass)
                                       from a second stream, so that a UI thread polling the buffer sees the frame build up as it
                                       does with the reference, whose workers write finished pixels in place (Renderer.cpp:149-157;

@@ -498,12 +498,14 @@ int mrt_create(const mrt_scene_desc *scene, const mrt_camera_desc *camera, const
         if ((e = cudaMallocHost(reinterpret_cast<void **>(&h->h_pinned_bitmap), npix * sizeof(int32_t))) != cudaSuccess) { rc = cuda_fail(h, e, "pinned bitmap"); break; }
         h->pinned_bytes = npix * sizeof(int32_t);
         if (render->shader == MRT_SHADER_PATHTRACER) {
+            const char *sk = std::getenv("MRT_B200_SORT_KEY");   // diagnostic: "primitive" bins by primitive id instead of material
+            const int sort_mode = (render->flags & MRT_FLAG_SORT_BY_MATERIAL) ? ((sk && std::strcmp(sk, "primitive") == 0) ? 2 : 1) : 0;
             const char *be = std::getenv("MRT_B200_BATCH");   // samples traced together per wavefront pass
             // default: up to 16 samples per pass, as long as the queues (about 390 + 100 * samples_light bytes per pixel and sample) stay below 32 GB
             const double per_sample = (390.0 + 100.0 * std::max(1, render->samples_light)) * static_cast<double>(std::max<uint32_t>(h->roots_per_sample, 1u));
             const int by_memory = static_cast<int>(std::max(1.0, std::min(16.0, 32.0e9 / std::max(per_sample, 1.0))));
             const int batch = std::max(1, std::min(be ? std::atoi(be) : by_memory, render->samples_pixel));
-            if ((e = wavefront_create(h->roots_per_sample, batch, render->samples_light, &h->wavefront)) != cudaSuccess) { rc = cuda_fail(h, e, "wavefront queues"); break; }
+            if ((e = wavefront_create(h->roots_per_sample, batch, render->samples_light, sort_mode, static_cast<uint32_t>(h->scene.n_bvh_prims), &h->wavefront)) != cudaSuccess) { rc = cuda_fail(h, e, "wavefront queues"); break; }
         }
         if ((e = cudaStreamSynchronize(h->stream)) != cudaSuccess) { rc = cuda_fail(h, e, "create sync"); break; }
     } while (false);

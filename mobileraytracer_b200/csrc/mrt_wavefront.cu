@@ -54,6 +54,11 @@ struct Queues {
     uint32_t *counts;            // [0..7] ray count per level, [8] shadow count, [9] chain pool size, [10..17] chain pool size after each level,
                                  // [20],[21] work counters
     uint32_t cap_rays, cap_shadow, cap_chains;
+    // MRT_FLAG_SORT_BY_MATERIAL: the shade kernel visits the hits of a level in the order perm[0 .. n), binned by sort key
+    uint32_t *perm;              // null when the flag is off
+    uint32_t *sort_bins;         // kSortBins + 1 counters / offsets
+    int32_t sort_key;            // 0: material index of the hit primitive; 1: primitive id (hit locality)
+    uint32_t sort_shift;         // sort_key 1: bin = primitive id >> sort_shift
 };
 
 struct WfMark { cudaEvent_t ev; int cls; };
@@ -65,6 +70,8 @@ struct Wavefront {
     int batch = 1;
     int spl = 1;
     int factor = 2;                   // ray-queue capacity in camera paths of a full pass (wf_alloc_queues)
+    int sort_mode = 0;                // 0: off; 1: bin the hits by material before shading; 2: by primitive id (A/B of hit locality)
+    uint32_t sort_shift = 0;
     size_t bytes = 0;
     std::vector<void *> allocs;
     std::vector<WfMark> marks;        // one event after every launch; the class says what ran before it
@@ -455,6 +462,64 @@ MRT_D v3 cosine_sample_hemisphere(v3 normal, float uniformRandom1, float uniform
     return normalize(direction);
 }
 
+// ---- optional: bin the hits of a level by material (north_star 3: "ray queues ... sorted by material") -------------
+// A counting sort of hit indices: histogram per CTA chunk in shared memory, one global atomicAdd per bin and CTA to reserve
+// the bin's range, then the scatter. The shade kernel then walks perm[] instead of 0 .. n-1. Every material runs the same
+// shading code here (materials are data, Material.hpp:18-43), so what binning can buy is locality of the records the
+// shade kernel gathers (materials; with sort_key 1 the 64-byte TriShade records), paid for with three more kernels per
+// level and gathered instead of streamed hit / ray records. Measured: profiles/r2_ab_material_sort.txt.
+constexpr uint32_t kSortBins = 1024, kSortChunk = 8192;
+
+MRT_D uint32_t sort_bin(const SceneDev &s, const Queues &Q, uint32_t i) {
+    const uint32_t packed = __float_as_uint(Q.hit[i].w);
+    const uint32_t kind = packed >> 28, idx = packed & 0x0fffffffu;
+    if (kind != HIT_TRIANGLE) { return kSortBins - 1u - min(kind, 7u); }          // misses, lights, planes, spheres: bins of their own at the end
+    if (Q.sort_key == 1) { return min(idx >> Q.sort_shift, kSortBins - 9u); }
+    const uint32_t m = static_cast<uint32_t>(__float_as_int(__ldg(reinterpret_cast<const float4 *>(s.tri_shade + idx) + 3).w));
+    return min(m, kSortBins - 9u);
+}
+
+__global__ void __launch_bounds__(256) k_wf_sort_count(SceneDev s, Queues Q, int level) {
+    __shared__ uint32_t local[kSortBins];
+    const uint32_t n = min(Q.counts[level], Q.cap_rays);
+    for (uint32_t k = threadIdx.x; k < kSortBins; k += 256u) { local[k] = 0u; }
+    __syncthreads();
+    const uint32_t c0 = blockIdx.x * kSortChunk, c1 = min(c0 + kSortChunk, n);
+    for (uint32_t i = c0 + threadIdx.x; i < c1; i += 256u) { atomicAdd(&local[sort_bin(s, Q, i)], 1u); }
+    __syncthreads();
+    for (uint32_t k = threadIdx.x; k < kSortBins; k += 256u) { if (local[k]) { atomicAdd(&Q.sort_bins[k], local[k]); } }
+}
+
+__global__ void __launch_bounds__(kSortBins) k_wf_sort_scan(Queues Q) {   // exclusive scan of the bin counts (one CTA)
+    __shared__ uint32_t tmp[kSortBins];
+    const uint32_t k = threadIdx.x, v = Q.sort_bins[k];
+    tmp[k] = v;
+    __syncthreads();
+    for (uint32_t d = 1; d < kSortBins; d <<= 1) {
+        const uint32_t add = k >= d ? tmp[k - d] : 0u;
+        __syncthreads();
+        tmp[k] += add;
+        __syncthreads();
+    }
+    Q.sort_bins[k] = tmp[k] - v;
+}
+
+__global__ void __launch_bounds__(256) k_wf_sort_scatter(SceneDev s, Queues Q, int level) {
+    __shared__ uint32_t local[kSortBins], base[kSortBins];
+    const uint32_t n = min(Q.counts[level], Q.cap_rays);
+    for (uint32_t k = threadIdx.x; k < kSortBins; k += 256u) { local[k] = 0u; }
+    __syncthreads();
+    const uint32_t c0 = blockIdx.x * kSortChunk, c1 = min(c0 + kSortChunk, n);
+    for (uint32_t i = c0 + threadIdx.x; i < c1; i += 256u) { atomicAdd(&local[sort_bin(s, Q, i)], 1u); }
+    __syncthreads();
+    for (uint32_t k = threadIdx.x; k < kSortBins; k += 256u) { base[k] = local[k] ? atomicAdd(&Q.sort_bins[k], local[k]) : 0u; local[k] = 0u; }
+    __syncthreads();
+    for (uint32_t i = c0 + threadIdx.x; i < c1; i += 256u) {
+        const uint32_t k = sort_bin(s, Q, i);
+        Q.perm[base[k] + atomicAdd(&local[k], 1u)] = i;
+    }
+}
+
 // ---- shade: PathTracer::shade for every hit of the level; emits shadow rays and the next level's rays --------------
 // Where a draw of the reference's tables comes from (Shader.cpp:188-233, Sampler.hpp:58-63, PathTracer.cpp:91): the
 // reference hands out table[counter++] in execution order, which no parallel schedule can replay for a path tracer
@@ -477,6 +542,7 @@ constexpr int kShadeMatCap = 64, kShadeLightCap = 256;   // records staged in sh
 // PointLight::getPosition (PointLight.cpp:16-18) or AreaLight::getPosition (AreaLight.cpp:17-26). True when the light point
 // lies in front of the surface, i.e. when the reference casts the shadow ray.
 struct LightSample { v3 dir; float dist; v3 ld; };
+MRT_D uint32_t dir_octant(v3 d) { return (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u); }
 MRT_D bool pt_light_sample(const SceneDev &s, const RenderParams &rp, const float4 *lightp, const Surface &sf, uint32_t q, uint32_t eb, uint32_t k,
                            LightSample &ls) {
     const float rl = pt_draw(s.shader_table, s.shader_table_is_perm, q, eb + k, DS_LIGHT_INDEX, rp.seed);
@@ -511,6 +577,9 @@ __global__ void __launch_bounds__(kShadeThreads, MRT_SHADE_MIN_BLOCKS) k_wf_shad
     __shared__ float4 sm_light[kShadeLightCap * 4];
     __shared__ unsigned long long sm_warp[kShadeThreads / 32];   // per warp: shadow rays | rays << 24 | chains << 44 of this iteration
     __shared__ uint32_t sm_base[3];
+#ifdef MRT_BIN_OCTANT
+    __shared__ uint32_t sm_bin[3][8];   // this iteration's records per direction octant: shadow rays, rays; [2][0]: chains
+#endif
     const bool mat_sh = s.n_materials <= kShadeMatCap, light_sh = s.n_lights <= kShadeLightCap;
     if (mat_sh) { for (int k = threadIdx.x; k < s.n_materials * 4; k += kShadeThreads) { sm_mat[k] = __ldg(reinterpret_cast<const float4 *>(s.materials) + k); } }
     if (light_sh) { for (int k = threadIdx.x; k < s.n_lights * 4; k += kShadeThreads) { sm_light[k] = __ldg(reinterpret_cast<const float4 *>(s.lights) + k); } }
@@ -524,7 +593,8 @@ __global__ void __launch_bounds__(kShadeThreads, MRT_SHADE_MIN_BLOCKS) k_wf_shad
     RayCounters rc = {0u, 0u, 0u};
     int overflow = 0;
     for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += stride) {   // the same trip count for every thread of the CTA
-        const uint32_t i = base + threadIdx.x;
+        const uint32_t j = base + threadIdx.x;
+        const uint32_t i = (Q.perm != nullptr && j < n) ? Q.perm[j] : j;   // MRT_FLAG_SORT_BY_MATERIAL: hits binned by material
         // ---- phase 1: the surface, and how many shadow rays / rays / chains this hit emits
         uint32_t ns = 0u, nr = 0u, nc = 0u;
         bool shading = false, first_lit = false, go = false, spec = false, trans = false;
@@ -534,9 +604,11 @@ __global__ void __launch_bounds__(kShadeThreads, MRT_SHADE_MIN_BLOCKS) k_wf_shad
         uint32_t q = 0u, branch = 1u, chain = i, eb = 0u;
         int depth = 1;
         float r_h0 = 0.0f, r_h1 = 0.0f;
-        if (i < n) {
+        uint32_t sbin = 0u, rbin = 0u;                  // direction octants of the first shadow ray / of the diffuse ray
+        v3 nd_diffuse = mk3(0.0f, 0.0f, 0.0f);
+        if (j < n) {
             // the records of this thread's next iteration start their trip from HBM to L2 now
-            if (i + stride < n) {
+            if (Q.perm == nullptr && i + stride < n) {
                 asm volatile("prefetch.global.L2 [%0];" :: "l"(Q.hit + i + stride));
                 asm volatile("prefetch.global.L2 [%0];" :: "l"(Q.r0[b] + i + stride));
                 asm volatile("prefetch.global.L2 [%0];" :: "l"(Q.r1[b] + i + stride));
@@ -585,9 +657,10 @@ __global__ void __launch_bounds__(kShadeThreads, MRT_SHADE_MIN_BLOCKS) k_wf_shad
                     if (diffuse && s.n_lights > 0) {                    // PathTracer.cpp:55-87: direct light, one shadow ray per light sample
                         first_lit = pt_light_sample(s, rp, lightp, sf, q, eb, 0u, ls0);
                         ns = first_lit ? 1u : 0u;
+                        if (first_lit) { sbin = dir_octant(ls0.dir); }
                         for (int k = 1; k < rp.spl; ++k) {
                             LightSample ls;
-                            if (pt_light_sample(s, rp, lightp, sf, q, eb, static_cast<uint32_t>(k), ls)) { ++ns; }
+                            if (pt_light_sample(s, rp, lightp, sf, q, eb, static_cast<uint32_t>(k), ls)) { if (ns == 0u) { sbin = dir_octant(ls.dir); } ++ns; }
                         }
                         rc.shadow += ns;
                     }
@@ -597,9 +670,38 @@ __global__ void __launch_bounds__(kShadeThreads, MRT_SHADE_MIN_BLOCKS) k_wf_shad
                     rc.secondary += (go ? 1u : 0u) + (spec ? 1u : 0u) + (trans ? 1u : 0u);
                     if (traceable) { nc = (spec ? 1u : 0u) + (trans ? 1u : 0u); nr = nc + (go ? 1u : 0u); }
                     else { go = false; spec = false; trans = false; }
+                    if (go) { nd_diffuse = cosine_sample_hemisphere(sf.normal, r_h0, r_h1); rbin = dir_octant(nd_diffuse); }
                 }
             }
         }
+#ifdef MRT_BIN_OCTANT
+        // ---- slots: the CTA's records are laid out by direction octant (8 bins per queue, shared-memory counters), so that the rays
+        // a traversal warp picks up together descend the BVH8 in the same child order; one global atomicAdd per queue
+        if (threadIdx.x < 17u) { (&sm_bin[0][0])[threadIdx.x] = 0u; }
+        __syncthreads();
+        uint32_t spos = 0u, rpos = 0u, cpos = 0u;
+        if (ns) { spos = atomicAdd(&sm_bin[0][sbin], ns); }
+        if (nr) { rpos = atomicAdd(&sm_bin[1][rbin], nr); }
+        if (nc) { cpos = atomicAdd(&sm_bin[2][0], nc); }
+        __syncthreads();
+        uint32_t sbefore = 0u, rbefore = 0u, stotal = 0u, rtotal = 0u;
+#pragma unroll
+        for (uint32_t k = 0; k < 8u; ++k) {
+            const uint32_t a0 = sm_bin[0][k], a1 = sm_bin[1][k];
+            stotal += a0; rtotal += a1;
+            if (k < sbin) { sbefore += a0; }
+            if (k < rbin) { rbefore += a1; }
+        }
+        if (threadIdx.x < 3u) {
+            const uint32_t cnt = threadIdx.x == 0u ? stotal : (threadIdx.x == 1u ? rtotal : sm_bin[2][0]);
+            uint32_t *ctr = &Q.counts[threadIdx.x == 0u ? 8 : (threadIdx.x == 1u ? level + 1 : 9)];
+            sm_base[threadIdx.x] = cnt ? atomicAdd(ctr, cnt) : 0u;
+        }
+        __syncthreads();
+        uint32_t sslot = sm_base[0] + sbefore + spos;
+        uint32_t rslot = sm_base[1] + rbefore + rpos;
+        uint32_t cslot = sm_base[2] + cpos;
+#else
         // ---- slots: prefix sums over the CTA, one atomicAdd per queue
         unsigned long long mine = static_cast<unsigned long long>(ns) | (static_cast<unsigned long long>(nr) << 24) | (static_cast<unsigned long long>(nc) << 44);
         unsigned long long incl = mine;
@@ -628,6 +730,7 @@ __global__ void __launch_bounds__(kShadeThreads, MRT_SHADE_MIN_BLOCKS) k_wf_shad
         uint32_t sslot = sm_base[0] + static_cast<uint32_t>(excl & 0xffffffu);
         uint32_t rslot = sm_base[1] + static_cast<uint32_t>((excl >> 24) & 0xfffffu);
         uint32_t cslot = sm_base[2] + static_cast<uint32_t>(excl >> 44);
+#endif
         if (!shading) { continue; }
         // ---- phase 2: write the records
         const uint32_t skip = pack_skip(sf.skipKind, sf.skipIdx);
@@ -647,7 +750,7 @@ __global__ void __launch_bounds__(kShadeThreads, MRT_SHADE_MIN_BLOCKS) k_wf_shad
             }
         }
         if (go) {                                                   // PathTracer.cpp:89-111: indirect diffuse
-            const v3 nd = cosine_sample_hemisphere(sf.normal, r_h0, r_h1);
+            const v3 nd = nd_diffuse;
             v3 Tn = T * sf.Kd;
             if (depth > kRayDepthMin) { Tn = Tn / (0.5f * 0.5f); }
             if (rslot < Q.cap_rays) {
@@ -828,6 +931,13 @@ static cudaError_t wf_alloc_queues(Wavefront *w, size_t paths, int factor) {
     WF_TRY(wf_alloc(w, &q.vis, static_cast<size_t>(q.cap_shadow) + 64));
     WF_TRY(wf_alloc(w, &q.acc, q.cap_chains));
     WF_TRY(wf_alloc(w, &q.counts, kWfCounts));
+    q.perm = nullptr; q.sort_bins = nullptr;
+    if (w->sort_mode != 0) {
+        WF_TRY(wf_alloc(w, &q.perm, q.cap_rays));
+        WF_TRY(wf_alloc(w, &q.sort_bins, kSortBins + 1));
+        q.sort_key = w->sort_mode == 2 ? 1 : 0;
+        q.sort_shift = w->sort_shift;
+    }
     w->bytes = static_cast<size_t>(q.cap_rays) * (8 * 16 + 16) + static_cast<size_t>(q.cap_shadow) * (3 * 16 + 1) + static_cast<size_t>(q.cap_chains) * sizeof(PathAcc);
     w->factor = factor;
     return cudaSuccess;
@@ -837,10 +947,12 @@ static void wf_free_queues(Wavefront *w) {
     w->allocs.clear();
 }
 
-cudaError_t wavefront_create(size_t paths_per_sample, int batch, int spl, Wavefront **out) {
+cudaError_t wavefront_create(size_t paths_per_sample, int batch, int spl, int sort_mode, uint32_t n_primitives, Wavefront **out) {
     Wavefront *w = new Wavefront;
     *out = w;
     w->paths_per_sample = paths_per_sample; w->spl = spl;
+    w->sort_mode = sort_mode;
+    while ((n_primitives >> w->sort_shift) > kSortBins - 9u) { ++w->sort_shift; }
     w->batch = batch < 1 ? 1 : (batch > kWfMaxBatch ? kWfMaxBatch : batch);
     int dev = 0;
     cudaGetDevice(&dev);
@@ -930,6 +1042,14 @@ cudaError_t wavefront_trace_batch(Wavefront *w, const SceneDev &s, const CameraR
     for (int level = 0; level < kLevels; ++level) {
         k_wf_extend<<<grid, kWfThreads, 0, st>>>(s, Q, level, dc);
         WF_TRY(wf_mark(w, WF_EXTEND, st));
+        if (Q.perm != nullptr) {
+            WF_TRY(cudaMemsetAsync(Q.sort_bins, 0, (kSortBins + 1) * sizeof(uint32_t), st));
+            const unsigned sblocks = static_cast<unsigned>((static_cast<size_t>(n_samples) * roots_per_sample * static_cast<size_t>(w->factor) + kSortChunk - 1) / kSortChunk);
+            k_wf_sort_count<<<sblocks, 256, 0, st>>>(s, Q, level);
+            k_wf_sort_scan<<<1, kSortBins, 0, st>>>(Q);
+            k_wf_sort_scatter<<<sblocks, 256, 0, st>>>(s, Q, level);
+            *launches += 3;
+        }
         if (level == 0) { k_wf_shade<true><<<sgrid, kShadeThreads, 0, st>>>(s, rp, Q, level, dc); }
         else { k_wf_shade<false><<<sgrid, kShadeThreads, 0, st>>>(s, rp, Q, level, dc); }
         WF_TRY(wf_mark(w, WF_SHADE, st));

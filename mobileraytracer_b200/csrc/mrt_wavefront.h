@@ -13,7 +13,9 @@ constexpr int kWfMaxBatch = 16;
 constexpr int kWfCounts = 32;   // Queues::counts entries (see mrt_wavefront.cu)
 // batch: samples of every pixel traced together in one pass (1..kWfMaxBatch); the queues are sized for it and for
 // samples_light shadow rays per hit
-cudaError_t wavefront_create(size_t paths_per_sample, int batch, int samples_light, Wavefront **out);
+// sort_mode: 0 off; 1 = MRT_FLAG_SORT_BY_MATERIAL (the shade kernel visits the hits of a level binned by material); 2 = binned by
+// primitive id instead (diagnostic: MRT_B200_SORT_KEY=primitive)
+cudaError_t wavefront_create(size_t paths_per_sample, int batch, int samples_light, int sort_mode, uint32_t n_primitives, Wavefront **out);
 int wavefront_batch(const Wavefront *w);
 uint64_t wavefront_capacity(const Wavefront *w);   // rays one pass can hold
 size_t wavefront_bytes(const Wavefront *w);        // device memory of the queues

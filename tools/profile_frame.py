@@ -15,12 +15,13 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--spp", type=int, default=2)
 ap.add_argument("--shader", type=int, default=capi.SHADER_PATHTRACER)
 ap.add_argument("--frames", type=int, default=1)
+ap.add_argument("--flags", type=int, default=0, help="MRT_FLAG_* bits, e.g. 2 = sort by material")
 a = ap.parse_args()
 h = bench.round_down16(bench.HEIGHT_ASKED)
 obj, mtl, cam = bench.scene_files()
 scene = loaders.load_obj(obj, mtl).arrays()
 camera = loaders.load_camera(cam, np.float32(bench.WIDTH) / np.float32(h))
-r = mrt.Renderer(scene, camera, bench.WIDTH, h, a.spp, 1, a.shader)
+r = mrt.Renderer(scene, camera, bench.WIDTH, h, a.spp, 1, a.shader, flags=a.flags)
 bm = np.zeros(bench.WIDTH * h, np.int32)
 for _ in range(a.frames):
     r.renderFrame(bm)
