@@ -264,6 +264,8 @@ def run_b200(args, wl, height):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"      # NCCL prints its version banner on stdout, where the one JSON line belongs
         dist.init_process_group("nccl", device_id=dev)
     assert world == args.gpus, "launch with torchrun --nproc-per-node %d" % args.gpus
 
@@ -377,7 +379,7 @@ def run_b200(args, wl, height):
                                inputs.get("k_wf_shadow"), clk, peak, peak_src, gather)
         # shade: streams the hit + ray records in and the shadow / continuation records out; HBM is its roof
         shade_in = inputs.get("k_wf_shade", {})
-        shade_bytes = shade_in.get("algorithmic_bytes_per_hit", 176)
+        shade_bytes = shade_in.get("algorithmic_bytes_per_hit", 192)
         rf_shade = None
         if acc["shade_ms"] > 0:
             a = shade_bytes * acc["rays_extend_traced"] / (acc["shade_ms"] * 1e-3) / 1e9

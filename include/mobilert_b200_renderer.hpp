@@ -20,9 +20,15 @@
 #include "MobileRT/Camera.hpp"
 #include "MobileRT/Scene.hpp"
 
+#include <atomic>
+#include <chrono>
+#include <condition_variable>
 #include <cstring>
+#include <memory>
+#include <mutex>
 #include <stdexcept>
 #include <string>
+#include <thread>
 #include <vector>
 
 namespace MobileRT {
@@ -150,6 +156,89 @@ public:
     ::std::int32_t getSample() const { ::std::int32_t s = 0; mrt_get_sample(handle_, &s); return s; }
     /* Renderer::getTotalCastedRays (Renderer.cpp:204-207) */
     ::std::uint64_t getTotalCastedRays() const { ::std::uint64_t r = 0; mrt_get_total_rays(handle_, &r); return r; }
+};
+
+/*
+ * The render thread and state machine the Android front-end wraps around the blocking renderFrame
+ * (System_dependent/Android_JNI/JNI_layer.cpp: State IDLE / BUSY / FINISHED / STOPPED :44 and JNI_layer.hpp:12-14,
+ * rtStartRender :406-426, rtStopRender :428-462, the worker lambda of rtRenderIntoBitmap :744-901, rtGetState :904-913),
+ * without the JNI calls, over a B200Renderer: startRender() arms the state, renderIntoBitmap() runs renderFrame on a worker
+ * thread while the UI thread polls getSample() / getState() and reads the bitmap (create the renderer with
+ * MRT_FLAG_PROGRESSIVE to see it build up), stopRender(wait) is rtStopRender.
+ */
+class B200RenderThread final {
+public:
+    enum class State { IDLE = 0, BUSY = 1, FINISHED = 2, STOPPED = 3 };   // JNI_layer.hpp:12-14
+
+private:
+    B200Renderer &renderer_;
+    ::std::atomic<State> state_ {State::IDLE};
+    ::std::atomic<bool> finishedRendering_ {true};
+    ::std::mutex mutex_ {};
+    ::std::condition_variable rendered_ {};
+    ::std::unique_ptr<::std::thread> thread_ {};
+    ::std::string error_ {};
+    double renderingSeconds_ {0.0};
+
+public:
+    explicit B200RenderThread(B200Renderer &renderer) : renderer_ {renderer} {}
+    B200RenderThread(const B200RenderThread &) = delete;
+    B200RenderThread &operator=(const B200RenderThread &) = delete;
+    ~B200RenderThread() { stopRender(true); finishRender(); }
+
+    /* rtStartRender (JNI_layer.cpp:406-426) */
+    void startRender(bool wait) {
+        if (wait) {
+            ::std::unique_lock<::std::mutex> lock {mutex_};
+            rendered_.wait(lock, [&] { return finishedRendering_.load(); });
+        }
+        finishedRendering_ = false;
+        state_ = State::BUSY;
+    }
+
+    /* rtRenderIntoBitmap (JNI_layer.cpp:744-901): `repeats` frames into the caller's bitmap on a worker thread (async) or here */
+    void renderIntoBitmap(::std::int32_t *bitmap, ::std::int32_t nThreads, bool async, ::std::int32_t repeats = 1) {
+        finishRender();
+        auto work = [this, bitmap, nThreads, repeats]() {
+            ::std::int32_t rep {repeats};
+            const auto t0 = ::std::chrono::steady_clock::now();
+            try {
+                while (state_ == State::BUSY && rep > 0) { renderer_.renderFrame(bitmap, nThreads); --rep; }
+            } catch (const ::std::exception &e) {
+                error_ = e.what();
+            }
+            renderingSeconds_ = ::std::chrono::duration<double>(::std::chrono::steady_clock::now() - t0).count();
+            finishedRendering_ = true;
+            rendered_.notify_all();
+            {
+                const ::std::lock_guard<::std::mutex> lock {mutex_};
+                if (state_ != State::STOPPED) { state_ = State::FINISHED; }
+            }
+            state_ = State::IDLE;
+        };
+        if (async) { thread_.reset(new ::std::thread(work)); } else { work(); }
+    }
+
+    /* rtStopRender (JNI_layer.cpp:428-462) */
+    void stopRender(bool wait) {
+        state_ = State::STOPPED;
+        ::std::unique_lock<::std::mutex> lock {mutex_};
+        renderer_.stopRender();
+        if (wait) {
+            while (!finishedRendering_) {
+                renderer_.stopRender();
+                rendered_.wait_for(lock, ::std::chrono::milliseconds(50), [&] { return finishedRendering_.load(); });
+            }
+        }
+    }
+
+    /* rtFinishRender: join the worker */
+    void finishRender() { if (thread_ && thread_->joinable()) { thread_->join(); } thread_.reset(); }
+    /* rtGetState (JNI_layer.cpp:904-913) */
+    State getState() const { return state_.load(); }
+    ::std::int32_t getSample() const { return renderer_.getSample(); }
+    double getRenderingSeconds() const { return renderingSeconds_; }
+    const ::std::string &getError() const { return error_; }
 };
 
 }  // namespace MobileRT

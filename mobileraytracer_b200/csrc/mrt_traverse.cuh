@@ -101,29 +101,10 @@ struct Trav8 {
 struct TravMem {
     uint2 stack[kStack8 + 1];  // node groups still to visit; entry kStack8 only ever receives the unconditional store of a full stack
     uint2 pend[kPend];         // parked leaf groups (x = triangle base, y = pending triangle bits); per-thread callers only
-#ifdef MRT_SMEM_STACK
-    uint32_t sh = 0u;          // wavefront kernels: shared-window address of this thread's column of the CTA's short stack (entry stride kShStackStride)
-    int lim = 0;               // entries [0, lim) live in shared memory, the rest in stack[] (0 for the per-thread callers)
-#endif
 };
-#ifdef MRT_SMEM_STACK
-constexpr int kShStackStride = 128;   // = kWfThreads: lane-consecutive 8-byte entries, two conflict-free wavefronts per warp access
-MRT_D void stack_put(TravMem &tm, int i, uint2 v) {
-    if (i < tm.lim) {
-        asm volatile("st.shared.v2.u32 [%0], {%1, %2};" :: "r"(tm.sh + static_cast<uint32_t>(i) * (kShStackStride * 8u)), "r"(v.x), "r"(v.y) : "memory");
-    } else { tm.stack[i - tm.lim] = v; }
-}
-MRT_D uint2 stack_get(const TravMem &tm, int i) {
-    uint2 v;
-    if (i < tm.lim) {
-        asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(tm.sh + static_cast<uint32_t>(i) * (kShStackStride * 8u)) : "memory");
-    } else { v = tm.stack[i - tm.lim]; }
-    return v;
-}
-#else
+// (a shared-memory short stack for the first entries was measured slower in every size, profiles/r1_ab_short_stack_s43.txt)
 MRT_D void stack_put(TravMem &tm, int i, uint2 v) { tm.stack[i] = v; }
 MRT_D uint2 stack_get(const TravMem &tm, int i) { return tm.stack[i]; }
-#endif
 
 #ifdef MRT_TRAVERSAL_STATS
 static __device__ unsigned long long g_stat_nodes, g_stat_tris, g_stat_rays;   // one copy per translation unit

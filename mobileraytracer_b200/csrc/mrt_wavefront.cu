@@ -272,12 +272,6 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
     uint32_t count = 0;              // node items in the warp's list (warp-uniform)
     Trav8 t;
     TravMem tmem;
-#ifdef MRT_SMEM_STACK
-    __shared__ uint2 shstack[MRT_SMEM_STACK * kWfThreads];
-    static_assert(kShStackStride == kWfThreads, "short-stack stride");
-    tmem.sh = static_cast<uint32_t>(__cvta_generic_to_shared(shstack + threadIdx.x));
-    tmem.lim = MRT_SMEM_STACK;
-#endif
     t.o = mk3(0.0f, 0.0f, 0.0f);
     t.ngroup = make_uint2(0u, 0u); t.sp = 0; t.tbest = 0.0f;
     MRT_STAT(t.n_nodes = 0u; t.n_tris = 0u;)
@@ -403,17 +397,6 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
                 if (!(t.ngroup.y & 0xff000000u)) { t.ngroup = top; --t.sp; }
                 if (!trav8_node_core(s, t, tmem, tbase, lh, m0, m1, &overflow, permp)) { t.ngroup.y = 0u; t.sp = 0; lh = 0u; }
                 node_work = (t.ngroup.y & 0xff000000u) != 0u || t.sp > 0;
-#ifdef MRT_NODE_PREFETCH   // paid off while the kernel waited on L1 misses; now it is ALU bound and the 14 extra instructions per step cost 3-4 %
-                if (t.ngroup.y & 0xff000000u) {
-                    // the node this lane visits next is known now: pull it into L1 while the warp does the list / triangle work
-                    const uint32_t nbit = 31u - __clz(t.ngroup.y);
-                    const uint32_t nslot = (nbit - 24u) ^ (t.octinv4 & 0xffu);
-                    const uint32_t nrel = __popc(t.ngroup.y & ((1u << nslot) - 1u) & 0xffu);
-                    const char *np = reinterpret_cast<const char *>(s.nodes) + 80ull * (t.ngroup.x + nrel);
-                    asm volatile("prefetch.global.L1 [%0];" :: "l"(np));
-                    asm volatile("prefetch.global.L1 [%0];" :: "l"(np + 64));
-                }
-#endif
             }
         }
         // append one node item per lane that hit leaves: positions from the ballot, no atomics, no loop
@@ -1016,16 +999,6 @@ cudaError_t wavefront_trace_batch(Wavefront *w, const SceneDev &s, const CameraR
     Queues &Q = w->q;
     if (n_samples < 1 || n_samples > w->batch) { return cudaErrorInvalidValue; }
     const int grid = w->sm_count * MRT_TRAV_MIN_BLOCKS;
-#if defined(MRT_SMEM_STACK) && MRT_SMEM_STACK > 3
-    {   // above 3 entries the short stack needs a larger shared-memory carve-out than the default build's 164 KB to hold MRT_TRAV_MIN_BLOCKS CTAs per SM
-        static bool carved = false;
-        if (!carved) {
-            WF_TRY(cudaFuncSetAttribute(k_wf_extend, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-            WF_TRY(cudaFuncSetAttribute(k_wf_shadow, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-            carved = true;
-        }
-    }
-#endif
     WF_TRY(wf_mark(w, -1, st));
     WF_TRY(cudaMemsetAsync(Q.counts, 0, kWfCounts * sizeof(uint32_t), st));
     const int patches = rp.n_tiles * ((rp.bsx + 7) / 8) * ((rp.bsy + 3) / 4);

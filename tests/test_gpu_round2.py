@@ -418,3 +418,31 @@ def test_sort_by_material_renders_the_same_frame(mrt, conf, key, monkeypatch):
         g.close()
     assert acc[0][1] == acc[1][1]
     assert torch.equal(acc[0][0], acc[1][0])
+
+
+def test_cpp_render_thread_state_machine(mrt, tmp_path):
+    """SURVEY 8(f) rank 3 / VERDICT r1 missing #6: MobileRT::B200RenderThread (include/mobilert_b200_renderer.hpp) is the render
+    thread + State machine the Android front-end wraps around renderFrame (JNI_layer.cpp:406-462,744-913). The adapter
+    executable renders scene 3 (Whitted, 512 x 512, many samples) on a worker thread with MRT_FLAG_PROGRESSIVE while its main
+    thread polls getSample() and the bitmap like the UI does: partial frames are visible, the finished frame equals the
+    blocking call's frame, and stopRender(true) ends a frame early and leaves the machine IDLE."""
+    exe = os.path.join(ROOT, "oracle", "_ref", "b200_adapter_demo")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/b200_adapter_demo not built (needs /root/reference at build time)")
+    spp = 3000
+    args = ["3", "1", "512", "512", str(spp), "1"]
+    sync_out, async_out, stop_out = (str(tmp_path / n) for n in ("sync.raw", "async.raw", "stop.raw"))
+    r = subprocess.run([exe] + args + [sync_out], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, (r.stdout, r.stderr)
+    r = subprocess.run([exe] + args + [async_out], capture_output=True, text=True, timeout=600, env=dict(os.environ, MRT_DEMO_ASYNC="1"))
+    assert r.returncode == 0, (r.stdout, r.stderr)
+    f = dict(zip(r.stdout.split()[1::2], r.stdout.split()[2::2]))     # "async polls N busy N partial N stopped N final_sample N state N secs X"
+    assert int(f["busy"]) > 0 and int(f["partial"]) > 0, r.stdout
+    assert int(f["final_sample"]) == spp and int(f["state"]) == 0, r.stdout
+    assert np.array_equal(np.fromfile(async_out, np.int32), np.fromfile(sync_out, np.int32))
+    r = subprocess.run([exe] + args + [stop_out], capture_output=True, text=True, timeout=600,
+                       env=dict(os.environ, MRT_DEMO_ASYNC="1", MRT_DEMO_STOP_AT="200"))
+    assert r.returncode == 0, (r.stdout, r.stderr)
+    f = dict(zip(r.stdout.split()[1::2], r.stdout.split()[2::2]))
+    assert int(f["stopped"]) == 1 and 200 <= int(f["final_sample"]) < spp and int(f["state"]) == 0, r.stdout
+    assert (np.fromfile(stop_out, np.int32) != 0).mean() > 0.5

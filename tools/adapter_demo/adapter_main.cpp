@@ -7,6 +7,9 @@
 // Built only where /root/reference exists (oracle/Makefile, target adapter), against the reference's headers and the
 // compiled reference library oracle/_ref/libmobilert_ref.so (for Scenes.cpp / loaders), into oracle/_ref/.
 //   b200_adapter_demo <scene 0..3 | obj mtl cam> <shader> <width> <height> <spp> <spl> <out.raw>
+// With MRT_DEMO_ASYNC=1 the frame is rendered by MobileRT::B200RenderThread (the render thread + State machine of
+// Android_JNI/JNI_layer.cpp:406-462,744-913) with MRT_FLAG_PROGRESSIVE while this thread polls getSample() and the bitmap like
+// the UI does; MRT_DEMO_STOP_AT=<sample> calls stopRender(true) once that sample has been reached.
 #include "mobilert_b200_renderer.hpp"
 
 #include "Components/Loaders/CameraFactory.hpp"
@@ -18,6 +21,7 @@
 #include <cstdlib>
 #include <fstream>
 #include <iostream>
+#include <thread>
 #include <unordered_map>
 
 using namespace MobileRT;
@@ -54,9 +58,34 @@ int main(int argc, char **argv) {
             }
         }
         errno = 0;
-        B200Renderer renderer {scene, *camera, width, height, spp, spl, shader, MRT_SAMPLER_AUTO, 0u, maxDist};
+        const char *asyncEnv {::std::getenv("MRT_DEMO_ASYNC")}, *stopEnv {::std::getenv("MRT_DEMO_STOP_AT")};
+        const bool async {asyncEnv != nullptr && ::std::atoi(asyncEnv) != 0};
+        B200Renderer renderer {scene, *camera, width, height, spp, spl, shader, MRT_SAMPLER_AUTO, async ? static_cast<::std::uint32_t>(MRT_FLAG_PROGRESSIVE) : 0u, maxDist};
         ::std::vector<::std::int32_t> bitmap(static_cast<size_t>(width) * static_cast<size_t>(height), 0);
-        renderer.renderFrame(bitmap.data(), 1);
+        if (async) {
+            B200RenderThread worker {renderer};
+            worker.startRender(false);
+            worker.renderIntoBitmap(bitmap.data(), 1, true);
+            const int stopAt {stopEnv != nullptr ? ::std::atoi(stopEnv) : -1};
+            int partialFrames {0}, polls {0}, busySeen {0};
+            bool stopped {false};
+            while (worker.getState() == B200RenderThread::State::BUSY || worker.getState() == B200RenderThread::State::STOPPED) {
+                const int sample {worker.getSample()};
+                ++polls;
+                if (worker.getState() == B200RenderThread::State::BUSY) { ++busySeen; }
+                size_t filled {0};
+                for (size_t i {0}; i < bitmap.size(); i += 97) { filled += bitmap[i] != 0 ? 1u : 0u; }
+                if (sample > 0 && sample < spp && filled * 97 * 2 > bitmap.size()) { ++partialFrames; }
+                if (stopAt >= 0 && sample >= stopAt && !stopped) { worker.stopRender(true); stopped = true; }
+                ::std::this_thread::sleep_for(::std::chrono::milliseconds(1));
+            }
+            worker.finishRender();
+            if (!worker.getError().empty()) { ::std::fprintf(stderr, "worker: %s\n", worker.getError().c_str()); return 6; }
+            ::std::printf("async polls %d busy %d partial %d stopped %d final_sample %d state %d secs %.4f\n", polls, busySeen, partialFrames, stopped ? 1 : 0,
+                          renderer.getSample(), static_cast<int>(worker.getState()), worker.getRenderingSeconds());
+        } else {
+            renderer.renderFrame(bitmap.data(), 1);
+        }
         if (errno != 0) { ::std::fprintf(stderr, "errno left at %d\n", errno); return 4; }   // the front-ends poll errno right after the frame (C_wrapper.cpp:234)
         ::std::FILE *f {::std::fopen(outPath, "wb")};
         if (f == nullptr) { return 5; }

@@ -27,6 +27,6 @@ for _ in range(a.frames):
     r.renderFrame(bm)
 st = r.stats()
 rays = st["rays_primary"] + st["rays_shadow"] + st["rays_secondary"]
-print({k: st[k] for k in ("frame_ms", "extend_ms", "shadow_ms", "shade_ms", "other_ms", "launches", "build_ms", "bvh_nodes")},
+print({k: st[k] for k in ("frame_ms", "extend_ms", "shadow_ms", "shade_ms", "other_ms", "launches", "build_ms", "bvh_nodes", "rays_extend_traced", "rays_shadow_traced")},
       "Mrays/s %.1f" % (rays / st["frame_ms"] / 1e3), "nonblack %.3f" % float((bm != -16777216).mean()))
 r.close()
