@@ -603,6 +603,7 @@ int render_samples(mrt_handle *h, int32_t *d_bitmap, float4 *d_accum, int sample
     FrameTargets tg {d_bitmap, d_accum};
     WavefrontTimes wt {};
     uint64_t launches = 0;
+    uint64_t samples_rendered = 0;   // megakernel path: samples launched (one camera ray per path slot each, Ray.cpp:11)
     const int spp = h->rp.spp;
     h->stats.pass_retries = 0;
     bool stopped = false;
@@ -690,6 +691,7 @@ int render_samples(mrt_handle *h, int32_t *d_bitmap, float4 *d_accum, int sample
             API_CUDA(h, launch_render_sample(h->scene, h->camera, h->rp, h->d_inv_tile.as<int2>(), s, d_bitmap ? s + 1 : k + 1, tg,
                                              h->d_counters.as<DeviceCounters>(), st, rep));
             ++launches;
+            ++samples_rendered;
             API_CUDA(h, progress_refresh(h, d_bitmap));
             while (h->sample_events.size() < depth) { cudaEvent_t e; API_CUDA(h, cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); h->sample_events.push_back(e); }
             API_CUDA(h, cudaEventRecord(h->sample_events[static_cast<size_t>(k) % depth], st));
@@ -699,6 +701,7 @@ int render_samples(mrt_handle *h, int32_t *d_bitmap, float4 *d_accum, int sample
     DeviceCounters hc {};
     API_CUDA(h, cudaMemcpyAsync(&hc, h->d_counters.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
     API_CUDA(h, cudaStreamSynchronize(st));
+    hc.rays_primary += samples_rendered * h->roots_per_sample;
     float ms = 0.0f;
     cudaEventElapsedTime(&ms, h->ev0, h->ev1);
     if (h->wavefront) { API_CUDA(h, wavefront_collect_times(h->wavefront, &wt)); }

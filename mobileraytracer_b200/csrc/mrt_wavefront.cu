@@ -93,14 +93,13 @@ MRT_D void unpack_skip(uint32_t s, int &kind, int &idx) { kind = static_cast<int
 // ---- generate: Renderer::renderScene's jitter + Camera::generateRay (Renderer.cpp:130-141) ---------------------------
 __global__ void __launch_bounds__(kWfThreads) k_wf_generate(Queues Q, SceneDev s, CameraRec cam, RenderParams rp,
                                                             const int2 *__restrict__ tile_origin, const uint32_t *__restrict__ tile_base,
-                                                            uint32_t roots_per_sample, BatchInts samples, DeviceCounters *dc) {
+                                                            uint32_t roots_per_sample, BatchInts samples) {
     const int sample = samples.v[blockIdx.y];                       // blockIdx.y: position of the sample in the pass
     const uint32_t slot_base = blockIdx.y * roots_per_sample;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int patch = blockIdx.x * (kWfThreads / 32) + warp;
     uint32_t q = 0;
     int x, y, pix;
-    RayCounters rc = {0u, 0u, 0u};
     int tile, rank;
     if (tile_pixel(rp, tile_origin, patch, lane, sample, x, y, pix, q, &tile, &rank)) {
         const float invImgWidth = 1.0f / static_cast<float>(rp.width), invImgHeight = 1.0f / static_cast<float>(rp.height);
@@ -114,15 +113,15 @@ __global__ void __launch_bounds__(kWfThreads) k_wf_generate(Queues Q, SceneDev s
         // 32 bytes per camera ray; its accumulator (chain `slot`) is initialised by the shade kernel of level 0
         Q.r0[0][slot] = make_float4(o.x, o.y, o.z, d.x);
         Q.r1[0][slot] = make_float4(d.y, d.z, __uint_as_float(q), __int_as_float(pix));
-        rc.primary = 1u;
     }
-    const uint32_t p = __reduce_add_sync(0xffffffffu, rc.primary);
-    if (lane == 0 && p) { atomicAdd(&dc->rays_primary, static_cast<unsigned long long>(p)); }
+    // (the camera rays are counted by k_wf_begin_levels: one same-address atomicAdd per warp here, 1 M per launch at about 0.7 ns
+    // each, was three quarters of this kernel's time)
 }
 
 // the chain pool starts right after the root chains: camera paths of batch sample i are chains [i, i + 1) * roots_per_sample
-__global__ void k_wf_begin_levels(Queues Q, uint32_t n_samples, uint32_t roots_per_sample) {
+__global__ void k_wf_begin_levels(Queues Q, uint32_t n_samples, uint32_t roots_per_sample, DeviceCounters *dc) {
     Q.counts[0] = n_samples * roots_per_sample; Q.counts[9] = n_samples * roots_per_sample;
+    dc->rays_primary += static_cast<unsigned long long>(n_samples) * roots_per_sample;   // every path slot holds one camera ray (Ray.cpp:11)
 }
 
 // ---- extend / shadow: persistent traversal kernels --------------------------------------------------------------
@@ -263,6 +262,9 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
     const int b = level & 1;
     const uint32_t n = ANY ? min(Q.counts[8], Q.cap_shadow) : min(Q.counts[level], Q.cap_rays);
     uint32_t *work = &Q.counts[ANY ? kCounterShadow : kCounterExtend];
+#ifdef MRT_WORK_CHUNK
+    uint32_t chunk_next = 0u, chunk_end = 0u;   // the warp's current chunk of the queue (warp-uniform)
+#endif
     int overflow = 0;
     bool exhausted = false;
     bool node_work = false;          // this lane has pending inner nodes
@@ -327,6 +329,31 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
             }
             hasmask &= ~done;
         }
+#ifdef MRT_WORK_CHUNK
+        // refill the idle lanes from the warp's own chunk of the queue; when it runs out, one atomicAdd on the level's work counter
+        // fetches the next chunk and the same refill is completed from it (one round trip per MRT_WORK_CHUNK rays instead of per refill)
+        if (refill_now) {
+            const uint32_t idle = ~hasmask;
+            const uint32_t want = __popc(idle), avail = chunk_end - chunk_next;
+            const uint32_t rank = __popc(idle & (lane_bit - 1u));
+            uint32_t cur = chunk_next + rank;
+            bool have = rank < avail;
+            if (avail < want) {
+                uint32_t base = 0;
+                if (lane == 0) { base = atomicAdd(work, static_cast<uint32_t>(MRT_WORK_CHUNK)); }
+                base = __shfl_sync(full, base, 0);
+                const uint32_t nn = base < n ? base : n, ne = base + MRT_WORK_CHUNK < n ? base + MRT_WORK_CHUNK : n;
+                if (rank >= avail) { cur = nn + (rank - avail); have = cur < ne; }
+                const uint32_t used = want - avail < ne - nn ? want - avail : ne - nn;
+                chunk_next = nn + used; chunk_end = ne;
+                if (nn == ne) { exhausted = true; }
+            } else {
+                chunk_next += want;
+            }
+            bool got = false;
+            if ((idle & lane_bit) && have) {
+                {
+#else
         // refill the idle lanes (one warp-aggregated atomicAdd on the level's work counter per refill; handing every warp chunks
         // of 32-128 rays per atomicAdd instead was measured slower, shadow +5 %, extend +1 %: a chunk that runs out in the middle
         // of a refill leaves lanes idle until the next one)
@@ -340,6 +367,7 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
             if (idle & lane_bit) {
                 const uint32_t cur = base + __popc(idle & (lane_bit - 1u));
                 if (cur < n) {
+#endif
                     HitRec h;
                     const float4 a = ANY ? Q.s0[cur] : Q.r0[b][cur], c = ANY ? Q.s1[cur] : Q.r1[b][cur];
 #ifndef MRT_NO_QUEUE_PREFETCH
@@ -1007,8 +1035,8 @@ cudaError_t wavefront_trace_batch(Wavefront *w, const SceneDev &s, const CameraR
     BatchInts sl {};
     for (int i = 0; i < n_samples; ++i) { sl.v[i] = samples[i]; }
     const dim3 ggrid(static_cast<unsigned>((patches + kWfThreads / 32 - 1) / (kWfThreads / 32)), static_cast<unsigned>(n_samples));
-    k_wf_generate<<<ggrid, kWfThreads, 0, st>>>(Q, s, cam, rp, d_tile_origin, d_tile_base, roots_per_sample, sl, dc);
-    k_wf_begin_levels<<<1, 1, 0, st>>>(Q, static_cast<uint32_t>(n_samples), roots_per_sample);
+    k_wf_generate<<<ggrid, kWfThreads, 0, st>>>(Q, s, cam, rp, d_tile_origin, d_tile_base, roots_per_sample, sl);
+    k_wf_begin_levels<<<1, 1, 0, st>>>(Q, static_cast<uint32_t>(n_samples), roots_per_sample, dc);
     WF_TRY(wf_mark(w, WF_OTHER, st));
     *launches += 2;
     const int sgrid = w->sm_count * MRT_SHADE_MIN_BLOCKS;
