@@ -262,9 +262,6 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
     const int b = level & 1;
     const uint32_t n = ANY ? min(Q.counts[8], Q.cap_shadow) : min(Q.counts[level], Q.cap_rays);
     uint32_t *work = &Q.counts[ANY ? kCounterShadow : kCounterExtend];
-#ifdef MRT_WORK_CHUNK
-    uint32_t chunk_next = 0u, chunk_end = 0u;   // the warp's current chunk of the queue (warp-uniform)
-#endif
     int overflow = 0;
     bool exhausted = false;
     bool node_work = false;          // this lane has pending inner nodes
@@ -329,34 +326,10 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
             }
             hasmask &= ~done;
         }
-#ifdef MRT_WORK_CHUNK
-        // refill the idle lanes from the warp's own chunk of the queue; when it runs out, one atomicAdd on the level's work counter
-        // fetches the next chunk and the same refill is completed from it (one round trip per MRT_WORK_CHUNK rays instead of per refill)
-        if (refill_now) {
-            const uint32_t idle = ~hasmask;
-            const uint32_t want = __popc(idle), avail = chunk_end - chunk_next;
-            const uint32_t rank = __popc(idle & (lane_bit - 1u));
-            uint32_t cur = chunk_next + rank;
-            bool have = rank < avail;
-            if (avail < want) {
-                uint32_t base = 0;
-                if (lane == 0) { base = atomicAdd(work, static_cast<uint32_t>(MRT_WORK_CHUNK)); }
-                base = __shfl_sync(full, base, 0);
-                const uint32_t nn = base < n ? base : n, ne = base + MRT_WORK_CHUNK < n ? base + MRT_WORK_CHUNK : n;
-                if (rank >= avail) { cur = nn + (rank - avail); have = cur < ne; }
-                const uint32_t used = want - avail < ne - nn ? want - avail : ne - nn;
-                chunk_next = nn + used; chunk_end = ne;
-                if (nn == ne) { exhausted = true; }
-            } else {
-                chunk_next += want;
-            }
-            bool got = false;
-            if ((idle & lane_bit) && have) {
-                {
-#else
         // refill the idle lanes (one warp-aggregated atomicAdd on the level's work counter per refill; handing every warp chunks
-        // of 32-128 rays per atomicAdd instead was measured slower, shadow +5 %, extend +1 %: a chunk that runs out in the middle
-        // of a refill leaves lanes idle until the next one)
+        // of 64-128 rays per atomicAdd instead was measured slower twice, extend +1.7 %, shadow +2.8 % even when a refill is
+        // completed from the next chunk: warps that run side by side then no longer work on neighbouring queue entries,
+        // profiles/r2_ab_sign_pack_and_tuning.txt)
         if (refill_now) {
             const uint32_t idle = ~hasmask;
             uint32_t base = 0;
@@ -367,7 +340,6 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
             if (idle & lane_bit) {
                 const uint32_t cur = base + __popc(idle & (lane_bit - 1u));
                 if (cur < n) {
-#endif
                     HitRec h;
                     const float4 a = ANY ? Q.s0[cur] : Q.r0[b][cur], c = ANY ? Q.s1[cur] : Q.r1[b][cur];
 #ifndef MRT_NO_QUEUE_PREFETCH
