@@ -23,7 +23,9 @@ typedef enum mrt_status {
     MRT_ERR_CUDA = 2,      /* CUDA runtime error or no device; see mrt_last_error() */
     MRT_ERR_OOM = 3,       /* host or device allocation failed (JNI maps this to LowMemoryException, JNI_layer.cpp:706-715) */
     MRT_ERR_STOPPED = 4,   /* mrt_stop() was called while rendering (Renderer::stopRender, MobileRT/Renderer.cpp:93-99) */
-    MRT_ERR_OVERFLOW = 5   /* an internal queue or traversal stack overflowed; result is invalid */
+    MRT_ERR_OVERFLOW = 5   /* a traversal stack overflowed, or the path tracer's ray queues overflowed even at the largest size the
+                              library allocates (an overflowing pass is first repeated with fewer samples, then with doubled queues:
+                              mrt_stats::pass_retries); result is invalid */
 } mrt_status;
 
 /* ---- scene records: byte-for-byte the reference's own layouts ---------------------------------------------- */

@@ -27,7 +27,7 @@ constexpr int kWfThreads = 128;
 #define MRT_TRAV_MIN_BLOCKS 8     // CTAs per SM of the persistent traversal kernels (64 registers per thread)
 #endif
 #ifndef MRT_SHADE_MIN_BLOCKS
-#define MRT_SHADE_MIN_BLOCKS 3    // CTAs of 256 threads per SM of the shade kernel: 80 registers per thread (4 CTAs = 64 registers spilled: +37 %; 2 CTAs: +24 %; 1: 2.2x, profiles/r2_ab_shade.txt)
+#define MRT_SHADE_MIN_BLOCKS 6    // CTAs per SM of the shade kernel: 768 threads, 80 registers per thread (1024 threads = 64 registers spilled: +37 %; 512: +24 %; 256: 2.2x, profiles/r2_ab_shade.txt)
 #endif
 
 // One sector per chain. info: bits 0..2 = j* (0: no vertex had direct light yet), bit 3 = ended on an emitter,
@@ -518,14 +518,16 @@ MRT_D float pt_draw(const float *__restrict__ table, int is_perm, uint32_t q, ui
     return is_perm ? __uint_as_float(0x3F800000u | (i << 3)) - 1.0f : __ldg(table + i);
 }
 
-constexpr int kShadeThreads = 256;
+#ifndef MRT_SHADE_THREADS
+#define MRT_SHADE_THREADS 128     // 128 x 6 CTAs per SM: 4.49 ms per 16-sample pass; 256 x 3: 4.89 (more warps wait at the two barriers); 512 x 1: 6.78
+#endif
+constexpr int kShadeThreads = MRT_SHADE_THREADS;
 constexpr int kShadeMatCap = 64, kShadeLightCap = 256;   // records staged in shared memory (64 bytes each); larger scenes read them from global memory
 
 // One light sample of a vertex (PathTracer.cpp:60-82): Shader::getLightIndex (Shader.cpp:223-233), then
 // PointLight::getPosition (PointLight.cpp:16-18) or AreaLight::getPosition (AreaLight.cpp:17-26). True when the light point
 // lies in front of the surface, i.e. when the reference casts the shadow ray.
 struct LightSample { v3 dir; float dist; v3 ld; };
-MRT_D uint32_t dir_octant(v3 d) { return (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u); }
 MRT_D bool pt_light_sample(const SceneDev &s, const RenderParams &rp, const float4 *lightp, const Surface &sf, uint32_t q, uint32_t eb, uint32_t k,
                            LightSample &ls) {
     const float rl = pt_draw(s.shader_table, s.shader_table_is_perm, q, eb + k, DS_LIGHT_INDEX, rp.seed);
@@ -549,8 +551,9 @@ MRT_D bool pt_light_sample(const SceneDev &s, const RenderParams &rp, const floa
 }
 
 // Queue slots are handed out per CTA: every thread first decides what its hit emits (phase 1), a block-wide prefix sum turns
-// the counts into offsets and ONE thread per queue bumps the global counter for all 256 hits, then the records are written
-// (phase 2). With one warp-aggregated atomicAdd per push site the kernel spent 48 % of its stall samples waiting for the two
+// the counts into offsets and ONE thread per queue bumps the global counter for all of the CTA's hits, then the records are written
+// (phase 2). (Laying the CTA's records out by direction octant instead of hit order was measured too: traversal -0.5 %, this
+// kernel +12 %, profiles/r2_ab_material_sort_and_octant_bins.txt.) With one warp-aggregated atomicAdd per push site the kernel spent 48 % of its stall samples waiting for the two
 // same-address atomics of the shadow and ray queues (2 M per 33 M-hit launch, about 0.7 ns each at the L2;
 // profiles/r2_shade_before_ncu_summary.txt). Consecutive hits now also get consecutive slots.
 template <bool L0>
@@ -560,9 +563,6 @@ __global__ void __launch_bounds__(kShadeThreads, MRT_SHADE_MIN_BLOCKS) k_wf_shad
     __shared__ float4 sm_light[kShadeLightCap * 4];
     __shared__ unsigned long long sm_warp[kShadeThreads / 32];   // per warp: shadow rays | rays << 24 | chains << 44 of this iteration
     __shared__ uint32_t sm_base[3];
-#ifdef MRT_BIN_OCTANT
-    __shared__ uint32_t sm_bin[3][8];   // this iteration's records per direction octant: shadow rays, rays; [2][0]: chains
-#endif
     const bool mat_sh = s.n_materials <= kShadeMatCap, light_sh = s.n_lights <= kShadeLightCap;
     if (mat_sh) { for (int k = threadIdx.x; k < s.n_materials * 4; k += kShadeThreads) { sm_mat[k] = __ldg(reinterpret_cast<const float4 *>(s.materials) + k); } }
     if (light_sh) { for (int k = threadIdx.x; k < s.n_lights * 4; k += kShadeThreads) { sm_light[k] = __ldg(reinterpret_cast<const float4 *>(s.lights) + k); } }
@@ -587,8 +587,6 @@ __global__ void __launch_bounds__(kShadeThreads, MRT_SHADE_MIN_BLOCKS) k_wf_shad
         uint32_t q = 0u, branch = 1u, chain = i, eb = 0u;
         int depth = 1;
         float r_h0 = 0.0f, r_h1 = 0.0f;
-        uint32_t sbin = 0u, rbin = 0u;                  // direction octants of the first shadow ray / of the diffuse ray
-        v3 nd_diffuse = mk3(0.0f, 0.0f, 0.0f);
         if (j < n) {
             // the records of this thread's next iteration start their trip from HBM to L2 now
             if (Q.perm == nullptr && i + stride < n) {
@@ -640,10 +638,9 @@ __global__ void __launch_bounds__(kShadeThreads, MRT_SHADE_MIN_BLOCKS) k_wf_shad
                     if (diffuse && s.n_lights > 0) {                    // PathTracer.cpp:55-87: direct light, one shadow ray per light sample
                         first_lit = pt_light_sample(s, rp, lightp, sf, q, eb, 0u, ls0);
                         ns = first_lit ? 1u : 0u;
-                        if (first_lit) { sbin = dir_octant(ls0.dir); }
                         for (int k = 1; k < rp.spl; ++k) {
                             LightSample ls;
-                            if (pt_light_sample(s, rp, lightp, sf, q, eb, static_cast<uint32_t>(k), ls)) { if (ns == 0u) { sbin = dir_octant(ls.dir); } ++ns; }
+                            if (pt_light_sample(s, rp, lightp, sf, q, eb, static_cast<uint32_t>(k), ls)) { ++ns; }
                         }
                         rc.shadow += ns;
                     }
@@ -653,38 +650,9 @@ __global__ void __launch_bounds__(kShadeThreads, MRT_SHADE_MIN_BLOCKS) k_wf_shad
                     rc.secondary += (go ? 1u : 0u) + (spec ? 1u : 0u) + (trans ? 1u : 0u);
                     if (traceable) { nc = (spec ? 1u : 0u) + (trans ? 1u : 0u); nr = nc + (go ? 1u : 0u); }
                     else { go = false; spec = false; trans = false; }
-                    if (go) { nd_diffuse = cosine_sample_hemisphere(sf.normal, r_h0, r_h1); rbin = dir_octant(nd_diffuse); }
                 }
             }
         }
-#ifdef MRT_BIN_OCTANT
-        // ---- slots: the CTA's records are laid out by direction octant (8 bins per queue, shared-memory counters), so that the rays
-        // a traversal warp picks up together descend the BVH8 in the same child order; one global atomicAdd per queue
-        if (threadIdx.x < 17u) { (&sm_bin[0][0])[threadIdx.x] = 0u; }
-        __syncthreads();
-        uint32_t spos = 0u, rpos = 0u, cpos = 0u;
-        if (ns) { spos = atomicAdd(&sm_bin[0][sbin], ns); }
-        if (nr) { rpos = atomicAdd(&sm_bin[1][rbin], nr); }
-        if (nc) { cpos = atomicAdd(&sm_bin[2][0], nc); }
-        __syncthreads();
-        uint32_t sbefore = 0u, rbefore = 0u, stotal = 0u, rtotal = 0u;
-#pragma unroll
-        for (uint32_t k = 0; k < 8u; ++k) {
-            const uint32_t a0 = sm_bin[0][k], a1 = sm_bin[1][k];
-            stotal += a0; rtotal += a1;
-            if (k < sbin) { sbefore += a0; }
-            if (k < rbin) { rbefore += a1; }
-        }
-        if (threadIdx.x < 3u) {
-            const uint32_t cnt = threadIdx.x == 0u ? stotal : (threadIdx.x == 1u ? rtotal : sm_bin[2][0]);
-            uint32_t *ctr = &Q.counts[threadIdx.x == 0u ? 8 : (threadIdx.x == 1u ? level + 1 : 9)];
-            sm_base[threadIdx.x] = cnt ? atomicAdd(ctr, cnt) : 0u;
-        }
-        __syncthreads();
-        uint32_t sslot = sm_base[0] + sbefore + spos;
-        uint32_t rslot = sm_base[1] + rbefore + rpos;
-        uint32_t cslot = sm_base[2] + cpos;
-#else
         // ---- slots: prefix sums over the CTA, one atomicAdd per queue
         unsigned long long mine = static_cast<unsigned long long>(ns) | (static_cast<unsigned long long>(nr) << 24) | (static_cast<unsigned long long>(nc) << 44);
         unsigned long long incl = mine;
@@ -713,7 +681,6 @@ __global__ void __launch_bounds__(kShadeThreads, MRT_SHADE_MIN_BLOCKS) k_wf_shad
         uint32_t sslot = sm_base[0] + static_cast<uint32_t>(excl & 0xffffffu);
         uint32_t rslot = sm_base[1] + static_cast<uint32_t>((excl >> 24) & 0xfffffu);
         uint32_t cslot = sm_base[2] + static_cast<uint32_t>(excl >> 44);
-#endif
         if (!shading) { continue; }
         // ---- phase 2: write the records
         const uint32_t skip = pack_skip(sf.skipKind, sf.skipIdx);
@@ -733,7 +700,7 @@ __global__ void __launch_bounds__(kShadeThreads, MRT_SHADE_MIN_BLOCKS) k_wf_shad
             }
         }
         if (go) {                                                   // PathTracer.cpp:89-111: indirect diffuse
-            const v3 nd = nd_diffuse;
+            const v3 nd = cosine_sample_hemisphere(sf.normal, r_h0, r_h1);
             v3 Tn = T * sf.Kd;
             if (depth > kRayDepthMin) { Tn = Tn / (0.5f * 0.5f); }
             if (rslot < Q.cap_rays) {
