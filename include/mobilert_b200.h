@@ -127,7 +127,10 @@ typedef struct mrt_render_desc {
     int32_t shader;                 /* MRT_SHADER_* */
     int32_t accelerator;            /* MRT_ACC_B200 or MRT_ACC_BVH: the reference's BVH visibility rules (finite plane boxes,
                                        root-box NaN rule); MRT_ACC_NAIVE: Naive<T>'s rules (every plane / sphere tested, caller
-                                       order). Triangles go through the BVH8 either way. MRT_ACC_REGULAR_GRID is rejected. */
+                                       order); triangles go through the BVH8 in both. MRT_ACC_REGULAR_GRID: RegularGrid<T>'s rules
+                                       (Accelerators/RegularGrid.hpp:112-513: three 32^3 grids built on the host with
+                                       T::intersect(AABB), rays walked from the clamped start cell); no BVH is built then and
+                                       every ray runs the reference's 3-D DDA, one thread per ray (a compatibility mode: slow). */
     int32_t pixel_sampler;          /* MRT_SAMPLER_* */
     uint32_t seed;                  /* seeds the library's own table shuffles when mrt_sampler_tables is NULL */
     uint32_t flags;                 /* MRT_FLAG_* */

@@ -75,7 +75,7 @@ public:
                  ::std::int32_t frontEndSampler = MRT_SAMPLER_AUTO,
                  ::std::uint32_t flags = 0u /* MRT_FLAG_*, e.g. MRT_FLAG_PROGRESSIVE for a UI that shows the bitmap while it renders */,
                  const ::glm::vec3 &depthMaxPoint = ::glm::vec3 {1.0F, 1.0F, 1.0F} /* DepthMap's maxPoint (C_wrapper.cpp:80-138) */,
-                 ::std::int32_t accelerator = MRT_ACC_B200 /* or MRT_ACC_NAIVE for Naive's visibility rules */) {
+                 ::std::int32_t accelerator = MRT_ACC_B200 /* or MRT_ACC_NAIVE / MRT_ACC_REGULAR_GRID for those accelerators' visibility rules */) {
         ::std::vector<mrt_triangle> tris; tris.reserve(scene.triangles_.size());
         for (const Triangle &t : scene.triangles_) { tris.push_back(flatten(t)); }
         ::std::vector<mrt_sphere> spheres;

@@ -73,7 +73,7 @@ SYMBOLS = ["mrt_create", "mrt_destroy", "mrt_render_frame", "mrt_render_frame_de
            "mrt_last_error", "mrt_trace_rays", "mrt_generate_rays", "mrt_shade_rays", "mrt_device_count", "mrt_version"]
 # every symbol include/mobilert_b200_test.h declares (libmobilert_b200_test.so: the device functions one call at a time)
 TEST_SYMBOLS = ["mrt_test_triangle_intersect", "mrt_test_sphere_intersect", "mrt_test_plane_intersect", "mrt_test_aabb_intersect",
-                "mrt_test_incremental_avg", "mrt_test_halton", "mrt_test_last_error"]
+                "mrt_test_incremental_avg", "mrt_test_halton", "mrt_test_build_grid", "mrt_test_last_error"]
 
 _lib = None
 
@@ -139,6 +139,7 @@ def test_lib():
         L.mrt_test_aabb_intersect.argtypes = [vp, vp, vp, vp, vp]
         L.mrt_test_incremental_avg.argtypes = [vp, i32, i32, vp]
         L.mrt_test_halton.argtypes = [C.c_uint32, i64, C.c_uint32, vp]
+        L.mrt_test_build_grid.argtypes = [C.POINTER(SceneDesc), i32, vp, vp, vp, i64, C.POINTER(i64)]
         L.mrt_test_last_error.restype = C.c_char_p
         _test_lib = L
     return _test_lib

@@ -2,12 +2,14 @@
 // Host logic only; every ray is traced by the CUDA kernels of mrt_render.cu / mrt_wavefront.cu. No CPU fallback.
 #include "../../include/mobilert_b200.h"
 #include "mrt_build.h"
+#include "mrt_grid.h"
 #include "mrt_refbvh.h"
 #include "mrt_render.h"
 #include "mrt_wavefront.h"
 #include <algorithm>
 #include <atomic>
 #include <cerrno>
+#include <chrono>
 #include <cstdlib>
 #include <cstring>
 #include <mutex>
@@ -40,6 +42,7 @@ struct DevMem {
 
 struct mrt_handle {
     bool naive = false;              // MRT_ACC_NAIVE semantics for planes / spheres / the triangle root box
+    bool grid = false;               // MRT_ACC_REGULAR_GRID: the reference's three 32^3 grids instead of the BVHs
     uint32_t roots_per_sample = 0;   // valid pixels of one sample (wavefront path slots)
     bool tiles_disjoint = true;      // no two path slots of a sample share a pixel (false for image sizes that are not multiples of 16)
     uint32_t replay_index_counter = 0;   // MRT_FLAG_REPLAY_SAMPLERS: value of Shader::getLightIndex's counter at the next frame's first draw
@@ -53,6 +56,7 @@ struct mrt_handle {
     RenderParams rp {};
     uint32_t flags = 0;
     Bvh8 bvh {};
+    DevMem d_grid_start[3], d_grid_items[3], d_grid_tris;
     DevMem d_tris9, d_tri_shade, d_sphere_nodes, d_spheres, d_plane_nodes, d_planes, d_materials, d_lights;
     DevMem d_tile, d_shader_table, d_static_halton, d_static_mt, d_static_pcg, d_inv_tile, d_tile_base, d_textures, d_texels, d_bitmap, d_accum, d_counters, d_counters_saved, d_pixel_stream;
     std::vector<int> plane_slot_of_id, sphere_slot_of_id;
@@ -240,10 +244,33 @@ int upload_scene(mrt_handle *h, const mrt_scene_desc &sc) {
         nodes.push_back(RefNode{-3.0e38f, -3.0e38f, -3.0e38f, 3.0e38f, 3.0e38f, 3.0e38f, 0, static_cast<int32_t>(count)});
         for (size_t i = 0; i < count; ++i) { order.push_back(static_cast<int>(i)); }
     };
-    if (h->naive) { naive_leaf(static_cast<size_t>(sc.n_planes), pnodes, porder); } else { build_ref_bvh(boxes, pnodes, porder); }
+    // MRT_ACC_REGULAR_GRID: caller order as well (the grids' cell lists hold caller indices), no binary tree at all
+    const bool flat = h->naive || h->grid;
+    GridHost grids[3];
+    const auto grid_t0 = std::chrono::steady_clock::now();
+    if (flat) { naive_leaf(static_cast<size_t>(sc.n_planes), pnodes, porder); } else { build_ref_bvh(boxes, pnodes, porder); }
+    if (h->grid) { build_ref_grid(boxes, [&](int64_t i, const HostBox &cell) { return grid_plane_overlaps(sc.planes[i].normal, sc.planes[i].point, cell); }, grids[0]); }
     boxes.clear();
     for (int64_t i = 0; i < sc.n_spheres; ++i) { boxes.push_back(hb_sphere(sc.spheres[i].center, sc.spheres[i].sq_radius)); }
-    if (h->naive) { naive_leaf(static_cast<size_t>(sc.n_spheres), snodes, sorder); } else { build_ref_bvh(boxes, snodes, sorder); }
+    if (flat) { naive_leaf(static_cast<size_t>(sc.n_spheres), snodes, sorder); } else { build_ref_bvh(boxes, snodes, sorder); }
+    if (h->grid) { build_ref_grid(boxes, [&](int64_t i, const HostBox &cell) { return grid_sphere_overlaps(sc.spheres[i].center, sc.spheres[i].sq_radius, cell); }, grids[1]); }
+    std::vector<TriGeom> grid_tris;
+    if (h->grid) {
+        boxes.clear();
+        boxes.reserve(static_cast<size_t>(nt));
+        grid_tris.resize(static_cast<size_t>(nt > 0 ? nt : 1));
+        for (int64_t i = 0; i < nt; ++i) {
+            const mrt_triangle &t = sc.triangles[i];
+            boxes.push_back(hb_triangle(t.A, t.AB, t.AC));
+            float idbits;
+            const int32_t id = static_cast<int32_t>(i);
+            std::memcpy(&idbits, &id, 4);
+            grid_tris[static_cast<size_t>(i)] = TriGeom{make_float4(t.A[0], t.A[1], t.A[2], t.AB[0]), make_float4(t.AB[1], t.AB[2], t.AC[0], t.AC[1]), make_float4(t.AC[2], idbits, 0.0f, 0.0f)};
+        }
+        build_ref_grid(boxes, [&](int64_t i, const HostBox &cell) { return grid_triangle_overlaps(sc.triangles[i].A, sc.triangles[i].AB, sc.triangles[i].AC, cell); }, grids[2]);
+        boxes.clear();
+    }
+    const float grid_build_ms = std::chrono::duration<float, std::milli>(std::chrono::steady_clock::now() - grid_t0).count();
     std::vector<PlaneRec> planes(porder.size() ? porder.size() : 1);
     h->plane_slot_of_id.assign(porder.size(), 0);
     for (size_t sidx = 0; sidx < porder.size(); ++sidx) {
@@ -263,7 +290,7 @@ int upload_scene(mrt_handle *h, const mrt_scene_desc &sc) {
     cudaEvent_t e0, e1;
     API_CUDA(h, cudaEventCreate(&e0)); API_CUDA(h, cudaEventCreate(&e1));
     API_CUDA(h, cudaEventRecord(e0, st));
-    API_CUDA(h, h->d_tris9.upload(tris9.data(), tris9.size() * sizeof(float), st));
+    if (!h->grid) { API_CUDA(h, h->d_tris9.upload(tris9.data(), tris9.size() * sizeof(float), st)); }
     API_CUDA(h, h->d_tri_shade.upload(shade.data(), shade.size() * sizeof(TriShade), st));
     API_CUDA(h, h->d_lights.upload(lights.data(), lights.size() * sizeof(LightRec), st));
     API_CUDA(h, h->d_materials.upload(mats.data(), mats.size() * sizeof(MaterialRec), st));
@@ -273,12 +300,46 @@ int upload_scene(mrt_handle *h, const mrt_scene_desc &sc) {
     API_CUDA(h, h->d_planes.upload(planes.data(), planes.size() * sizeof(PlaneRec), st));
     API_CUDA(h, h->d_sphere_nodes.upload(snodes.data(), snodes.size() * sizeof(RefNode), st));
     API_CUDA(h, h->d_spheres.upload(spheres.data(), spheres.size() * sizeof(SphereRec), st));
+    size_t grid_bytes = 0;
+    if (h->grid) {
+        API_CUDA(h, h->d_grid_tris.upload(grid_tris.data(), grid_tris.size() * sizeof(TriGeom), st));
+        grid_bytes += grid_tris.size() * sizeof(TriGeom);
+        for (int k = 0; k < 3; ++k) {
+            API_CUDA(h, h->d_grid_start[k].upload(grids[k].start.data(), grids[k].start.size() * sizeof(uint32_t), st));
+            API_CUDA(h, h->d_grid_items[k].upload(grids[k].items.data(), grids[k].items.size() * sizeof(int32_t), st));
+            grid_bytes += grids[k].start.size() * sizeof(uint32_t) + grids[k].items.size() * sizeof(int32_t);
+            GridDev &g = h->scene.grids[k];
+            g.bmin = mk3(grids[k].bmin[0], grids[k].bmin[1], grids[k].bmin[2]);
+            g.cellInv = mk3(grids[k].cellInv[0], grids[k].cellInv[1], grids[k].cellInv[2]);
+            g.cellSize = mk3(grids[k].cellSize[0], grids[k].cellSize[1], grids[k].cellSize[2]);
+            g.start = h->d_grid_start[k].as<uint32_t>(); g.items = h->d_grid_items[k].as<int32_t>();
+        }
+    }
     API_CUDA(h, cudaEventRecord(e1, st));
     API_CUDA(h, cudaEventSynchronize(e1));
     float ms = 0.0f;
     cudaEventElapsedTime(&ms, e0, e1);
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     h->stats.upload_ms = ms;
+    h->stats.n_primitives = nt + sc.n_spheres + sc.n_planes;
+    if (h->grid) {
+        // no BVH8: the grids are the acceleration structure (built on the host above; build_ms is that wall time)
+        h->stats.build_ms = grid_build_ms;
+        h->stats.bvh_nodes = 0;
+        h->stats.bvh_bytes = grid_bytes;
+        h->stats.scene_bytes = grid_bytes + shade.size() * sizeof(TriShade) + mats.size() * sizeof(MaterialRec) + lights.size() * sizeof(LightRec);
+        SceneDev &s = h->scene;
+        s.grid = 1; s.naive = 0; s.prmt_one = 0x3F800000u;
+        s.tune_postpone = 12; s.tune_refill = 26; s.tune_wait = 20; s.tune_wait_any = 24;
+        s.nodes = nullptr; s.tri_geom = h->d_grid_tris.as<TriGeom>(); s.tri_shade = h->d_tri_shade.as<TriShade>();
+        s.n_triangles = static_cast<int32_t>(nt); s.n_bvh_prims = static_cast<int32_t>(nt);
+        s.sphere_nodes = h->d_sphere_nodes.as<RefNode>(); s.spheres = h->d_spheres.as<SphereRec>(); s.n_spheres = static_cast<int32_t>(sc.n_spheres);
+        s.plane_nodes = h->d_plane_nodes.as<RefNode>(); s.planes = h->d_planes.as<PlaneRec>(); s.n_planes = static_cast<int32_t>(sc.n_planes);
+        s.materials = h->d_materials.as<MaterialRec>(); s.n_materials = static_cast<int32_t>(sc.n_materials);
+        s.textures = h->d_textures.as<TextureRec>(); s.texels = h->d_texels.as<uint8_t>(); s.n_textures = static_cast<int32_t>(sc.n_textures);
+        s.lights = h->d_lights.as<LightRec>(); s.n_lights = static_cast<int32_t>(nl);
+        return MRT_OK;
+    }
     // acceleration structure over triangles + light triangles, on the GPU
     // binned-SAH hierarchy by default; MRT_B200_BVH=lbvh selects the Morton-order hierarchy (build-speed / quality experiments)
     const char *bvh_env = std::getenv("MRT_B200_BVH");
@@ -447,8 +508,8 @@ int mrt_create(const mrt_scene_desc *scene, const mrt_camera_desc *camera, const
     *out = nullptr;
     if (render->width <= 0 || render->height <= 0 || render->samples_pixel < 0 || render->samples_light < 0) { return fail(nullptr, MRT_ERR_INVALID, "bad render size / sample counts"); }
     if (render->shader < 0 || render->shader > 4) { return fail(nullptr, MRT_ERR_INVALID, "unknown shader"); }
-    if (render->accelerator != MRT_ACC_B200 && render->accelerator != MRT_ACC_BVH && render->accelerator != MRT_ACC_NAIVE) {
-        return fail(nullptr, MRT_ERR_INVALID, "accelerator must be MRT_ACC_B200 / MRT_ACC_BVH (BVH semantics) or MRT_ACC_NAIVE (the reference's Naive visibility rules); RegularGrid is not provided");
+    if (render->accelerator != MRT_ACC_B200 && render->accelerator != MRT_ACC_BVH && render->accelerator != MRT_ACC_NAIVE && render->accelerator != MRT_ACC_REGULAR_GRID) {
+        return fail(nullptr, MRT_ERR_INVALID, "accelerator must be MRT_ACC_B200 / MRT_ACC_BVH (BVH semantics), MRT_ACC_NAIVE or MRT_ACC_REGULAR_GRID (the reference's visibility rules for those)");
     }
     if (scene->n_triangles < 0 || scene->n_spheres < 0 || scene->n_planes < 0 || scene->n_materials < 0 || scene->n_lights < 0) { return fail(nullptr, MRT_ERR_INVALID, "negative count"); }
     if ((scene->n_triangles && !scene->triangles) || (scene->n_spheres && !scene->spheres) || (scene->n_planes && !scene->planes) ||
@@ -479,6 +540,7 @@ int mrt_create(const mrt_scene_desc *scene, const mrt_camera_desc *camera, const
         if (e != cudaSuccess) { rc = cuda_fail(h, e, "device setup"); break; }
         h->flags = render->flags;
         h->naive = render->accelerator == MRT_ACC_NAIVE;
+        h->grid = render->accelerator == MRT_ACC_REGULAR_GRID;
         h->rp.width = render->width; h->rp.height = render->height; h->rp.spp = render->samples_pixel; h->rp.spl = render->samples_light;
         h->rp.shader = render->shader; h->rp.seed = render->seed;
         h->rp.bsx = render->width / 16; h->rp.bsy = render->height / 16;   // Renderer.cpp:33-34

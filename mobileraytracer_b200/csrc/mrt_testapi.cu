@@ -3,6 +3,7 @@
 // the product's device code: it compiles the same headers (mrt_math.cuh) as libmobilert_b200.so but is not linked into it,
 // so a front-end that links the product library gets none of these symbols. Built with -fmad=false like the product.
 #include "../../include/mobilert_b200_test.h"
+#include "mrt_grid.h"
 #include "mrt_math.cuh"
 #include <cerrno>
 #include <cstring>
@@ -176,5 +177,29 @@ int mrt_test_halton(uint32_t first, int64_t n, uint32_t base, float *out) {
     return MRT_OK;
 }
 
+
+// Host code only (no device needed): the cell lists libmobilert_b200.so builds for MRT_ACC_REGULAR_GRID (mrt_grid.h)
+int mrt_test_build_grid(const mrt_scene_desc *scene, int32_t kind, float *out_params12, uint32_t *out_start, int32_t *out_items, int64_t items_cap,
+                        int64_t *out_n_items) {
+    if (!scene || kind < 0 || kind > 2 || !out_params12 || !out_start || !out_n_items) { return fail(MRT_ERR_INVALID, "null argument or kind outside 0..2"); }
+    std::vector<HostBox> boxes;
+    GridHost g;
+    if (kind == 0) {
+        for (int64_t i = 0; i < scene->n_planes; ++i) { boxes.push_back(hb_plane(scene->planes[i].normal, scene->planes[i].point)); }
+        build_ref_grid(boxes, [&](int64_t i, const HostBox &cell) { return grid_plane_overlaps(scene->planes[i].normal, scene->planes[i].point, cell); }, g);
+    } else if (kind == 1) {
+        for (int64_t i = 0; i < scene->n_spheres; ++i) { boxes.push_back(hb_sphere(scene->spheres[i].center, scene->spheres[i].sq_radius)); }
+        build_ref_grid(boxes, [&](int64_t i, const HostBox &cell) { return grid_sphere_overlaps(scene->spheres[i].center, scene->spheres[i].sq_radius, cell); }, g);
+    } else {
+        for (int64_t i = 0; i < scene->n_triangles; ++i) { boxes.push_back(hb_triangle(scene->triangles[i].A, scene->triangles[i].AB, scene->triangles[i].AC)); }
+        build_ref_grid(boxes, [&](int64_t i, const HostBox &cell) { return grid_triangle_overlaps(scene->triangles[i].A, scene->triangles[i].AB, scene->triangles[i].AC, cell); }, g);
+    }
+    for (int k = 0; k < 3; ++k) { out_params12[k] = g.bmin[k]; out_params12[3 + k] = g.bmax[k]; out_params12[6 + k] = g.cellInv[k]; out_params12[9 + k] = g.cellSize[k]; }
+    std::memcpy(out_start, g.start.data(), g.start.size() * sizeof(uint32_t));
+    *out_n_items = static_cast<int64_t>(g.items.size());
+    if (out_items) { std::memcpy(out_items, g.items.data(), static_cast<size_t>(std::min<int64_t>(items_cap, *out_n_items)) * sizeof(int32_t)); }
+    errno = 0;
+    return MRT_OK;
+}
 
 }  // extern "C"

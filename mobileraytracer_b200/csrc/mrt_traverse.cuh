@@ -396,11 +396,111 @@ MRT_D void trace_lights_linear(const SceneDev &s, v3 o, v3 d, HitRec &h) {
     }
 }
 
+// ---- the reference's regular grids (MRT_ACC_REGULAR_GRID) ---------------------------------------------------------
+// RegularGrid<T>::intersect (Accelerators/RegularGrid.hpp:333-513) on the cell lists of mrt_grid.h, one thread per ray:
+// the 3-D DDA starts in the cell of the ray origin CLAMPED into the grid (a ray that starts outside is walked from the
+// nearest border cell with the boundary distances of that cell, RegularGrid.hpp:337-347), tests every primitive of a
+// cell against the running nearest hit, and once any cell has produced a hit it stops as soon as the hit lies before the
+// next cell boundary (the reference's second loop, :461-512; re-testing the first hit's cell there changes nothing). A
+// shadow ray returns at its first hit (:436-438). PRIM: 0 planes, 1 spheres, 2 triangles. Performance is not a goal
+// here; the point is that a front-end configured for this accelerator sees the reference's visibility, quirks included.
+MRT_D int32_t grid_to_int(float v) {   // static_cast<int32_t> of the reference's x86-64 build: out of range and NaN give INT_MIN
+    return (v > -2147483904.0f && v < 2147483648.0f) ? __float2int_rz(v) : static_cast<int32_t>(0x80000000u);
+}
+
+template <int PRIM>
+MRT_D bool trace_grid(const SceneDev &s, v3 o, v3 d, bool shadow, int skipKind, int skipIdx, HitRec &h) {
+    const int nprims = PRIM == 0 ? s.n_planes : (PRIM == 1 ? s.n_spheres : s.n_triangles);
+    if (nprims == 0) { return false; }
+    constexpr int kSize = 32, kShift = 5;
+    const GridDev &g = s.grids[PRIM];
+    const float oo[3] = {o.x, o.y, o.z}, dd[3] = {d.x, d.y, d.z};
+    const float bmin[3] = {g.bmin.x, g.bmin.y, g.bmin.z}, csize[3] = {g.cellSize.x, g.cellSize.y, g.cellSize.z}, cinv[3] = {g.cellInv.x, g.cellInv.y, g.cellInv.z};
+    int32_t cell[3], step[3], out[3];
+    float tmax[3], tdelta[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        int32_t c = grid_to_int((oo[k] - bmin[k]) * cinv[k]);
+        c = min(c, kSize - 1);
+        c = max(c, 0);
+        float cb;
+        if (dd[k] > 0.0f) { step[k] = 1; out[k] = kSize; cb = bmin[k] + (static_cast<float>(c) + 1.0f) * csize[k]; }
+        else { step[k] = -1; out[k] = -1; cb = bmin[k] + static_cast<float>(c) * csize[k]; }
+        if (fabsf(dd[k]) > 1.1920929e-7f) {
+            const float r = 1.0f / dd[k];
+            tmax[k] = (cb - oo[k]) * r;
+            tdelta[k] = csize[k] * static_cast<float>(step[k]) * r;
+        } else { tmax[k] = kRayLengthMax; tdelta[k] = 0.0f; }
+        cell[k] = c;
+    }
+    bool found = false;
+    while (true) {
+        const uint32_t idx = static_cast<uint32_t>(cell[0]) + (static_cast<uint32_t>(cell[1]) << kShift) + (static_cast<uint32_t>(cell[2]) << (2 * kShift));
+        const uint32_t first = __ldg(g.start + idx), last = __ldg(g.start + idx + 1);
+        const float before = h.t;
+        for (uint32_t i = first; i < last; ++i) {
+            const int id = __ldg(g.items + i);
+            float t, u = 0.0f, v = 0.0f;
+            bool ok;
+            if (PRIM == 0) {
+                const PlaneRec p = s.planes[id];
+                ok = !(skipKind == HIT_PLANE && skipIdx == id) && plane_intersect(mk3(p.nx, p.ny, p.nz), mk3(p.px, p.py, p.pz), o, d, t);
+            } else if (PRIM == 1) {
+                const SphereRec sp_ = s.spheres[id];
+                ok = sphere_intersect(mk3(sp_.cx, sp_.cy, sp_.cz), sp_.sqRadius, o, d, t);
+            } else {
+                const float4 *tp = reinterpret_cast<const float4 *>(s.tri_geom) + 3ull * static_cast<uint32_t>(id);
+                const float4 g0 = __ldg(tp), g1 = __ldg(tp + 1), g2 = __ldg(tp + 2);
+                ok = !(skipKind == HIT_TRIANGLE && skipIdx == id) && tri_hit(g0, g1, g2, o, d, h.t, t, u, v);
+            }
+            if (ok && t < h.t) {
+                h.t = t; h.kind = PRIM == 0 ? HIT_PLANE : (PRIM == 1 ? HIT_SPHERE : HIT_TRIANGLE); h.idx = id; h.u = u; h.v = v;
+                if (shadow) { return true; }
+            }
+        }
+        found = found || h.t < before;
+        if (tmax[0] < tmax[1]) {
+            if (tmax[0] < tmax[2]) {
+                if (found && h.t < tmax[0]) { break; }
+                cell[0] += step[0]; if (cell[0] == out[0]) { break; } tmax[0] = tmax[0] + tdelta[0];
+            } else {
+                if (found && h.t < tmax[2]) { break; }
+                cell[2] += step[2]; if (cell[2] == out[2]) { break; } tmax[2] = tmax[2] + tdelta[2];
+            }
+        } else {
+            if (tmax[1] < tmax[2]) {
+                if (found && h.t < tmax[1]) { break; }
+                cell[1] += step[1]; if (cell[1] == out[1]) { break; } tmax[1] = tmax[1] + tdelta[1];
+            } else {
+                if (found && h.t < tmax[2]) { break; }
+                cell[2] += step[2]; if (cell[2] == out[2]) { break; } tmax[2] = tmax[2] + tdelta[2];
+            }
+        }
+    }
+    return false;
+}
+
+// Shader::rayTrace / shadowTrace with Accelerator::ACC_REGULAR_GRID (Shader.cpp:97-102,142-147): the three grids share one
+// running t, then every light is tested (Shader.cpp:166-171)
+MRT_D void trace_closest_grid(const SceneDev &s, v3 o, v3 d, int skipKind, int skipIdx, HitRec &h) {
+    trace_grid<0>(s, o, d, false, skipKind, skipIdx, h);
+    trace_grid<1>(s, o, d, false, skipKind, skipIdx, h);
+    trace_grid<2>(s, o, d, false, skipKind, skipIdx, h);
+    if (s.n_lights > 0) { trace_lights_linear(s, o, d, h); }
+}
+MRT_D bool trace_shadow_grid(const SceneDev &s, v3 o, v3 d, float distance, int skipKind, int skipIdx) {
+    HitRec h;
+    h.t = distance; h.kind = HIT_NONE; h.idx = -1; h.u = 0.0f; h.v = 0.0f;
+    return trace_grid<0>(s, o, d, true, skipKind, skipIdx, h) || trace_grid<1>(s, o, d, true, skipKind, skipIdx, h) ||
+           trace_grid<2>(s, o, d, true, skipKind, skipIdx, h);
+}
+
 // Shader::rayTrace's geometric part (Shader.cpp:86-111): planes, then spheres, then triangles share one running t;
 // area lights are tested last with the same strict "<" rule, which the tie rule of trace_bvh8 reproduces because
 // light primitive ids come after all scene triangles.
 MRT_D void trace_closest(const SceneDev &s, v3 o, v3 d, int skipKind, int skipIdx, HitRec &h, int *overflow) {
     h.t = kRayLengthMax; h.kind = HIT_NONE; h.idx = -1; h.u = 0.0f; h.v = 0.0f;
+    if (s.grid) { trace_closest_grid(s, o, d, skipKind, skipIdx, h); return; }
     trace_ref_bvh<0>(s, o, d, false, skipKind, skipIdx, h, overflow);
     trace_ref_bvh<1>(s, o, d, false, skipKind, skipIdx, h, overflow);
     if (s.n_bvh_prims == 0) { return; }
@@ -418,6 +518,7 @@ MRT_D void trace_closest(const SceneDev &s, v3 o, v3 d, int skipKind, int skipId
 
 // Shader::shadowTrace (Shader.cpp:132-158): true when something lies within `distance`.
 MRT_D bool trace_shadow(const SceneDev &s, v3 o, v3 d, float distance, int skipKind, int skipIdx, int *overflow) {
+    if (s.grid) { return trace_shadow_grid(s, o, d, distance, skipKind, skipIdx); }
     HitRec h;
     h.t = distance; h.kind = HIT_NONE; h.idx = -1; h.u = 0.0f; h.v = 0.0f;
     if (trace_ref_bvh<0>(s, o, d, true, skipKind, skipIdx, h, overflow)) { return true; }

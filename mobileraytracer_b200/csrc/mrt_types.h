@@ -53,6 +53,9 @@ struct CameraRec {
     float a, b;  // perspective: hFov, vFov in radians; orthographic: sizeH/2, sizeV/2
 };
 
+// One RegularGrid<T> of the reference (mrt_grid.h): cell c = x + (y << 5) + (z << 10) holds items[start[c] .. start[c + 1])
+struct GridDev { v3 bmin, cellInv, cellSize; const uint32_t *start; const int32_t *items; };
+
 enum HitKind : int32_t { HIT_NONE = 0, HIT_PLANE = 1, HIT_SPHERE = 2, HIT_TRIANGLE = 3, HIT_LIGHT = 4 };
 
 // Everything a traversal / shading kernel needs, passed by value as a kernel parameter.
@@ -78,6 +81,10 @@ struct SceneDev {
     // 1: the table is a permutation of {k / 2^20} (what fillArrayWithHaltonSeq + std::shuffle produce, Utils.hpp:209-218), so the
     // value of a uniformly chosen slot can be computed instead of gathered (wavefront path tracer, mrt_wavefront.cu pt_draw)
     int32_t shader_table_is_perm, static_halton_is_perm;
+    // MRT_ACC_REGULAR_GRID: 1 = every ray walks the reference's three grids (0 planes, 1 spheres, 2 triangles) instead of the
+    // BVHs; planes / spheres / tri_geom are then stored in the caller's order and there is no BVH8 (nodes == nullptr)
+    int32_t grid;
+    GridDev grids[3];
 };
 
 struct RenderParams {

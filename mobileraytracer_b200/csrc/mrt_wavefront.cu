@@ -433,6 +433,31 @@ MRT_D void wf_traverse(const SceneDev &s, const Queues &Q, int level, DeviceCoun
 __global__ void __launch_bounds__(kWfThreads, MRT_TRAV_MIN_BLOCKS) k_wf_extend(SceneDev s, Queues Q, int level, DeviceCounters *dc) { wf_traverse<false>(s, Q, level, dc); }
 __global__ void __launch_bounds__(kWfThreads, MRT_TRAV_MIN_BLOCKS) k_wf_shadow(SceneDev s, Queues Q, DeviceCounters *dc) { wf_traverse<true>(s, Q, 0, dc); }
 
+// MRT_ACC_REGULAR_GRID: the same queue records in and out, one thread per ray walking the reference's grids (trace_grid,
+// mrt_traverse.cuh). Not tuned: this mode exists for its visibility rules, not for speed.
+__global__ void __launch_bounds__(256) k_wf_extend_grid(SceneDev s, Queues Q, int level) {
+    const int b = level & 1;
+    const uint32_t n = min(Q.counts[level], Q.cap_rays);
+    for (uint32_t cur = blockIdx.x * blockDim.x + threadIdx.x; cur < n; cur += gridDim.x * blockDim.x) {
+        const float4 a = Q.r0[b][cur], c = Q.r1[b][cur];
+        int sk, si;
+        unpack_skip(level == 0 ? 0u : __float_as_uint(c.z), sk, si);
+        HitRec h;
+        h.t = kRayLengthMax; h.kind = HIT_NONE; h.idx = -1; h.u = 0.0f; h.v = 0.0f;
+        trace_closest_grid(s, mk3(a.x, a.y, a.z), mk3(a.w, c.x, c.y), sk, si, h);
+        Q.hit[cur] = make_float4(h.t, h.u, h.v, __uint_as_float(pack_hit(h)));
+    }
+}
+__global__ void __launch_bounds__(256) k_wf_shadow_grid(SceneDev s, Queues Q) {
+    const uint32_t n = min(Q.counts[8], Q.cap_shadow);
+    for (uint32_t cur = blockIdx.x * blockDim.x + threadIdx.x; cur < n; cur += gridDim.x * blockDim.x) {
+        const float4 a = Q.s0[cur], c = Q.s1[cur];
+        int sk, si;
+        unpack_skip(__float_as_uint(c.w), sk, si);
+        Q.vis[cur] = trace_shadow_grid(s, mk3(a.x, a.y, a.z), mk3(a.w, c.x, c.y), c.z, sk, si) ? 0 : 1;
+    }
+}
+
 // Shader::getCosineSampleHemisphere (Shader.cpp:188-216)
 MRT_D v3 cosine_sample_hemisphere(v3 normal, float uniformRandom1, float uniformRandom2) {
     const float phi = 6.28318530717958647692528676655900576f * uniformRandom1;
@@ -980,7 +1005,7 @@ cudaError_t wavefront_trace_batch(Wavefront *w, const SceneDev &s, const CameraR
     *launches += 2;
     const int sgrid = w->sm_count * MRT_SHADE_MIN_BLOCKS;
     for (int level = 0; level < kLevels; ++level) {
-        k_wf_extend<<<grid, kWfThreads, 0, st>>>(s, Q, level, dc);
+        if (s.grid) { k_wf_extend_grid<<<grid, 256, 0, st>>>(s, Q, level); } else { k_wf_extend<<<grid, kWfThreads, 0, st>>>(s, Q, level, dc); }
         WF_TRY(wf_mark(w, WF_EXTEND, st));
         if (Q.perm != nullptr) {
             WF_TRY(cudaMemsetAsync(Q.sort_bins, 0, (kSortBins + 1) * sizeof(uint32_t), st));
@@ -994,7 +1019,7 @@ cudaError_t wavefront_trace_batch(Wavefront *w, const SceneDev &s, const CameraR
         else { k_wf_shade<false><<<sgrid, kShadeThreads, 0, st>>>(s, rp, Q, level, dc); }
         WF_TRY(wf_mark(w, WF_SHADE, st));
         k_wf_after_shade<<<1, 1, 0, st>>>(Q, level, dc);
-        k_wf_shadow<<<grid, kWfThreads, 0, st>>>(s, Q, dc);
+        if (s.grid) { k_wf_shadow_grid<<<grid, 256, 0, st>>>(s, Q); } else { k_wf_shadow<<<grid, kWfThreads, 0, st>>>(s, Q, dc); }
         WF_TRY(wf_mark(w, WF_SHADOW, st));
         k_wf_fold<<<w->sm_count * 8, 256, 0, st>>>(Q);
         k_wf_after_fold<<<1, 1, 0, st>>>(Q, dc);
@@ -1099,8 +1124,13 @@ cudaError_t wavefront_trace_rays(Wavefront *w, const SceneDev &s, int64_t n, con
     WF_TRY(cudaMemsetAsync(Q.counts, 0, kWfCounts * sizeof(uint32_t), st));
     const int blocks = static_cast<int>((n + 255) / 256), grid = w->sm_count * MRT_TRAV_MIN_BLOCKS;
     k_wf_test_fill<<<blocks, 256, 0, st>>>(Q, n, d_o, d_d, d_okind, d_oidx, d_sdist);
-    k_wf_extend<<<grid, kWfThreads, 0, st>>>(s, Q, kTestLevel, dc);
-    k_wf_shadow<<<grid, kWfThreads, 0, st>>>(s, Q, dc);
+    if (s.grid) {
+        k_wf_extend_grid<<<grid, 256, 0, st>>>(s, Q, kTestLevel);
+        k_wf_shadow_grid<<<grid, 256, 0, st>>>(s, Q);
+    } else {
+        k_wf_extend<<<grid, kWfThreads, 0, st>>>(s, Q, kTestLevel, dc);
+        k_wf_shadow<<<grid, kWfThreads, 0, st>>>(s, Q, dc);
+    }
     k_wf_test_gather<<<blocks, 256, 0, st>>>(s, Q, d_t, d_kind, d_idx, d_mat, d_normal);
     return cudaGetLastError();
 }

@@ -31,6 +31,7 @@
 #include "MobileRT/Scene.hpp"
 #include "Scenes/Scenes.hpp"
 #include "C_wrapper.h"
+#include <algorithm>
 #include <chrono>
 #include <cstring>
 #include <fstream>
@@ -74,6 +75,23 @@ struct Quiet {
 NullBuf Quiet::sink;
 double now() {
     return ::std::chrono::duration<double>(::std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+// see ref_grid_cells
+template <typename T>
+long long gridCells(RegularGrid<T> &g, float *params, unsigned *start, int *items, long long cap) {
+    const ::glm::vec3 mn {g.worldBoundaries_.getPointMin()}, mx {g.worldBoundaries_.getPointMax()};
+    for (int k = 0; k < 3; ++k) { params[k] = mn[k]; params[3 + k] = mx[k]; params[6 + k] = g.cellSizeInverted_[k]; params[9 + k] = g.cellSize_[k]; }
+    long long total {0};
+    const T *base {g.primitives_.data()};
+    for (size_t c = 0; c < g.grid_.size(); ++c) {
+        start[c] = static_cast<unsigned>(total);
+        ::std::vector<int> ids {};
+        for (const T *prim : g.grid_[c]) { ids.push_back(static_cast<int>(prim - base)); }
+        ::std::sort(ids.begin(), ids.end());
+        for (const int id : ids) { if (items != nullptr && total < cap) { items[total] = id; } ++total; }
+    }
+    start[g.grid_.size()] = static_cast<unsigned>(total);
+    return total;
 }
 }
 
@@ -339,10 +357,32 @@ void ref_trace_rays(void *p, int n, const float *o, const float *d, const int *o
         Intersection isect {::std::move(ray), shadow ? shadowDist[i] : RayLengthMax};
         const float start {isect.length_};
         int kind {0}, idx {-1};
-        isect = s.bvhPlanes_.trace(isect);
+        // the accelerator the Shader was built with (Shader.cpp:89-110,134-155); shadowTrace == trace for the grid (RegularGrid.hpp:308-311)
+        const auto tracePlanes = [&](Intersection in) {
+            switch (s.accelerator_) {
+                case Shader::ACC_NAIVE: return shadow ? s.naivePlanes_.shadowTrace(in) : s.naivePlanes_.trace(in);
+                case Shader::ACC_REGULAR_GRID: return shadow ? s.gridPlanes_.shadowTrace(in) : s.gridPlanes_.trace(in);
+                default: return shadow ? s.bvhPlanes_.shadowTrace(in) : s.bvhPlanes_.trace(in);
+            }
+        };
+        const auto traceSpheres = [&](Intersection in) {
+            switch (s.accelerator_) {
+                case Shader::ACC_NAIVE: return shadow ? s.naiveSpheres_.shadowTrace(in) : s.naiveSpheres_.trace(in);
+                case Shader::ACC_REGULAR_GRID: return shadow ? s.gridSpheres_.shadowTrace(in) : s.gridSpheres_.trace(in);
+                default: return shadow ? s.bvhSpheres_.shadowTrace(in) : s.bvhSpheres_.trace(in);
+            }
+        };
+        const auto traceTriangles = [&](Intersection in) {
+            switch (s.accelerator_) {
+                case Shader::ACC_NAIVE: return shadow ? s.naiveTriangles_.shadowTrace(in) : s.naiveTriangles_.trace(in);
+                case Shader::ACC_REGULAR_GRID: return shadow ? s.gridTriangles_.shadowTrace(in) : s.gridTriangles_.trace(in);
+                default: return shadow ? s.bvhTriangles_.shadowTrace(in) : s.bvhTriangles_.trace(in);
+            }
+        };
+        isect = tracePlanes(isect);
         if (isect.length_ < start) { kind = 1; idx = static_cast<int>(static_cast<const Plane *>(isect.primitive_) - plas.data()); }
         float before {isect.length_};
-        isect = s.bvhSpheres_.trace(isect);
+        isect = traceSpheres(isect);
         if (isect.length_ < before) {
             kind = 2; idx = -1;
             for (size_t k = 0; k < sphs.size(); ++k) {
@@ -352,7 +392,7 @@ void ref_trace_rays(void *p, int n, const float *o, const float *d, const int *o
             }
         }
         before = isect.length_;
-        isect = s.bvhTriangles_.trace(isect);
+        isect = traceTriangles(isect);
         if (isect.length_ < before) { kind = 3; idx = static_cast<int>(static_cast<const Triangle *>(isect.primitive_) - tris.data()); }
         if (!shadow) {
             before = isect.length_;
@@ -370,6 +410,19 @@ void ref_trace_rays(void *p, int n, const float *o, const float *d, const int *o
         if (outNormal != nullptr) { for (int k = 0; k < 3; ++k) outNormal[3 * i + k] = isect.normal_[k]; }
     }
     errno = 0;
+}
+
+// The cell lists of the Shader's RegularGrid<T> (kind 0 planes, 1 spheres, 2 triangles; only for a handle created with
+// accelerator 2). params: bounds min, max, cellSizeInverted_, cellSize_ (12 floats). start: 32^3 + 1 offsets; items: the
+// primitive indices cell after cell, sorted ascending inside a cell (the reference's own order depends on thread timing,
+// RegularGrid.hpp:191-203). Returns the number of items, or -1 (items may be null to ask for the count only).
+long long ref_grid_cells(void *p, int kind, float *params, unsigned *start, int *items, long long cap) {
+    Shader &s = *static_cast<RefHandle *>(p)->renderer->shader_;
+    errno = 0;
+    if (s.accelerator_ != Shader::ACC_REGULAR_GRID) { return -1; }
+    if (kind == 0) { return gridCells(s.gridPlanes_, params, start, items, cap); }
+    if (kind == 1) { return gridCells(s.gridSpheres_, params, start, items, cap); }
+    return gridCells(s.gridTriangles_, params, start, items, cap);
 }
 
 // Shader::rayTrace (Shader.cpp:86) on arbitrary rays of the given depth -> rgb.

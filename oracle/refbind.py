@@ -59,6 +59,8 @@ def lib():
         L.ref_generate_rays.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]
         L.ref_trace_rays.argtypes = [C.c_void_p, C.c_int] + [C.c_void_p] * 10
         L.ref_shade_rays.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
+        L.ref_grid_cells.restype = C.c_longlong
+        L.ref_grid_cells.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_longlong]
         L.ref_triangle_intersect.restype = C.c_float
         L.ref_triangle_intersect.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_int, C.c_void_p]
         L.ref_triangle_build.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]
@@ -236,6 +238,18 @@ class RefRenderer:
         nrm = np.zeros((n, 3), np.float32)
         lib().ref_trace_rays(self.h, n, _p(o), _p(d), _p(ok), _p(oi), _p(sd), _p(t), _p(kind), _p(idx), _p(mat), _p(nrm))
         return {"t": t, "kind": kind, "idx": idx, "mat": mat, "normal": nrm}
+
+    def grid_cells(self, kind):
+        """Cell lists of the Shader's RegularGrid<T> (handle created with accelerator=2): kind 0 planes, 1 spheres, 2 triangles.
+        Returns (params[12] = bounds min, max, cellSizeInverted_, cellSize_; start[32^3 + 1]; items sorted inside each cell)."""
+        params = np.zeros(12, np.float32)
+        start = np.zeros(32 ** 3 + 1, np.uint32)
+        n = lib().ref_grid_cells(self.h, kind, _p(params), _p(start), None, 0)
+        if n < 0:
+            raise RuntimeError("the reference handle was not created with the RegularGrid accelerator")
+        items = np.zeros(max(int(n), 1), np.int32)
+        lib().ref_grid_cells(self.h, kind, _p(params), _p(start), _p(items), int(n))
+        return params, start, items[:int(n)]
 
     def shade(self, o, d, depth=1):
         o = np.ascontiguousarray(o, np.float32).reshape(-1, 3)

@@ -37,17 +37,17 @@ def camera_from_config(scene_index, ratio, cam_file=None):
     return loaders.load_camera(cam_file, np.float32(ratio))
 
 
-def gpu_from_ref(refbind, r, scene_index, shader, width, height, spp=1, spl=1, flags=0, cam_file=None, seed=1, samplers=0):
+def gpu_from_ref(refbind, r, scene_index, shader, width, height, spp=1, spl=1, flags=0, cam_file=None, seed=1, samplers=0, accelerator=None):
     """GPU renderer over exactly the reference's scene, camera and (current) sampler tables.
     samplers=1: the Android front-end's StaticPCG for pixel jitter, OBJ lights and russian roulette (RefRenderer(samplers=1))."""
     from mobileraytracer_b200 import capi
     arrays = scene_arrays_from_ref(r)
     tables = {"tile_order": refbind.table("tile"), "shader_table": refbind.table("shader"),
               "static_halton": refbind.table("static_halton")}
-    kw = {}
+    kw = {} if accelerator is None else {"accelerator": accelerator}
     if samplers == 1:
         tables["static_pcg"] = refbind.table("static_pcg")
-        kw = dict(light_sampler=capi.SAMPLER_STATIC_PCG,
+        kw.update(light_sampler=capi.SAMPLER_STATIC_PCG,
                   pixel_sampler=capi.SAMPLER_STATIC_PCG if spp > 1 else capi.SAMPLER_CONSTANT)
     cam = camera_from_config(scene_index, np.float32(width) / np.float32(height), cam_file)
     max_point = S.BUILTIN[scene_index][2] if scene_index in S.BUILTIN else (1, 1, 1)
