@@ -237,6 +237,22 @@ const char *mrt_last_error(mrt_handle *h);
 int mrt_trace_rays(mrt_handle *h, int64_t n, const float *origins, const float *directions,
                    const int32_t *origin_kind, const int32_t *origin_idx, const float *shadow_dist,
                    float *out_t, int32_t *out_kind, int32_t *out_idx, int32_t *out_material, float *out_normal);
+/* mrt_trace_rays without any allocation. No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same results as mrt_trace_rays, through the persistent extend / shadow kernels (the RegularGrid kernels on an
+ * MRT_ACC_REGULAR_GRID handle), on any handle. Differences:
+ *  - every array is a DEVICE pointer the caller owns (inputs and outputs; origin_kind / origin_idx / shadow_dist / out_normal
+ *    may be NULL, origin_kind and origin_idx only together); the call returns after the handle's stream has finished;
+ *  - the kernels' ray / hit / shadow queues live in a static device array of the library, MRT_STATIC_TRACE_MAX_RAYS = 65536
+ *    rays (7.1 MiB that every GPU which loads the library holds until the process exits); n beyond that is rejected with
+ *    MRT_ERR_INVALID and a message naming the limit. The call performs no cudaMalloc / cudaFree / allocating library call;
+ *  - every call on a GPU shares that array: calls that overlap on one GPU (two handles, two threads, two streams) race on it.
+ *    Serialise them. The array keeps the last call's records; the call clears the counters it needs to start at zero;
+ *  - origin_kind[i] may be 0 (no primitive to skip) or 3 (triangle origin_idx[i]); plane origins (1) are not remapped here. */
+#define MRT_STATIC_TRACE_MAX_RAYS 65536
+int mrt_trace_rays_static(mrt_handle *h, int64_t n, const float *d_origins, const float *d_directions,
+                          const int32_t *d_origin_kind, const int32_t *d_origin_idx, const float *d_shadow_dist,
+                          float *d_out_t, int32_t *d_out_kind, int32_t *d_out_idx, int32_t *d_out_material, float *d_out_normal);
 /* Camera::generateRay (Perspective.cpp:16-28, Orthographic.cpp:15-23) for n (u,v,du,dv) tuples. HOST arrays. */
 int mrt_generate_rays(mrt_handle *h, int64_t n, const float *uvdd, float *out_origins, float *out_directions);
 /* Shader::rayTrace (Shader.cpp:86) on arbitrary rays of the given depth -> rgb (deterministic shaders). HOST arrays. */

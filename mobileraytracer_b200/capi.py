@@ -13,6 +13,7 @@ ACC_NAIVE, ACC_REGULAR_GRID, ACC_BVH, ACC_B200 = 1, 2, 3, 4
 SAMPLER_AUTO, SAMPLER_CONSTANT, SAMPLER_STATIC_HALTON, SAMPLER_STATIC_MT, SAMPLER_STATIC_PCG, SAMPLER_HALTON, SAMPLER_STRATIFIED, SAMPLER_STREAM = range(8)
 FLAG_FP32_ACCUMULATE, FLAG_SORT_BY_MATERIAL, FLAG_REPLAY_SAMPLERS, FLAG_PROGRESSIVE = 1, 2, 4, 8
 CAMERA_PERSPECTIVE, CAMERA_ORTHOGRAPHIC = 0, 1
+STATIC_TRACE_MAX_RAYS = 65536   # MRT_STATIC_TRACE_MAX_RAYS
 LIGHT_POINT, LIGHT_AREA = 0, 1
 
 # numpy mirrors of the C records (the reference's own layouts, Triangle.hpp:18-27 etc.)
@@ -70,7 +71,7 @@ class Stats(C.Structure):
 # every symbol include/mobilert_b200.h declares
 SYMBOLS = ["mrt_create", "mrt_destroy", "mrt_render_frame", "mrt_render_frame_device", "mrt_render_accumulate_device",
            "mrt_resolve_device", "mrt_set_camera", "mrt_set_pixel_stream", "mrt_set_stream", "mrt_stop", "mrt_set_replay_counter", "mrt_get_replay_counter", "mrt_get_sample", "mrt_get_total_rays", "mrt_get_stats",
-           "mrt_last_error", "mrt_trace_rays", "mrt_generate_rays", "mrt_shade_rays", "mrt_device_count", "mrt_version"]
+           "mrt_last_error", "mrt_trace_rays", "mrt_trace_rays_static", "mrt_generate_rays", "mrt_shade_rays", "mrt_device_count", "mrt_version"]
 # every symbol include/mobilert_b200_test.h declares (libmobilert_b200_test.so: the device functions one call at a time)
 TEST_SYMBOLS = ["mrt_test_triangle_intersect", "mrt_test_sphere_intersect", "mrt_test_plane_intersect", "mrt_test_aabb_intersect",
                 "mrt_test_incremental_avg", "mrt_test_halton", "mrt_test_build_grid", "mrt_test_last_error"]
@@ -113,6 +114,8 @@ def lib():
         L.mrt_last_error.argtypes = [vp]
         L.mrt_last_error.restype = C.c_char_p
         L.mrt_trace_rays.argtypes = [vp, i64] + [vp] * 10
+        if hasattr(L, "mrt_trace_rays_static"):   # absent from older diagnostic builds loaded through MRT_B200_LIB
+            L.mrt_trace_rays_static.argtypes = [vp, i64] + [vp] * 10
         L.mrt_generate_rays.argtypes = [vp, i64, vp, vp, vp]
         L.mrt_shade_rays.argtypes = [vp, i64, vp, vp, i32, vp]
         L.mrt_device_count.restype = C.c_int

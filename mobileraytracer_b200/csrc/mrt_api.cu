@@ -933,6 +933,33 @@ int mrt_trace_rays(mrt_handle *h, int64_t n, const float *origins, const float *
     return MRT_OK;
 }
 
+// No counterpart in the reference: mrt_trace_rays for callers that may not
+// allocate. DEVICE arrays in and out, the kernels' queue scratch in a static device array (mrt_wavefront.cu); no cudaMalloc,
+// cudaFree or any allocating routine on this path.
+int mrt_trace_rays_static(mrt_handle *h, int64_t n, const float *d_origins, const float *d_directions, const int32_t *d_origin_kind,
+                          const int32_t *d_origin_idx, const float *d_shadow_dist, float *d_out_t, int32_t *d_out_kind, int32_t *d_out_idx,
+                          int32_t *d_out_material, float *d_out_normal) {
+    if (!h || n < 0 || !d_origins || !d_directions || !d_out_t || !d_out_kind || !d_out_idx || !d_out_material) { return fail(h, MRT_ERR_INVALID, "bad argument"); }
+    if ((d_origin_kind == nullptr) != (d_origin_idx == nullptr)) { return fail(h, MRT_ERR_INVALID, "origin_kind and origin_idx go together"); }
+    if (static_cast<uint64_t>(n) > wavefront_static_capacity()) {
+        return fail(h, MRT_ERR_INVALID, "mrt_trace_rays_static: n = " + std::to_string(n) + " exceeds the static scratch capacity of " +
+                                        std::to_string(wavefront_static_capacity()) + " rays (MRT_STATIC_TRACE_MAX_RAYS); split the batch or use mrt_trace_rays");
+    }
+    API_CUDA(h, cudaSetDevice(h->device));
+    cudaStream_t st = h->stream;
+    const size_t N = static_cast<size_t>(n);
+    if (d_out_normal) { API_CUDA(h, cudaMemsetAsync(d_out_normal, 0, 3 * N * sizeof(float), st)); }
+    API_CUDA(h, cudaMemsetAsync(h->d_counters.p, 0, sizeof(DeviceCounters), st));
+    API_CUDA(h, wavefront_trace_rays_static(h->scene, n, d_origins, d_directions, d_origin_kind, d_origin_idx, d_shadow_dist, d_out_t, d_out_kind,
+                                            d_out_idx, d_out_material, d_out_normal, h->d_counters.as<DeviceCounters>(), st));
+    DeviceCounters hc {};
+    API_CUDA(h, cudaMemcpyAsync(&hc, h->d_counters.p, sizeof(hc), cudaMemcpyDeviceToHost, st));
+    API_CUDA(h, cudaStreamSynchronize(st));
+    if (hc.overflow) { return fail(h, MRT_ERR_OVERFLOW, "traversal stack overflow"); }
+    errno = 0;
+    return MRT_OK;
+}
+
 int mrt_generate_rays(mrt_handle *h, int64_t n, const float *uvdd, float *out_origins, float *out_directions) {
     if (!h || n < 0 || !uvdd || !out_origins || !out_directions) { return fail(h, MRT_ERR_INVALID, "bad argument"); }
     API_CUDA(h, cudaSetDevice(h->device));

@@ -17,6 +17,7 @@
 #include "mrt_wavefront.h"
 #include "mrt_shade.cuh"
 #include <cstdlib>
+#include <mutex>
 #include <vector>
 
 namespace mrt {
@@ -1123,6 +1124,70 @@ cudaError_t wavefront_trace_rays(Wavefront *w, const SceneDev &s, int64_t n, con
     if (n == 0) { return cudaSuccess; }
     WF_TRY(cudaMemsetAsync(Q.counts, 0, kWfCounts * sizeof(uint32_t), st));
     const int blocks = static_cast<int>((n + 255) / 256), grid = w->sm_count * MRT_TRAV_MIN_BLOCKS;
+    k_wf_test_fill<<<blocks, 256, 0, st>>>(Q, n, d_o, d_d, d_okind, d_oidx, d_sdist);
+    if (s.grid) {
+        k_wf_extend_grid<<<grid, 256, 0, st>>>(s, Q, kTestLevel);
+        k_wf_shadow_grid<<<grid, 256, 0, st>>>(s, Q);
+    } else {
+        k_wf_extend<<<grid, kWfThreads, 0, st>>>(s, Q, kTestLevel, dc);
+        k_wf_shadow<<<grid, kWfThreads, 0, st>>>(s, Q, dc);
+    }
+    k_wf_test_gather<<<blocks, 256, 0, st>>>(s, Q, d_t, d_kind, d_idx, d_mat, d_normal);
+    return cudaGetLastError();
+}
+
+// ---- the same per-ray path without any allocation (mrt_trace_rays_static, include/mobilert_b200.h) -------------------
+// The queues the extend / shadow kernels work on are scratch memory; here they live in a file-scope device array instead of
+// cudaMalloc'ed buffers, so that a caller that may not allocate (stream capture, a tight serving loop) can still trace rays.
+// Every GPU that loads the library holds the array until the process exits. All calls share it and it keeps the previous
+// call's contents: the counters at its start are cleared per call, every other record that is read was written by the same
+// call first. Calls that overlap on one GPU race on it.
+//   [0, 256)                     kWfCounts counters (Queues::counts)
+//   7 x kStaticRays x 16 bytes   r0 r1 r3 hit s0 s1 s2
+//   kStaticRays bytes            vis
+constexpr uint32_t kStaticRays = MRT_STATIC_TRACE_MAX_RAYS;
+constexpr size_t kStaticScratchBytes = 256 + static_cast<size_t>(kStaticRays) * (7 * sizeof(float4) + 1);
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mutex;
+unsigned char *g_static_ptr[kMaxDevices];   // device address of g_static_scratch on each device (the symbol itself is not one)
+int g_static_sms[kMaxDevices];
+}  // namespace
+
+uint32_t wavefront_static_capacity() { return kStaticRays; }
+
+cudaError_t wavefront_trace_rays_static(const SceneDev &s, int64_t n, const float *d_o, const float *d_d, const int32_t *d_okind,
+                                        const int32_t *d_oidx, const float *d_sdist, float *d_t, int32_t *d_kind, int32_t *d_idx, int32_t *d_mat,
+                                        float *d_normal, DeviceCounters *dc, cudaStream_t st) {
+    if (n < 0 || static_cast<uint64_t>(n) > kStaticRays) { return cudaErrorInvalidValue; }
+    if (n == 0) { return cudaSuccess; }
+    int dev = -1;
+    WF_TRY(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) { return cudaErrorInvalidDevice; }
+    unsigned char *base = nullptr;
+    int sms = 0;
+    {
+        std::lock_guard<std::mutex> lock(g_static_mutex);
+        if (g_static_ptr[dev] == nullptr) {   // once per device, with that device current
+            void *p = nullptr;
+            WF_TRY(cudaGetSymbolAddress(&p, g_static_scratch));
+            WF_TRY(cudaDeviceGetAttribute(&g_static_sms[dev], cudaDevAttrMultiProcessorCount, dev));
+            g_static_ptr[dev] = static_cast<unsigned char *>(p);
+        }
+        base = g_static_ptr[dev];
+        sms = g_static_sms[dev];
+    }
+    Queues Q {};
+    Q.counts = reinterpret_cast<uint32_t *>(base);
+    float4 *rec = reinterpret_cast<float4 *>(base + 256);
+    Q.r0[0] = rec; Q.r1[0] = rec + kStaticRays; Q.r3[0] = rec + 2ull * kStaticRays; Q.hit = rec + 3ull * kStaticRays;
+    Q.s0 = rec + 4ull * kStaticRays; Q.s1 = rec + 5ull * kStaticRays; Q.s2 = rec + 6ull * kStaticRays;
+    Q.vis = reinterpret_cast<uint8_t *>(rec + 7ull * kStaticRays);
+    Q.cap_rays = kStaticRays; Q.cap_shadow = kStaticRays; Q.cap_chains = 0;
+    WF_TRY(cudaMemsetAsync(Q.counts, 0, kWfCounts * sizeof(uint32_t), st));
+    const int blocks = static_cast<int>((n + 255) / 256), grid = sms * MRT_TRAV_MIN_BLOCKS;
     k_wf_test_fill<<<blocks, 256, 0, st>>>(Q, n, d_o, d_d, d_okind, d_oidx, d_sdist);
     if (s.grid) {
         k_wf_extend_grid<<<grid, 256, 0, st>>>(s, Q, kTestLevel);

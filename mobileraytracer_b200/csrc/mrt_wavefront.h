@@ -39,6 +39,16 @@ cudaError_t wavefront_trace_rays(Wavefront *w, const SceneDev &s, int64_t n, con
                                  const int32_t *d_oidx, const float *d_sdist, float *d_t, int32_t *d_kind, int32_t *d_idx, int32_t *d_mat,
                                  float *d_normal, DeviceCounters *dc, cudaStream_t st);
 
+// The same, allocation-free: the queues are a file-scope device array of wavefront_static_capacity() rays (mrt_wavefront.cu,
+// g_static_scratch), shared by every call on a device. No Wavefront object is needed. n beyond the capacity: cudaErrorInvalidValue.
+#ifndef MRT_STATIC_TRACE_MAX_RAYS
+#define MRT_STATIC_TRACE_MAX_RAYS 65536
+#endif
+uint32_t wavefront_static_capacity();
+cudaError_t wavefront_trace_rays_static(const SceneDev &s, int64_t n, const float *d_o, const float *d_d, const int32_t *d_okind,
+                                        const int32_t *d_oidx, const float *d_sdist, float *d_t, int32_t *d_kind, int32_t *d_idx, int32_t *d_mat,
+                                        float *d_normal, DeviceCounters *dc, cudaStream_t st);
+
 // After the stream has been synchronised: adds the device time of every launch since the last call, per kernel class.
 cudaError_t wavefront_collect_times(Wavefront *w, WavefrontTimes *times);
 
