@@ -108,6 +108,7 @@ MRT_D uint2 stack_get(const TravMem &tm, int i) { return tm.stack[i]; }
 
 #ifdef MRT_TRAVERSAL_STATS
 static __device__ unsigned long long g_stat_nodes, g_stat_tris, g_stat_rays;   // one copy per translation unit
+static __device__ unsigned long long g_stat_fruitless, g_stat_stale;           // node visits that hit no child / that hit none only because of tbest
 #define MRT_STAT(x) x
 #else
 #define MRT_STAT(x)
@@ -234,6 +235,20 @@ MRT_D bool trav8_node_core(const SceneDev &s, Trav8 &t, TravMem &tm_, uint32_t &
     MRT_CHILD(0, nx1, ny1, nz1, fx1, fy1, fz1, 4) MRT_CHILD(1, nx1, ny1, nz1, fx1, fy1, fz1, 5)
     MRT_CHILD(2, nx1, ny1, nz1, fx1, fy1, fz1, 6) MRT_CHILD(3, nx1, ny1, nz1, fx1, fy1, fz1, 7)
 #undef MRT_CHILD
+#endif
+#ifdef MRT_TRAVERSAL_STATS
+    if (hits == 0u) {
+        atomicAdd(&g_stat_fruitless, 1ull);
+        uint32_t far = 0u;   // the same eight tests without the tbest bound
+#define MRT_CHILD(B, NX, NY, NZ, FX, FY, FZ, K) \
+        if (child_hit<B>(NX, NY, NZ, FX, FY, FZ, ax, ay, az, ox0, oy0, oz0, ox1, oy1, oz1, 1.0e30f, one)) { far |= 1u << (K); }
+        MRT_CHILD(0, nx0, ny0, nz0, fx0, fy0, fz0, 0) MRT_CHILD(1, nx0, ny0, nz0, fx0, fy0, fz0, 1)
+        MRT_CHILD(2, nx0, ny0, nz0, fx0, fy0, fz0, 2) MRT_CHILD(3, nx0, ny0, nz0, fx0, fy0, fz0, 3)
+        MRT_CHILD(0, nx1, ny1, nz1, fx1, fy1, fz1, 4) MRT_CHILD(1, nx1, ny1, nz1, fx1, fy1, fz1, 5)
+        MRT_CHILD(2, nx1, ny1, nz1, fx1, fy1, fz1, 6) MRT_CHILD(3, nx1, ny1, nz1, fx1, fy1, fz1, 7)
+#undef MRT_CHILD
+        if (far != 0u) { atomicAdd(&g_stat_stale, 1ull); }
+    }
 #endif
     // inner children: bit (slot ^ octinv), so that the highest pending bit is always the nearest child along the ray
     // (slot s of a node holds the child lying towards +axis k for every set bit k of s, see k_collapse8)

@@ -1052,10 +1052,15 @@ cudaError_t wavefront_resolve_batch(Wavefront *w, const uint32_t *d_tile_base, i
 
 #ifdef MRT_TRAVERSAL_STATS
 // diagnostic library only: node visits / triangle tests / rays of the wavefront kernels since the last reset
-extern "C" int mrt_debug_traversal_stats(unsigned long long out[3], int reset) {
+extern "C" int mrt_debug_traversal_stats(unsigned long long out[5], int reset) {
     cudaDeviceSynchronize();
     cudaMemcpyFromSymbol(&out[0], mrt::g_stat_nodes, 8); cudaMemcpyFromSymbol(&out[1], mrt::g_stat_tris, 8); cudaMemcpyFromSymbol(&out[2], mrt::g_stat_rays, 8);
-    if (reset) { const unsigned long long z = 0; cudaMemcpyToSymbol(mrt::g_stat_nodes, &z, 8); cudaMemcpyToSymbol(mrt::g_stat_tris, &z, 8); cudaMemcpyToSymbol(mrt::g_stat_rays, &z, 8); }
+    cudaMemcpyFromSymbol(&out[3], mrt::g_stat_fruitless, 8); cudaMemcpyFromSymbol(&out[4], mrt::g_stat_stale, 8);
+    if (reset) {
+        const unsigned long long z = 0;
+        cudaMemcpyToSymbol(mrt::g_stat_nodes, &z, 8); cudaMemcpyToSymbol(mrt::g_stat_tris, &z, 8); cudaMemcpyToSymbol(mrt::g_stat_rays, &z, 8);
+        cudaMemcpyToSymbol(mrt::g_stat_fruitless, &z, 8); cudaMemcpyToSymbol(mrt::g_stat_stale, &z, 8);
+    }
     return 0;
 }
 #endif
