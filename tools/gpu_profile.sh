@@ -13,4 +13,4 @@ for k in extend shadow shade; do
   ncu --set full --clock-control none --import-source on -k regex:k_wf_$k -s 1 -c 1 -o gpurun_out/${T}_$k -f python tools/profile_frame.py --spp 16 > gpurun_out/${T}_${k}_ncu.log 2>&1
   tail -1 gpurun_out/${T}_${k}_ncu.log
 done
-MRT_B200_LIB=$PWD/mobileraytracer_b200/libmobilert_b200_stats.so python tools/traversal_stats.py 2>&1 | tail -1 | tee gpurun_out/${T}_traversal_stats.txt
+MRT_B200_LIB=$PWD/mobileraytracer_b200/libmobilert_b200_stats.so python tools/traversal_stats.py 2>&1 | tail -2 | tee gpurun_out/${T}_traversal_stats.txt
