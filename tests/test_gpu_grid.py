@@ -163,3 +163,31 @@ def test_grid_pathtracer_frame_is_statistically_the_reference_grid(mrt, ref):
     assert abs(mine.mean() - mean_ref.mean()) <= 0.02 * mean_ref.mean() + 0.5
     g.close()
     r.close()
+
+
+@pytest.mark.parametrize("shader", [1, 2, 3])
+def test_grid_mode_on_an_empty_scene_and_on_one_primitive(mrt, shader):
+    """Degenerate inputs of the grid build: no primitives at all (bounds stay at +-RayLengthMax, every ray misses), and a single
+    triangle (its grid has zero extent on one axis: the cell range collapses to cell 0 there, RegularGrid.hpp:243-259)."""
+    from mobileraytracer_b200 import scene as S
+    capi = mrt.capi
+    w, h = 64, 48
+    cam = S.Camera(capi.CAMERA_PERSPECTIVE, (0, 0, -3), (0, 0, 0), (0, 1, 0), 45.0, 45.0)
+    g = mrt.Renderer(S.Scene(), cam, w, h, 2, 1, shader, accelerator=capi.ACC_REGULAR_GRID)
+    bm = g.renderFrame()
+    assert (np.asarray(bm).reshape(-1).view(np.uint32) == 0xFF000000).all()
+    assert g.getTotalCastedRays() == 2 * w * h
+    g.close()
+    one = S.Scene()
+    m = one.add_material(S.make_material(Kd=(0.5, 0.5, 0.5)))
+    one.triangles_.append(S.make_triangle((-1, -1, 0), (1, -1, 0), (0, 1, 0), material=m))
+    gg = mrt.Renderer(one, cam, w, h, 1, 1, shader, accelerator=capi.ACC_REGULAR_GRID)
+    gb = mrt.Renderer(one, cam, w, h, 1, 1, shader)
+    o = np.tile(np.array([[0.0, 0.0, -3.0]], np.float32), (4, 1))
+    d = np.array([[0, 0, 1], [0.05, 0.02, 1], [1, 0, 0], [0, 0, -1]], np.float32)
+    d = (d / np.linalg.norm(d, axis=1, keepdims=True)).astype(np.float32)
+    a, b = gg.traceRays(o, d), gb.traceRays(o, d)
+    assert list(a["kind"]) == [3, 3, 0, 0] and np.array_equal(a["kind"], b["kind"]) and np.array_equal(a["t"], b["t"])
+    gg.close()
+    gb.close()
+
