@@ -322,52 +322,48 @@ int upload_scene(mrt_handle *h, const mrt_scene_desc &sc) {
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     h->stats.upload_ms = ms;
     h->stats.n_primitives = nt + sc.n_spheres + sc.n_planes;
+    SceneDev &s = h->scene;
+    const size_t records_bytes = shade.size() * sizeof(TriShade) + mats.size() * sizeof(MaterialRec) + lights.size() * sizeof(LightRec);
     if (h->grid) {
         // no BVH8: the grids are the acceleration structure (built on the host above; build_ms is that wall time)
         h->stats.build_ms = grid_build_ms;
         h->stats.bvh_nodes = 0;
         h->stats.bvh_bytes = grid_bytes;
-        h->stats.scene_bytes = grid_bytes + shade.size() * sizeof(TriShade) + mats.size() * sizeof(MaterialRec) + lights.size() * sizeof(LightRec);
-        SceneDev &s = h->scene;
-        s.grid = 1; s.naive = 0; s.prmt_one = 0x3F800000u;
-        s.tune_postpone = 12; s.tune_refill = 26; s.tune_wait = 20; s.tune_wait_any = 24;
-        s.nodes = nullptr; s.tri_geom = h->d_grid_tris.as<TriGeom>(); s.tri_shade = h->d_tri_shade.as<TriShade>();
-        s.n_triangles = static_cast<int32_t>(nt); s.n_bvh_prims = static_cast<int32_t>(nt);
-        s.sphere_nodes = h->d_sphere_nodes.as<RefNode>(); s.spheres = h->d_spheres.as<SphereRec>(); s.n_spheres = static_cast<int32_t>(sc.n_spheres);
-        s.plane_nodes = h->d_plane_nodes.as<RefNode>(); s.planes = h->d_planes.as<PlaneRec>(); s.n_planes = static_cast<int32_t>(sc.n_planes);
-        s.materials = h->d_materials.as<MaterialRec>(); s.n_materials = static_cast<int32_t>(sc.n_materials);
-        s.textures = h->d_textures.as<TextureRec>(); s.texels = h->d_texels.as<uint8_t>(); s.n_textures = static_cast<int32_t>(sc.n_textures);
-        s.lights = h->d_lights.as<LightRec>(); s.n_lights = static_cast<int32_t>(nl);
-        return MRT_OK;
+        h->stats.scene_bytes = grid_bytes + records_bytes;
+        s.grid = 1;
+        s.nodes = nullptr; s.tri_geom = h->d_grid_tris.as<TriGeom>();
+        s.n_bvh_prims = static_cast<int32_t>(nt);
+    } else {
+        // acceleration structure over triangles + light triangles, on the GPU
+        // binned-SAH hierarchy by default; MRT_B200_BVH=lbvh selects the Morton-order hierarchy (build-speed / quality experiments)
+        const char *bvh_env = std::getenv("MRT_B200_BVH");
+        const char *leaf_env = std::getenv("MRT_B200_LEAF");   // triangles per leaf slot, 1..7 (tuning experiments)
+        const uint32_t leaf = leaf_env ? static_cast<uint32_t>(std::atoi(leaf_env)) & 7u : 4u;
+        const char *fat_env = std::getenv("MRT_B200_FATLEAF");   // 1: never split a subtree that fits one leaf slot (tuning experiments)
+        const uint32_t build_flags = ((bvh_env && std::strcmp(bvh_env, "lbvh") == 0) ? 0u : 1u) | (leaf << 8) | ((fat_env && std::atoi(fat_env)) ? 2u : 0u);
+        API_CUDA(h, build_bvh8(h->d_tris9.as<float>(), static_cast<int>(nprims), build_flags, st, &h->bvh));
+        h->stats.build_ms = h->bvh.build_ms;
+        h->stats.bvh_nodes = h->bvh.n_nodes;
+        h->stats.bvh_bytes = h->bvh.bytes();
+        h->stats.scene_bytes = h->bvh.bytes() + records_bytes;
+        h->d_tris9.release();   // geometry now lives in the BVH8 leaf array
+        s.grid = 0;
+        s.nodes = h->bvh.nodes; s.tri_geom = h->bvh.tri_geom;
+        s.n_bvh_prims = static_cast<int32_t>(nprims);
     }
-    // acceleration structure over triangles + light triangles, on the GPU
-    // binned-SAH hierarchy by default; MRT_B200_BVH=lbvh selects the Morton-order hierarchy (build-speed / quality experiments)
-    const char *bvh_env = std::getenv("MRT_B200_BVH");
-    const char *leaf_env = std::getenv("MRT_B200_LEAF");   // triangles per leaf slot, 1..7 (tuning experiments)
-    const uint32_t leaf = leaf_env ? static_cast<uint32_t>(std::atoi(leaf_env)) & 7u : 4u;
-    const char *fat_env = std::getenv("MRT_B200_FATLEAF");   // 1: never split a subtree that fits one leaf slot (tuning experiments)
-    const uint32_t build_flags = ((bvh_env && std::strcmp(bvh_env, "lbvh") == 0) ? 0u : 1u) | (leaf << 8) | ((fat_env && std::atoi(fat_env)) ? 2u : 0u);
-    API_CUDA(h, build_bvh8(h->d_tris9.as<float>(), static_cast<int>(nprims), build_flags, st, &h->bvh));
-    h->stats.build_ms = h->bvh.build_ms;
-    h->stats.bvh_nodes = h->bvh.n_nodes;
-    h->stats.bvh_bytes = h->bvh.bytes();
-    h->stats.scene_bytes = h->bvh.bytes() + shade.size() * sizeof(TriShade) + mats.size() * sizeof(MaterialRec) + lights.size() * sizeof(LightRec);
-    h->stats.n_primitives = nt + sc.n_spheres + sc.n_planes;
-    h->d_tris9.release();   // geometry now lives in the BVH8 leaf array
-    SceneDev &s = h->scene;
     {
         const char *tp = std::getenv("MRT_B200_POSTPONE"), *tr = std::getenv("MRT_B200_REFILL");   // tuning experiments only
         s.tune_postpone = tp ? std::atoi(tp) : 12;
         s.tune_refill = tr ? std::atoi(tr) : 26;
         s.prmt_one = 0x3F800000u;
-        s.naive = h->naive ? 1 : 0;
+        s.naive = (h->naive && !h->grid) ? 1 : 0;
         const char *tw = std::getenv("MRT_B200_WAIT");
         s.tune_wait = tw ? std::atoi(tw) : 20;
         const char *twa = std::getenv("MRT_B200_WAIT_ANY");
         s.tune_wait_any = twa ? std::atoi(twa) : (tw ? std::atoi(tw) : 24);
     }
-    s.nodes = h->bvh.nodes; s.tri_geom = h->bvh.tri_geom; s.tri_shade = h->d_tri_shade.as<TriShade>();
-    s.n_triangles = static_cast<int32_t>(nt); s.n_bvh_prims = static_cast<int32_t>(nprims);
+    s.tri_shade = h->d_tri_shade.as<TriShade>();
+    s.n_triangles = static_cast<int32_t>(nt);
     s.sphere_nodes = h->d_sphere_nodes.as<RefNode>(); s.spheres = h->d_spheres.as<SphereRec>(); s.n_spheres = static_cast<int32_t>(sc.n_spheres);
     s.plane_nodes = h->d_plane_nodes.as<RefNode>(); s.planes = h->d_planes.as<PlaneRec>(); s.n_planes = static_cast<int32_t>(sc.n_planes);
     s.materials = h->d_materials.as<MaterialRec>(); s.n_materials = static_cast<int32_t>(sc.n_materials);
