@@ -559,10 +559,15 @@ int mrt_create(const mrt_scene_desc *scene, const mrt_camera_desc *camera, const
             const char *sk = std::getenv("MRT_B200_SORT_KEY");   // diagnostic: "primitive" bins by primitive id instead of material
             const int sort_mode = (render->flags & MRT_FLAG_SORT_BY_MATERIAL) ? ((sk && std::strcmp(sk, "primitive") == 0) ? 2 : 1) : 0;
             const char *be = std::getenv("MRT_B200_BATCH");   // samples traced together per wavefront pass
-            // default: up to 16 samples per pass, as long as the queues (about 390 + 100 * samples_light bytes per pixel and sample) stay below 32 GB
+            // default: as few equally large passes as keep the queues (about 390 + 100 * samples_light bytes per pixel and sample) below
+            // 40 GB. Every pass ends with the persistent kernels of each level draining, so fewer, larger passes are faster: the 64-spp
+            // frame of config 4 takes 182.8 ms in four passes of 16, 181.1 in two of 32 (33 GB), 180.3 in one of 64 (65 GB).
             const double per_sample = (390.0 + 100.0 * std::max(1, render->samples_light)) * static_cast<double>(std::max<uint32_t>(h->roots_per_sample, 1u));
-            const int by_memory = static_cast<int>(std::max(1.0, std::min(16.0, 32.0e9 / std::max(per_sample, 1.0))));
-            const int batch = std::max(1, std::min(be ? std::atoi(be) : by_memory, render->samples_pixel));
+            const int cap = static_cast<int>(std::max(1.0, std::min(static_cast<double>(kWfMaxBatch), 40.0e9 / std::max(per_sample, 1.0))));
+            const int spp = std::max(1, render->samples_pixel);
+            const int passes = (spp + cap - 1) / cap;
+            const int balanced = (spp + passes - 1) / passes;
+            const int batch = std::max(1, std::min(be ? std::atoi(be) : balanced, spp));
             if ((e = wavefront_create(h->roots_per_sample, batch, render->samples_light, sort_mode, static_cast<uint32_t>(h->scene.n_bvh_prims), &h->wavefront)) != cudaSuccess) { rc = cuda_fail(h, e, "wavefront queues"); break; }
         }
         if ((e = cudaStreamSynchronize(h->stream)) != cudaSuccess) { rc = cuda_fail(h, e, "create sync"); break; }

@@ -9,7 +9,7 @@ struct Wavefront;   // opaque: queues, chain records, counters
 
 struct WavefrontTimes { double extend_ms = 0, shadow_ms = 0, shade_ms = 0, other_ms = 0; uint64_t extend_launches = 0; };
 
-constexpr int kWfMaxBatch = 16;
+constexpr int kWfMaxBatch = 64;
 constexpr int kWfCounts = 32;   // Queues::counts entries (see mrt_wavefront.cu)
 // batch: samples of every pixel traced together in one pass (1..kWfMaxBatch); the queues are sized for it and for
 // samples_light shadow rays per hit
