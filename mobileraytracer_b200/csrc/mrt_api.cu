@@ -567,8 +567,14 @@ int mrt_create(const mrt_scene_desc *scene, const mrt_camera_desc *camera, const
             const int spp = std::max(1, render->samples_pixel);
             const int passes = (spp + cap - 1) / cap;
             const int balanced = (spp + passes - 1) / passes;
-            const int batch = std::max(1, std::min(be ? std::atoi(be) : balanced, spp));
-            if ((e = wavefront_create(h->roots_per_sample, batch, render->samples_light, sort_mode, static_cast<uint32_t>(h->scene.n_bvh_prims), &h->wavefront)) != cudaSuccess) { rc = cuda_fail(h, e, "wavefront queues"); break; }
+            int batch = std::max(1, std::min(be ? std::atoi(be) : balanced, spp));
+            // a device that other handles or processes have filled: smaller passes instead of no renderer
+            while ((e = wavefront_create(h->roots_per_sample, batch, render->samples_light, sort_mode, static_cast<uint32_t>(h->scene.n_bvh_prims), &h->wavefront)) == cudaErrorMemoryAllocation && batch > 1) {
+                cudaGetLastError();
+                wavefront_destroy(h->wavefront); h->wavefront = nullptr;   // frees what the failed attempt had allocated
+                batch = (batch + 1) / 2;
+            }
+            if (e != cudaSuccess) { rc = cuda_fail(h, e, "wavefront queues"); break; }
         }
         if ((e = cudaStreamSynchronize(h->stream)) != cudaSuccess) { rc = cuda_fail(h, e, "create sync"); break; }
     } while (false);

@@ -446,3 +446,35 @@ def test_cpp_render_thread_state_machine(mrt, tmp_path):
     f = dict(zip(r.stdout.split()[1::2], r.stdout.split()[2::2]))
     assert int(f["stopped"]) == 1 and 200 <= int(f["final_sample"]) < spp and int(f["state"]) == 0, r.stdout
     assert (np.fromfile(stop_out, np.int32) != 0).mean() > 0.5
+
+
+def test_queues_shrink_instead_of_failing_on_a_full_device(mrt, conf):
+    """mrt_create sizes the wavefront queues for as few passes as fit 40 GB. On a device that something else has filled it
+    must come up with smaller passes (more of them) rather than fail, and render the same accumulators."""
+    import torch
+    from mobileraytracer_b200 import loaders, capi
+    obj, mtl, cam = conf
+    w, h, spp = 1920, 1072, 64
+    arrays = loaders.load_obj(obj, mtl).arrays()
+    camera = loaders.load_camera(cam, np.float32(w) / np.float32(h))
+    roomy = mrt.Renderer(arrays, camera, w, h, spp, 1, capi.SHADER_PATHTRACER, flags=capi.FLAG_FP32_ACCUMULATE, seed=5)
+    a = torch.zeros(h * w, 4, device="cuda")
+    roomy.renderAccumulateDevice(a.data_ptr(), 0, 16)        # 4 of the 64 samples
+    full_bytes = roomy.stats()["queue_bytes"]
+    roomy.close()
+    torch.cuda.synchronize()
+    free, _total = torch.cuda.mem_get_info()
+    if free < (60 << 30):
+        pytest.skip("the device is shared: not enough free memory to stage the experiment")
+    filler = torch.empty(free - (14 << 30), dtype=torch.uint8, device="cuda")   # leave about 14 GB
+    try:
+        tight = mrt.Renderer(arrays, camera, w, h, spp, 1, capi.SHADER_PATHTRACER, flags=capi.FLAG_FP32_ACCUMULATE, seed=5)
+        b = torch.zeros(h * w, 4, device="cuda")
+        tight.renderAccumulateDevice(b.data_ptr(), 0, 16)
+        assert 0 < tight.stats()["queue_bytes"] < full_bytes
+        tight.close()
+    finally:
+        del filler
+        torch.cuda.empty_cache()
+    assert full_bytes > (20 << 30)
+    assert torch.equal(a, b)
