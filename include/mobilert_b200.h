@@ -180,7 +180,10 @@ typedef struct mrt_handle mrt_handle;
 
 /* Replaces: Scene -> Shader subclass ctor (-> Shader::initializeAccelerators, MobileRT/Shader.cpp:33-77, BVH build
  * MobileRT/Accelerators/BVH.hpp:125-283) -> Renderer ctor (MobileRT/Renderer.cpp:25-45), i.e. what work_thread
- * (C_wrapper.cpp:76-203) and rtInitialize (JNI_layer.cpp:465-716) do before the first frame. */
+ * (C_wrapper.cpp:76-203) and rtInitialize (JNI_layer.cpp:465-716) do before the first frame.
+ * Device memory: the scene, and for MRT_SHADER_PATHTRACER the wavefront's ray / shadow queues and path accumulators, sized so
+ * that a frame runs in as few equally large passes as fit 40 GB (about 0.5 KB per pixel and sample of a pass; 31.7 GB for 64 spp
+ * at 1920x1072; mrt_stats::queue_bytes). When that much is not free the handle comes up with smaller passes instead of failing. */
 int mrt_create(const mrt_scene_desc *scene, const mrt_camera_desc *camera, const mrt_render_desc *render,
                const mrt_sampler_tables *tables, mrt_handle **out);
 /* Replaces: ~Renderer / renderer_.reset (C_wrapper.cpp:266, JNI_layer.cpp:406-431). */
