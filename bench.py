@@ -410,7 +410,7 @@ def run_b200(args, wl, height):
             "gather_peaks": gather,
             "phases_ms_per_frame_rank0": {k: v / K for k, v in phases.items()},
             "kernel_ms_per_frame": {"extend": acc["extend_ms"] / K, "shadow": acc["shadow_ms"] / K, "shade": acc["shade_ms"] / K, "other": acc["other_ms"] / K,
-                                    "note": "rank 0's share; CUDA events around every launch on the frame stream"},
+                                    "note": "rank 0's share; CUDA-event intervals around the launches; k_wf_fold (in 'other') runs on a second stream beside the next level's extend kernel, so its interval lies inside that one and the sum exceeds the frame"},
             "rays_per_frame": {"total_all_gpus": rays_frame, "primary": kinds[0], "shadow": kinds[1], "secondary": kinds[2],
                                "extend_traced": kinds[3], "shadow_traced": kinds[4]},
             "kernel_grays_per_s": {"extend_closest_hit": rf_ext["grays_per_s"] if rf_ext else None, "shadow_any_hit": rf_sh["grays_per_s"] if rf_sh else None,

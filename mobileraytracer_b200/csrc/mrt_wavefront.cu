@@ -78,6 +78,10 @@ struct Wavefront {
     std::vector<WfMark> marks;        // one event after every launch; the class says what ran before it
     std::vector<cudaEvent_t> pool;
     size_t used = 0;
+    // fold(level) next to extend(level + 1): see wavefront_trace_batch
+    int overlap = 0;
+    cudaStream_t side = nullptr;
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
 };
 
 // A fresh accumulator, written as two full 16-byte stores: the whole sector is overwritten, so the L2 never has to
@@ -933,6 +937,13 @@ cudaError_t wavefront_create(size_t paths_per_sample, int batch, int spl, int so
     int dev = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&w->sm_count, cudaDevAttrMultiProcessorCount, dev);
+    const char *ov = std::getenv("MRT_B200_OVERLAP");
+    w->overlap = ov ? std::atoi(ov) : 1;   // 0: everything on the frame stream (A/B)
+    if (w->overlap) {
+        WF_TRY(cudaStreamCreateWithFlags(&w->side, cudaStreamNonBlocking));
+        WF_TRY(cudaEventCreateWithFlags(&w->ev_fork, cudaEventDisableTiming));
+        WF_TRY(cudaEventCreateWithFlags(&w->ev_join, cudaEventDisableTiming));
+    }
     return wf_alloc_queues(w, paths_per_sample * static_cast<size_t>(w->batch), 2);
 }
 
@@ -952,6 +963,9 @@ cudaError_t wavefront_grow(Wavefront *w, bool *grown) {
 void wavefront_destroy(Wavefront *w) {
     if (!w) { return; }
     for (cudaEvent_t e : w->pool) { cudaEventDestroy(e); }
+    if (w->side) { cudaStreamSynchronize(w->side); cudaStreamDestroy(w->side); }
+    if (w->ev_fork) { cudaEventDestroy(w->ev_fork); }
+    if (w->ev_join) { cudaEventDestroy(w->ev_join); }
     wf_free_queues(w);
     delete w;
 }
@@ -1005,9 +1019,24 @@ cudaError_t wavefront_trace_batch(Wavefront *w, const SceneDev &s, const CameraR
     WF_TRY(wf_mark(w, WF_OTHER, st));
     *launches += 2;
     const int sgrid = w->sm_count * MRT_SHADE_MIN_BLOCKS;
+    // overlap: k_wf_fold(level) streams the shadow queue at half the HBM rate and nothing needs its result before
+    // k_wf_shade(level + 1), while k_wf_extend(level + 1) is bound by instruction issue. So the extend kernel of the next level is
+    // launched with one CTA per SM fewer right after shadow(level), and fold(level) runs next to it on a second stream in the
+    // registers and thread slots that leaves free (256 threads x 16 registers per CTA, one CTA per SM). The extend kernel gets 4 %
+    // slower, the fold kernels disappear from the critical path: 180.9 -> 178.0 ms per 64-spp frame, 23.25 -> 22.92 ms per 8-spp
+    // frame (profiles/r2_ab_fold_overlap.txt). The per-kernel times the library reports are event intervals: the fold interval now
+    // lies inside the extend interval of the next level.
+    const bool overlap = w->overlap != 0 && !s.grid;
+    const int xgrid = (overlap && w->overlap == 1) ? w->sm_count * (MRT_TRAV_MIN_BLOCKS - 1) : grid;   // overlap == 2 (A/B): full grid, fold only fills the tails (slower)
+    static const int fold_mult = std::getenv("MRT_B200_FOLD_GRID") ? std::atoi(std::getenv("MRT_B200_FOLD_GRID")) : 1;   // CTAs per SM of the overlapped fold (A/B: 1 / 2 / 4 = 177.98 / 178.30 / 178.33 ms)
+    bool extend_launched = false, joined = true;
     for (int level = 0; level < kLevels; ++level) {
-        if (s.grid) { k_wf_extend_grid<<<grid, 256, 0, st>>>(s, Q, level); } else { k_wf_extend<<<grid, kWfThreads, 0, st>>>(s, Q, level, dc); }
-        WF_TRY(wf_mark(w, WF_EXTEND, st));
+        if (!extend_launched) {
+            if (s.grid) { k_wf_extend_grid<<<grid, 256, 0, st>>>(s, Q, level); } else { k_wf_extend<<<grid, kWfThreads, 0, st>>>(s, Q, level, dc); }
+            WF_TRY(wf_mark(w, WF_EXTEND, st));
+        }
+        extend_launched = false;
+        if (!joined) { WF_TRY(cudaStreamWaitEvent(st, w->ev_join, 0)); joined = true; }   // fold(level - 1) has updated the accumulators
         if (Q.perm != nullptr) {
             WF_TRY(cudaMemsetAsync(Q.sort_bins, 0, (kSortBins + 1) * sizeof(uint32_t), st));
             const unsigned sblocks = static_cast<unsigned>((static_cast<size_t>(n_samples) * roots_per_sample * static_cast<size_t>(w->factor) + kSortChunk - 1) / kSortChunk);
@@ -1022,9 +1051,24 @@ cudaError_t wavefront_trace_batch(Wavefront *w, const SceneDev &s, const CameraR
         k_wf_after_shade<<<1, 1, 0, st>>>(Q, level, dc);
         if (s.grid) { k_wf_shadow_grid<<<grid, 256, 0, st>>>(s, Q); } else { k_wf_shadow<<<grid, kWfThreads, 0, st>>>(s, Q, dc); }
         WF_TRY(wf_mark(w, WF_SHADOW, st));
-        k_wf_fold<<<w->sm_count * 8, 256, 0, st>>>(Q);
-        k_wf_after_fold<<<1, 1, 0, st>>>(Q, dc);
-        WF_TRY(wf_mark(w, WF_OTHER, st));
+        if (overlap && level + 1 < kLevels) {
+            WF_TRY(cudaEventRecord(w->ev_fork, st));
+            k_wf_extend<<<xgrid, kWfThreads, 0, st>>>(s, Q, level + 1, dc);                 // first, so that its CTAs are placed first
+            WF_TRY(wf_mark(w, WF_EXTEND, st));
+            extend_launched = true;
+            WF_TRY(cudaStreamWaitEvent(w->side, w->ev_fork, 0));
+            WF_TRY(wf_mark(w, -1, w->side));
+            k_wf_fold<<<w->sm_count * fold_mult, 256, 0, w->side>>>(Q);
+            k_wf_after_fold<<<1, 1, 0, w->side>>>(Q, dc);
+            WF_TRY(wf_mark(w, WF_OTHER, w->side));
+            WF_TRY(cudaEventRecord(w->ev_join, w->side));
+            WF_TRY(wf_mark(w, -1, st));   // the next mark on the frame stream starts a new interval
+            joined = false;
+        } else {
+            k_wf_fold<<<w->sm_count * 8, 256, 0, st>>>(Q);
+            k_wf_after_fold<<<1, 1, 0, st>>>(Q, dc);
+            WF_TRY(wf_mark(w, WF_OTHER, st));
+        }
         *launches += 6;
     }
     for (int level = kLevels - 2; level >= 0; --level) {   // no chain is created while shading the last level
