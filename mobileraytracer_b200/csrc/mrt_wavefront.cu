@@ -938,7 +938,9 @@ cudaError_t wavefront_create(size_t paths_per_sample, int batch, int spl, int so
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&w->sm_count, cudaDevAttrMultiProcessorCount, dev);
     const char *ov = std::getenv("MRT_B200_OVERLAP");
-    w->overlap = ov ? std::atoi(ov) : 1;   // 0: everything on the frame stream (A/B)
+    // on by default while nodes and triangles fit the 126 MB L2 (80 B per 10 primitives + 48 B per primitive): with the 550 MB scene of
+    // config 5 the extend kernel needs its eighth CTA per SM to hide HBM latency and the frame gets 1 % slower instead (197.8 vs 195.9 ms)
+    w->overlap = ov ? std::atoi(ov) : (n_primitives <= 2000000u ? 1 : 0);   // MRT_B200_OVERLAP=0 / 1: A/B
     if (w->overlap) {
         WF_TRY(cudaStreamCreateWithFlags(&w->side, cudaStreamNonBlocking));
         WF_TRY(cudaEventCreateWithFlags(&w->ev_fork, cudaEventDisableTiming));
